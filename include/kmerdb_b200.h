@@ -1,0 +1,137 @@
+/* kmerdb_b200 — C-ABI of the B200-native `profile` hot path of kmerdb v0.9.6.
+ *
+ * The reference has no FFI: its seam for this path is the Python function
+ * kmerdb.parse.parsefile (kmerdb/parse.py:90-163) and the helpers in kmerdb/kmer.py.  The entry
+ * points below are what a ctypes binding inside kmerdb/parse.py would call instead of the
+ * per-window Python loop (INTEGRATION.md shows that stub).  Plain C types only, caller-allocated
+ * outputs, int status returns, no exceptions across the boundary.
+ *
+ * Threading: one context per GPU; a context is not thread-safe; different contexts are
+ * independent.  All calls return after the work they describe is complete (synchronous), like the
+ * reference (SURVEY §8b "Threading").
+ */
+#ifndef KMERDB_B200_H
+#define KMERDB_B200_H
+#include <stddef.h>
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+/* Status codes.  1..5 map 1:1 onto the exception classes the reference raises for this path. */
+enum {
+    KDB_OK = 0,
+    KDB_E_ALPHABET = 1, /* NameError      kmerdb/kmer.py:168-170 via :519 (letter outside ACGTRYSWKMBDHVN)  */
+    KDB_E_IUPAC = 2,    /* KeyError       kmerdb/kmer.py:309 (RYSWKMBDHV reaches the 2-bit encoder)          */
+    KDB_E_SHORT = 3,    /* AttributeError kmerdb/kmer.py:461-463 (record shorter than k)                    */
+    KDB_E_FORMAT = 4,   /* ValueError     Bio.SeqIO grammar violation (kmerdb/parse.py:70-72)               */
+    KDB_E_EMPTY = 5,    /* ValueError     kmerdb/parse.py:144 max([]) on a file with no records             */
+    KDB_E_ARG = 6,      /* TypeError/ValueError: bad argument                                               */
+    KDB_E_LAYOUT = 7,   /* input uses a text layout the device tokeniser does not take natively (lone CR,
+                           multi-line FASTQ, control/non-ASCII bytes ...): the host re-tokenises the file into
+                           the plain layout and feeds it again — counting always happens on the GPU.        */
+    KDB_E_CUDA = 8,     /* RuntimeError: CUDA failure, see kdb_last_error                                   */
+    KDB_E_STATE = 9     /* call order violated (e.g. kdb_counts before kdb_finish)                          */
+};
+
+/* Flags for kdb_create. */
+enum {
+    KDB_CANONICAL = 1, /* id = min(fwd, revcomp)  kmerdb/kmer.py:310-317 (reference default)               */
+    KDB_SKIP_N = 2,    /* replace_with_none=True  kmerdb/kmer.py:542-544; absent: 4^n expansion :550-565    */
+    KDB_FASTQ = 4      /* input is FASTQ (kmerdb/util.py:128-134), else FASTA (:120-126)                    */
+};
+
+typedef struct kdb_ctx kdb_ctx;
+
+/* Per-file reductions of kmerdb/parse.py:139-160 plus the legacy mononucleotide counts. */
+typedef struct {
+    uint64_t total_reads;  /* parse.py:153 */
+    uint64_t total_kmers;  /* parse.py:133-136 (N expansions included) */
+    uint64_t unique_kmers; /* parse.py:141 */
+    uint64_t sum_len;      /* sum of record lengths; avg_read_length = int(mean) parse.py:146 */
+    uint64_t min_len;      /* parse.py:145 */
+    uint64_t max_len;      /* parse.py:144 */
+    uint64_t mono[4];      /* A,C,G,T letter counts */
+    uint64_t err_record;   /* 0-based index of the first record that raises (valid when status != 0) */
+    uint64_t n_windows_with_n; /* windows holding at least one N */
+    int32_t status;        /* KDB_OK or the class of the first failing record, in the reference's order */
+    int32_t pad_;
+} kdb_stats_t;
+
+/* Device timing of the passes run so far (CUDA events on the context's stream). */
+typedef struct {
+    float scan_ms;    /* K1: line/record boundary scan (tile summaries + carry scan)        */
+    float count_ms;   /* K2+K3: 2-bit encode, rolling id, histogram, fused reductions        */
+    float fold_ms;    /* u32 -> u64 fold of the count table                                  */
+    float final_ms;   /* record-length check, unique/nullomer reductions                     */
+    float h2d_ms;     /* host -> device staging                                              */
+    float job_ms;     /* kdb_reset/kdb_create (table zeroing) .. end of kdb_finish, one event pair    */
+    uint64_t count_launches; /* number of count-kernel launches                              */
+    uint64_t total_launches; /* all kernel launches issued by this context                   */
+    uint64_t bytes_fed;
+} kdb_timing_t;
+
+/* Replaces the allocation at kmerdb/parse.py:117-121.  k in [1,16].  NULL on failure
+ * (kdb_last_error(NULL) then holds the reason). */
+kdb_ctx* kdb_create(int device, int k, int flags);
+void kdb_destroy(kdb_ctx* ctx);
+const char* kdb_last_error(const kdb_ctx* ctx);
+
+/* Replaces the record loop of kmerdb/parse.py:128-137 (+ kmer.shred kmerdb/kmer.py:489-577).
+ * `bytes` is the uncompressed file text, or a fragment of it that starts at a record boundary
+ * (start of a '>' / '@' title line) and ends at one; fragments are fed in file order.
+ * kdb_feed_host copies from host memory (pinned or pageable); kdb_feed_device takes a pointer
+ * already in this device's HBM (read-only, no copy is made). */
+int kdb_feed_host(kdb_ctx* ctx, const uint8_t* bytes, size_t n);
+int kdb_feed_device(kdb_ctx* ctx, const uint8_t* dev_bytes, size_t n);
+
+/* Replaces kmerdb/parse.py:139-146: folds partial tables, computes the reductions.  After this
+ * call kdb_stats/kdb_counts/kdb_nullomers are valid.  Returns stats.status. */
+int kdb_finish(kdb_ctx* ctx);
+int kdb_stats(kdb_ctx* ctx, kdb_stats_t* out);
+/* out: host uint64[4^k]  (the `counts` array returned at kmerdb/parse.py:163) */
+int kdb_counts(kdb_ctx* ctx, uint64_t* out);
+/* ascending ids with zero count (parse.py:139-140).  *n receives the total; at most cap are written. */
+int kdb_nullomers(kdb_ctx* ctx, uint64_t* out_ids, size_t cap, size_t* n);
+
+/* Multi-GPU: the device pointer of the uint64[4^k] partial table and of the
+ * additive scalar pack, for the caller's collective (torch.distributed / NCCL sum-reduce), and
+ * a call that recomputes the non-additive reductions (unique, nullomers) after the reduce. */
+int kdb_device_table(kdb_ctx* ctx, void** dev_counts_u64, size_t* n_bins);
+int kdb_export_partials(kdb_ctx* ctx, uint64_t* out16); /* [reads,kmers,sum_len,mono0..3,nwin_n,min,max,err_key,...] */
+int kdb_import_partials(kdb_ctx* ctx, const uint64_t* in16);
+int kdb_refinalize(kdb_ctx* ctx);
+
+/* Start a new file on the same context (tables zeroed, allocations kept). */
+int kdb_reset(kdb_ctx* ctx);
+int kdb_timing(kdb_ctx* ctx, kdb_timing_t* out);
+
+/* Batched scalar helpers (kmerdb/kmer.py:234-317 kmer_to_id, :320-363 id_to_kmer) on the GPU:
+ * n k-mers of k letters each, packed back to back.  ids[i] = id, or UINT64_MAX for a k-mer
+ * holding N (None), UINT64_MAX-1 for other non-ACGT letters (KeyError). */
+int kdb_kmer_to_id_batch(int device, const char* kmers, size_t n, int k, int canonical, uint64_t* ids);
+
+/* Synthetic benchmark input: n_reads records of read_len i.i.d. uniform ACGT letters,
+ * FASTA framing ">%09d\n" + letters + "\n" (or FASTQ framing), written straight into HBM.
+ * read index = first_read + i; counter-based generator, reproducible on the host
+ * (kdb_synth_host writes the same bytes into host memory). */
+size_t kdb_synth_record_bytes(int read_len, int fastq);
+int kdb_synth_device(int device, uint8_t* dev_out, uint64_t first_read, uint64_t n_reads, int read_len, int fastq, uint64_t seed);
+int kdb_synth_host(uint8_t* out, uint64_t first_read, uint64_t n_reads, int read_len, int fastq, uint64_t seed);
+
+/* Microbenchmarks backing the roofline discussion: random red.global.add.u32 into a
+ * table of `table_bytes`, and random shared-memory atomics.  Return updates per second. */
+int kdb_microbench_atomics(int device, size_t table_bytes, uint64_t n_updates, int mode, double* updates_per_s);
+
+/* Raw device memory helpers so callers without a CUDA binding (ctypes) can stage inputs. */
+int kdb_dev_alloc(int device, size_t n, void** out);
+int kdb_dev_free(int device, void* p);
+int kdb_host_alloc_pinned(size_t n, void** out);
+int kdb_host_free_pinned(void* p);
+int kdb_memcpy_h2d(int device, void* dst, const void* src, size_t n);
+int kdb_memcpy_d2h(int device, void* dst, const void* src, size_t n);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

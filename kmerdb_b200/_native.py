@@ -1,0 +1,272 @@
+"""ctypes binding of libkmerdb_b200.so (include/kmerdb_b200.h).
+
+There is no CPU fallback: if the shared library is missing or no CUDA device can be used, the
+calls raise.  Build with `python -m kmerdb_b200.build` (or `__graft_entry__.build()`)."""
+import ctypes
+import os
+
+import numpy as np
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+SO_PATH = os.path.join(_HERE, "libkmerdb_b200.so")
+
+KDB_OK, KDB_E_ALPHABET, KDB_E_IUPAC, KDB_E_SHORT, KDB_E_FORMAT, KDB_E_EMPTY, KDB_E_ARG, KDB_E_LAYOUT, KDB_E_CUDA, KDB_E_STATE = range(10)
+KDB_CANONICAL, KDB_SKIP_N, KDB_FASTQ = 1, 2, 4
+
+EXPORTS = [
+    "kdb_create", "kdb_destroy", "kdb_last_error", "kdb_feed_host", "kdb_feed_device", "kdb_finish", "kdb_stats",
+    "kdb_counts", "kdb_nullomers", "kdb_device_table", "kdb_export_partials", "kdb_import_partials", "kdb_refinalize",
+    "kdb_reset", "kdb_timing", "kdb_kmer_to_id_batch", "kdb_synth_record_bytes", "kdb_synth_device",
+    "kdb_synth_host", "kdb_microbench_atomics", "kdb_dev_alloc", "kdb_dev_free", "kdb_host_alloc_pinned",
+    "kdb_host_free_pinned", "kdb_memcpy_h2d", "kdb_memcpy_d2h",
+]
+
+
+class Stats(ctypes.Structure):
+    _fields_ = [("total_reads", ctypes.c_uint64), ("total_kmers", ctypes.c_uint64), ("unique_kmers", ctypes.c_uint64),
+                ("sum_len", ctypes.c_uint64), ("min_len", ctypes.c_uint64), ("max_len", ctypes.c_uint64),
+                ("mono", ctypes.c_uint64 * 4), ("err_record", ctypes.c_uint64), ("n_windows_with_n", ctypes.c_uint64),
+                ("status", ctypes.c_int32), ("pad_", ctypes.c_int32)]
+
+
+class Timing(ctypes.Structure):
+    _fields_ = [("scan_ms", ctypes.c_float), ("count_ms", ctypes.c_float), ("fold_ms", ctypes.c_float),
+                ("final_ms", ctypes.c_float), ("h2d_ms", ctypes.c_float), ("job_ms", ctypes.c_float), ("count_launches", ctypes.c_uint64),
+                ("total_launches", ctypes.c_uint64), ("bytes_fed", ctypes.c_uint64)]
+
+
+class NativeError(RuntimeError):
+    pass
+
+
+_lib = None
+
+
+def lib():
+    """Load the shared library (once).  Raises NativeError when it has not been built."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(SO_PATH):
+        raise NativeError("kmerdb_b200: %s is missing — the CUDA extension was not built (python -m kmerdb_b200.build); "
+                          "there is no CPU fallback" % SO_PATH)
+    L = ctypes.CDLL(SO_PATH)
+    vp, sz, u64, ci = ctypes.c_void_p, ctypes.c_size_t, ctypes.c_uint64, ctypes.c_int
+    L.kdb_create.restype = vp
+    L.kdb_create.argtypes = [ci, ci, ci]
+    L.kdb_destroy.restype = None
+    L.kdb_destroy.argtypes = [vp]
+    L.kdb_last_error.restype = ctypes.c_char_p
+    L.kdb_last_error.argtypes = [vp]
+    for name, args in [
+        ("kdb_feed_host", [vp, vp, sz]), ("kdb_feed_device", [vp, vp, sz]), ("kdb_finish", [vp]),
+        ("kdb_stats", [vp, ctypes.POINTER(Stats)]), ("kdb_counts", [vp, vp]),
+        ("kdb_nullomers", [vp, vp, sz, ctypes.POINTER(sz)]),
+        ("kdb_device_table", [vp, ctypes.POINTER(vp), ctypes.POINTER(sz)]),
+        ("kdb_export_partials", [vp, vp]), ("kdb_import_partials", [vp, vp]), ("kdb_refinalize", [vp]),
+        ("kdb_reset", [vp]), ("kdb_timing", [vp, ctypes.POINTER(Timing)]),
+        ("kdb_kmer_to_id_batch", [ci, ctypes.c_char_p, sz, ci, ci, vp]),
+        ("kdb_synth_device", [ci, vp, u64, u64, ci, ci, u64]), ("kdb_synth_host", [vp, u64, u64, ci, ci, u64]),
+        ("kdb_microbench_atomics", [ci, sz, u64, ci, ctypes.POINTER(ctypes.c_double)]),
+        ("kdb_dev_alloc", [ci, sz, ctypes.POINTER(vp)]), ("kdb_dev_free", [ci, vp]),
+        ("kdb_host_alloc_pinned", [sz, ctypes.POINTER(vp)]), ("kdb_host_free_pinned", [vp]),
+        ("kdb_memcpy_h2d", [ci, vp, vp, sz]), ("kdb_memcpy_d2h", [ci, vp, vp, sz]),
+    ]:
+        fn = getattr(L, name)
+        fn.restype = ci
+        fn.argtypes = args
+    L.kdb_synth_record_bytes.restype = sz
+    L.kdb_synth_record_bytes.argtypes = [ci, ci]
+    _lib = L
+    return L
+
+
+def _err(ctx=None):
+    msg = lib().kdb_last_error(ctx)
+    return msg.decode() if msg else ""
+
+
+class DeviceBuffer:
+    """A raw allocation in one GPU's HBM (for device-resident feeds)."""
+
+    def __init__(self, nbytes, device=0):
+        self.device, self.nbytes = device, int(nbytes)
+        p = ctypes.c_void_p()
+        rc = lib().kdb_dev_alloc(device, self.nbytes, ctypes.byref(p))
+        if rc:
+            raise NativeError("kdb_dev_alloc(%d bytes): %s" % (self.nbytes, _err()))
+        self.ptr = p.value
+
+    def upload(self, arr, offset=0):
+        a = np.ascontiguousarray(arr, dtype=np.uint8)
+        if lib().kdb_memcpy_h2d(self.device, self.ptr + offset, a.ctypes.data, a.size):
+            raise NativeError("kdb_memcpy_h2d: " + _err())
+
+    def download(self, nbytes=None, offset=0):
+        n = self.nbytes - offset if nbytes is None else nbytes
+        out = np.empty(n, dtype=np.uint8)
+        if lib().kdb_memcpy_d2h(self.device, out.ctypes.data, self.ptr + offset, n):
+            raise NativeError("kdb_memcpy_d2h: " + _err())
+        return out
+
+    def free(self):
+        if self.ptr:
+            lib().kdb_dev_free(self.device, self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class PinnedBuffer:
+    """Page-locked host memory exposed as a numpy uint8 array (`.array`)."""
+
+    def __init__(self, nbytes):
+        p = ctypes.c_void_p()
+        if lib().kdb_host_alloc_pinned(int(nbytes), ctypes.byref(p)):
+            raise NativeError("kdb_host_alloc_pinned: " + _err())
+        self.ptr, self.nbytes = p.value, int(nbytes)
+        self.array = np.ctypeslib.as_array((ctypes.c_uint8 * self.nbytes).from_address(self.ptr))
+
+    def free(self):
+        if self.ptr:
+            self.array = None
+            lib().kdb_host_free_pinned(self.ptr)
+            self.ptr = None
+
+    def __del__(self):
+        try:
+            self.free()
+        except Exception:
+            pass
+
+
+class Profiler:
+    """One device context (kdb_ctx): feed text fragments, finish, read counts and reductions."""
+
+    def __init__(self, k, canonical=True, skip_n=True, fastq=False, device=0):
+        flags = (KDB_CANONICAL if canonical else 0) | (KDB_SKIP_N if skip_n else 0) | (KDB_FASTQ if fastq else 0)
+        self.k, self.device = int(k), device
+        self._ctx = lib().kdb_create(device, self.k, flags)
+        if not self._ctx:
+            raise NativeError("kdb_create(device=%d, k=%d): %s — a CUDA device is required, there is no CPU fallback" % (device, k, _err()))
+
+    def _check(self, rc, what):
+        if rc in (KDB_E_CUDA, KDB_E_ARG, KDB_E_STATE):
+            raise NativeError("%s failed (%d): %s" % (what, rc, _err(self._ctx)))
+        return rc
+
+    def feed(self, data):
+        """data: bytes / bytearray / memoryview / numpy uint8 (host memory)."""
+        a = data if isinstance(data, np.ndarray) else np.frombuffer(data, dtype=np.uint8)
+        a = np.ascontiguousarray(a, dtype=np.uint8)
+        if a.size:
+            self._check(lib().kdb_feed_host(self._ctx, a.ctypes.data, a.size), "kdb_feed_host")
+
+    def feed_device(self, ptr, nbytes):
+        self._check(lib().kdb_feed_device(self._ctx, ptr, int(nbytes)), "kdb_feed_device")
+
+    def finish(self):
+        """Returns the status code (0, or the reference exception class code of the first failing record)."""
+        return self._check(lib().kdb_finish(self._ctx), "kdb_finish")
+
+    def refinalize(self):
+        return self._check(lib().kdb_refinalize(self._ctx), "kdb_refinalize")
+
+    def reset(self):
+        self._check(lib().kdb_reset(self._ctx), "kdb_reset")
+
+    def stats(self):
+        st = Stats()
+        self._check(lib().kdb_stats(self._ctx, ctypes.byref(st)), "kdb_stats")
+        d = {f: int(getattr(st, f)) for f, _ in Stats._fields_ if f not in ("mono", "pad_")}
+        d["mono"] = [int(x) for x in st.mono]
+        return d
+
+    def timing(self):
+        t = Timing()
+        self._check(lib().kdb_timing(self._ctx, ctypes.byref(t)), "kdb_timing")
+        return {f: (float(getattr(t, f)) if f.endswith("_ms") else int(getattr(t, f))) for f, _ in Timing._fields_}
+
+    def counts(self, out=None):
+        """uint64[4^k] histogram; `out` may be a caller-owned (e.g. pinned) uint64 array."""
+        if out is None:
+            out = np.empty(4 ** self.k, dtype=np.uint64)
+        assert out.dtype == np.uint64 and out.size == 4 ** self.k and out.flags.c_contiguous
+        self._check(lib().kdb_counts(self._ctx, out.ctypes.data), "kdb_counts")
+        return out
+
+    def nullomers(self):
+        n = ctypes.c_size_t()
+        self._check(lib().kdb_nullomers(self._ctx, None, 0, ctypes.byref(n)), "kdb_nullomers")
+        out = np.empty(n.value, dtype=np.uint64)
+        if n.value:
+            self._check(lib().kdb_nullomers(self._ctx, out.ctypes.data, n.value, ctypes.byref(n)), "kdb_nullomers")
+        return out
+
+    def device_table(self):
+        p, n = ctypes.c_void_p(), ctypes.c_size_t()
+        self._check(lib().kdb_device_table(self._ctx, ctypes.byref(p), ctypes.byref(n)), "kdb_device_table")
+        return p.value, n.value
+
+    def export_partials(self):
+        out = np.zeros(16, dtype=np.uint64)
+        self._check(lib().kdb_export_partials(self._ctx, out.ctypes.data), "kdb_export_partials")
+        return out
+
+    def import_partials(self, arr):
+        a = np.ascontiguousarray(arr, dtype=np.uint64)
+        self._check(lib().kdb_import_partials(self._ctx, a.ctypes.data), "kdb_import_partials")
+
+    def close(self):
+        if getattr(self, "_ctx", None):
+            lib().kdb_destroy(self._ctx)
+            self._ctx = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *exc):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass
+
+
+def synth_host(n_reads, read_len=150, fastq=False, seed=20261104, first_read=0):
+    rb = lib().kdb_synth_record_bytes(read_len, int(fastq))
+    out = np.empty(n_reads * rb, dtype=np.uint8)
+    if lib().kdb_synth_host(out.ctypes.data, first_read, n_reads, read_len, int(fastq), seed):
+        raise NativeError("kdb_synth_host failed")
+    return out
+
+
+def synth_device(buf, n_reads, read_len=150, fastq=False, seed=20261104, first_read=0, offset=0):
+    if lib().kdb_synth_device(buf.device, buf.ptr + offset, first_read, n_reads, read_len, int(fastq), seed):
+        raise NativeError("kdb_synth_device: " + _err())
+
+
+def synth_record_bytes(read_len=150, fastq=False):
+    return int(lib().kdb_synth_record_bytes(read_len, int(fastq)))
+
+
+def microbench_atomics(table_bytes, n_updates, mode=0, device=0):
+    v = ctypes.c_double()
+    if lib().kdb_microbench_atomics(device, table_bytes, n_updates, mode, ctypes.byref(v)):
+        raise NativeError("kdb_microbench_atomics: " + _err())
+    return v.value
+
+
+def kmer_to_id_batch(kmers, k, canonical=True, device=0):
+    """kmers: bytes of n*k letters.  Returns uint64 ids (2^64-1 = None, 2^64-2 = KeyError letters)."""
+    n = len(kmers) // k
+    out = np.empty(n, dtype=np.uint64)
+    if lib().kdb_kmer_to_id_batch(device, kmers, n, k, int(canonical), out.ctypes.data):
+        raise NativeError("kdb_kmer_to_id_batch: " + _err())
+    return out

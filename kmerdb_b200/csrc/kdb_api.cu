@@ -1,0 +1,647 @@
+// kmerdb_b200 — context and C-ABI (include/kmerdb_b200.h) over the sm_100a kernels.
+// One translation unit: every kernel header is included here.
+#include "../../include/kmerdb_b200.h"
+
+#include <algorithm>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <string>
+#include <vector>
+
+#include "kdb_common.cuh"
+#include "kdb_scan.cuh"
+#include "kdb_count.cuh"
+#include "kdb_final.cuh"
+#include "kdb_synth.cuh"
+
+using namespace kdb;
+
+static thread_local std::string g_last_error;
+
+struct kdb_ctx {
+    int device = 0, k = 0, flags = 0;
+    bool fastq = false, canonical = false, skip_n = false, smem_hist = false;
+    unsigned long long nbins = 0;
+    cudaStream_t s_compute = nullptr, s_copy = nullptr;
+    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev_job0 = nullptr, ev_job1 = nullptr;
+    std::vector<cudaEvent_t> ev_copy;
+    unsigned int* tab32 = nullptr;
+    unsigned long long* tab64 = nullptr;
+    Accum* acc = nullptr;
+    ScanCarry* carry = nullptr;
+    unsigned long long* carry_len = nullptr;   // 2 x u64: partial lengths of the last record seen
+    TileSummary* tile_sum = nullptr;
+    TileState* tile_state = nullptr;
+    size_t tile_cap = 0;
+    unsigned long long* rec_len = nullptr;
+    size_t rec_cap = 0;
+    uint8_t* feed_buf = nullptr;
+    size_t feed_cap = 0;
+    // host mirrors
+    ScanCarry h_carry{};
+    bool have_carry = false;
+    unsigned long long carry_rec_id = 0, fq_rec_base = 0;
+    unsigned long long bytes_since_fold = 0;
+    bool job_started = false, finished = false, host_layout = false;
+    int count_grid = 0;
+    kdb_stats_t stats{};
+    kdb_timing_t timing{};
+    std::string err;
+};
+
+#define CK(call)                                                                                   \
+    do {                                                                                           \
+        cudaError_t e_ = (call);                                                                   \
+        if (e_ != cudaSuccess) {                                                                   \
+            char b_[512];                                                                          \
+            snprintf(b_, sizeof b_, "%s failed at %s:%d: %s", #call, __FILE__, __LINE__, cudaGetErrorString(e_)); \
+            if (ctx) ctx->err = b_;                                                                \
+            g_last_error = b_;                                                                     \
+            return KDB_E_CUDA;                                                                     \
+        }                                                                                          \
+    } while (0)
+
+static void build_class_lut(uint8_t* lut) {
+    for (int c = 0; c < 256; c++) {
+        uint8_t v;
+        if (c >= 0x80 || c == 0x7f) v = C_WEIRD;
+        else if (c == '\n') v = C_LF;
+        else if (c == '\r') v = C_CR;
+        else if (c == ' ') v = C_SPACE;
+        else if (c < 0x20) v = C_WEIRD;
+        else v = C_ILLEGAL;
+        lut[c] = v;
+    }
+    lut['A'] = C_A; lut['C'] = C_C; lut['G'] = C_G; lut['T'] = C_T; lut['N'] = C_N;
+    for (const char* p = "RYSWKMBDHV"; *p; p++) lut[(unsigned char)*p] = C_IUPAC;   // kmerdb/kmer.py:66-80
+}
+
+static int set_device(kdb_ctx* ctx, int device) {
+    CK(cudaSetDevice(device));
+    return KDB_OK;
+}
+
+template <typename K>
+static int occupancy_grid(K kernel, size_t dyn_smem, int* grid) {
+    kdb_ctx* ctx = nullptr;
+    int per_sm = 0, sms = 0, dev = 0;
+    CK(cudaGetDevice(&dev));
+    CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, dyn_smem));
+    *grid = std::max(1, per_sm) * sms;   // persistent CTAs: a whole number of CTAs per SM
+    return KDB_OK;
+}
+
+extern "C" const char* kdb_last_error(const kdb_ctx* ctx) { return ctx ? ctx->err.c_str() : g_last_error.c_str(); }
+
+extern "C" void kdb_destroy(kdb_ctx* ctx) {
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaFree(ctx->tab32); cudaFree(ctx->tab64); cudaFree(ctx->acc); cudaFree(ctx->carry); cudaFree(ctx->carry_len);
+    cudaFree(ctx->tile_sum); /* tile_state lives inside the tile_sum allocation */ cudaFree(ctx->rec_len); cudaFree(ctx->feed_buf);
+    for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
+    for (auto& e : ctx->ev_copy) cudaEventDestroy(e);
+    if (ctx->ev_job0) cudaEventDestroy(ctx->ev_job0);
+    if (ctx->ev_job1) cudaEventDestroy(ctx->ev_job1);
+    if (ctx->s_compute) cudaStreamDestroy(ctx->s_compute);
+    if (ctx->s_copy) cudaStreamDestroy(ctx->s_copy);
+    delete ctx;
+}
+
+static int reset_state(kdb_ctx* ctx) {
+    CK(cudaEventRecord(ctx->ev_job0, ctx->s_compute));   // a job starts with zeroing its tables
+    CK(cudaMemsetAsync(ctx->tab32, 0, ctx->nbins * sizeof(unsigned int), ctx->s_compute));
+    CK(cudaMemsetAsync(ctx->tab64, 0, ctx->nbins * sizeof(unsigned long long), ctx->s_compute));
+    Accum a{};
+    a.min_len = ~0ull; a.err_key = ~0ull;
+    CK(cudaMemcpyAsync(ctx->acc, &a, sizeof a, cudaMemcpyHostToDevice, ctx->s_compute));
+    CK(cudaMemsetAsync(ctx->carry, 0, sizeof(ScanCarry), ctx->s_compute));
+    CK(cudaMemsetAsync(ctx->carry_len, 0, 2 * sizeof(unsigned long long), ctx->s_compute));
+    CK(cudaStreamSynchronize(ctx->s_compute));
+    ctx->h_carry = ScanCarry{};
+    ctx->have_carry = false; ctx->carry_rec_id = 0; ctx->fq_rec_base = 0; ctx->bytes_since_fold = 0;
+    ctx->job_started = true; ctx->finished = false; ctx->host_layout = false;
+    ctx->stats = kdb_stats_t{}; ctx->timing = kdb_timing_t{};
+    return KDB_OK;
+}
+
+extern "C" int kdb_reset(kdb_ctx* ctx) {
+    if (!ctx) return KDB_E_ARG;
+    if (int rc = set_device(ctx, ctx->device)) return rc;
+    return reset_state(ctx);
+}
+
+extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
+    if (k < 1 || k > 16) { g_last_error = "k must be in [1,16] for the dense 4^k device table"; return nullptr; }
+    kdb_ctx* ctx = new kdb_ctx();
+    ctx->device = device; ctx->k = k; ctx->flags = flags;
+    ctx->fastq = flags & KDB_FASTQ; ctx->canonical = flags & KDB_CANONICAL; ctx->skip_n = flags & KDB_SKIP_N;
+    ctx->smem_hist = k <= 7;
+    ctx->nbins = 1ull << (2 * k);
+    auto fail = [&](const char* what, cudaError_t e) -> kdb_ctx* {
+        g_last_error = std::string(what) + ": " + cudaGetErrorString(e);
+        kdb_destroy(ctx);
+        return nullptr;
+    };
+    cudaError_t e;
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail("cudaSetDevice", e);
+    uint8_t lut[256];
+    build_class_lut(lut);
+    if ((e = cudaMemcpyToSymbol(c_class_lut, lut, 256)) != cudaSuccess) return fail("cudaMemcpyToSymbol", e);
+    if ((e = cudaStreamCreateWithFlags(&ctx->s_compute, cudaStreamNonBlocking)) != cudaSuccess) return fail("stream", e);
+    if ((e = cudaStreamCreateWithFlags(&ctx->s_copy, cudaStreamNonBlocking)) != cudaSuccess) return fail("stream", e);
+    for (auto& ev : ctx->ev) if ((e = cudaEventCreate(&ev)) != cudaSuccess) return fail("event", e);
+    if ((e = cudaEventCreate(&ctx->ev_job0)) != cudaSuccess) return fail("event", e);
+    if ((e = cudaEventCreate(&ctx->ev_job1)) != cudaSuccess) return fail("event", e);
+    if ((e = cudaMalloc(&ctx->tab32, ctx->nbins * sizeof(unsigned int))) != cudaSuccess) return fail("cudaMalloc tab32", e);
+    if ((e = cudaMalloc(&ctx->tab64, ctx->nbins * sizeof(unsigned long long))) != cudaSuccess) return fail("cudaMalloc tab64", e);
+    if ((e = cudaMalloc(&ctx->acc, sizeof(Accum))) != cudaSuccess) return fail("cudaMalloc acc", e);
+    if ((e = cudaMalloc(&ctx->carry, sizeof(ScanCarry))) != cudaSuccess) return fail("cudaMalloc carry", e);
+    if ((e = cudaMalloc(&ctx->carry_len, 2 * sizeof(unsigned long long))) != cudaSuccess) return fail("cudaMalloc carry_len", e);
+    // launch geometry of the count kernel: persistent CTAs, a whole number per SM
+    int rc;
+    const size_t dyn = ctx->smem_hist ? ctx->nbins * sizeof(unsigned int) : 0;
+    if (ctx->smem_hist) {
+        auto kern = ctx->fastq ? k2_count<true, true> : k2_count<false, true>;
+        if ((e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)) != cudaSuccess) return fail("smem attr", e);
+        rc = occupancy_grid(kern, dyn, &ctx->count_grid);
+    } else {
+        auto kern = ctx->fastq ? k2_count<true, false> : k2_count<false, false>;
+        rc = occupancy_grid(kern, 0, &ctx->count_grid);
+    }
+    if (rc) { kdb_destroy(ctx); return nullptr; }
+    if (reset_state(ctx)) { g_last_error = ctx->err; kdb_destroy(ctx); return nullptr; }
+    if ((e = cudaGetLastError()) != cudaSuccess) return fail("kdb_create", e);
+    return ctx;
+}
+
+// ---- one pass: K1 scan -> (size rec_len) -> K2+K3 count -> K4 record checks ------------------------
+static int ensure(kdb_ctx* ctx, void** p, size_t* cap, size_t need, size_t elem) {
+    if (need <= *cap) return KDB_OK;
+    if (*p) CK(cudaFree(*p));
+    *p = nullptr; *cap = 0;
+    const size_t n = need + need / 4 + 64;
+    CK(cudaMalloc(p, n * elem));
+    *cap = n;
+    return KDB_OK;
+}
+
+static int fold_now(kdb_ctx* ctx) {
+    if (ctx->bytes_since_fold == 0) return KDB_OK;
+    CK(cudaEventRecord(ctx->ev[4], ctx->s_compute));
+    const unsigned long long quads = (ctx->nbins + 3) / 4;
+    const int grid = (int)std::min<unsigned long long>((quads + 255) / 256, 148ull * 16);
+    k3_fold<<<grid, 256, 0, ctx->s_compute>>>(ctx->tab32, ctx->tab64, ctx->nbins);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ctx->ev[5], ctx->s_compute));
+    CK(cudaEventSynchronize(ctx->ev[5]));
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[4], ctx->ev[5]));
+    ctx->timing.fold_ms += ms;
+    ctx->timing.total_launches++;
+    ctx->bytes_since_fold = 0;
+    return KDB_OK;
+}
+
+// The last record seen so far is complete: run the record check on it alone.
+static int close_carry_record(kdb_ctx* ctx) {
+    if (!ctx->have_carry) return KDB_OK;
+    if (ctx->fastq) k4_check_records<true><<<1, 32, 0, ctx->s_compute>>>(ctx->carry_len, 1, ctx->carry_rec_id, ctx->k, ctx->acc);
+    else k4_check_records<false><<<1, 32, 0, ctx->s_compute>>>(ctx->carry_len, 1, ctx->carry_rec_id, ctx->k, ctx->acc);
+    CK(cudaGetLastError());
+    ctx->timing.total_launches++;
+    CK(cudaMemsetAsync(ctx->carry_len, 0, 2 * sizeof(unsigned long long), ctx->s_compute));
+    ctx->have_carry = false;
+    return KDB_OK;
+}
+
+static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, unsigned long long hi, unsigned long long n) {
+    const unsigned int n_tiles = (unsigned int)((hi - lo + kTile - 1) / kTile);
+    if (int rc = ensure(ctx, (void**)&ctx->tile_sum, &ctx->tile_cap, n_tiles, sizeof(TileSummary) + sizeof(TileState))) return rc;
+    ctx->tile_state = reinterpret_cast<TileState*>(ctx->tile_sum + ctx->tile_cap);
+    // the u32 table must not wrap: every text byte adds at most 2 to one bin (DESIGN.md "fold rule")
+    if (ctx->bytes_since_fold + (hi - lo) > 0x7fffffffull) if (int rc = fold_now(ctx)) return rc;
+
+    const ScanCarry before = ctx->h_carry;
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ctx->ev[0], ctx->s_compute));
+    k1_tile_summary<<<n_tiles, kThreads, 0, ctx->s_compute>>>(text, lo, hi, ctx->tile_sum);
+    CK(cudaGetLastError());
+    k1_carry_scan<<<1, 1024, 0, ctx->s_compute>>>(ctx->tile_sum, ctx->tile_state, n_tiles, ctx->carry);
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ctx->ev[1], ctx->s_compute));
+    CK(cudaMemcpyAsync(&ctx->h_carry, ctx->carry, sizeof(ScanCarry), cudaMemcpyDeviceToHost, ctx->s_compute));
+    CK(cudaStreamSynchronize(ctx->s_compute));
+    const ScanCarry after = ctx->h_carry;
+
+    // record ids touched by this pass: [rec_first, rec_last]
+    unsigned long long rec_first, rec_last;
+    bool any_record;
+    if (ctx->fastq) {
+        rec_first = ctx->fq_rec_base + (before.ls_total ? (before.ls_total - 1) / 4 : 0);
+        rec_last = ctx->fq_rec_base + (after.ls_total ? (after.ls_total - 1) / 4 : 0);
+        any_record = after.ls_total != 0;
+    } else {
+        rec_first = before.hdr_total ? before.hdr_total - 1 : 0;
+        rec_last = after.hdr_total ? after.hdr_total - 1 : 0;
+        any_record = after.hdr_total != 0;
+    }
+    if (ctx->have_carry && ctx->carry_rec_id != rec_first) if (int rc = close_carry_record(ctx)) return rc;
+    const size_t per = ctx->fastq ? 2 : 1;
+    const size_t n_entries = (size_t)(rec_last - rec_first + 1);
+    if (int rc = ensure(ctx, (void**)&ctx->rec_len, &ctx->rec_cap, n_entries * per, sizeof(unsigned long long))) return rc;
+    CK(cudaMemsetAsync(ctx->rec_len, 0, n_entries * per * sizeof(unsigned long long), ctx->s_compute));
+    if (ctx->have_carry)
+        CK(cudaMemcpyAsync(ctx->rec_len, ctx->carry_len, per * sizeof(unsigned long long), cudaMemcpyDeviceToDevice, ctx->s_compute));
+
+    CountParams P{};
+    P.text = text; P.lo = lo; P.hi = hi; P.n = n; P.tiles = ctx->tile_state; P.n_tiles = n_tiles; P.k = ctx->k;
+    P.canonical = ctx->canonical; P.skip_n = ctx->skip_n; P.tab32 = ctx->tab32; P.rec_len = ctx->rec_len;
+    P.rec_first = rec_first; P.hdr_file_base = ctx->fq_rec_base; P.acc = ctx->acc;
+    const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->count_grid);
+    const size_t dyn = ctx->smem_hist ? ctx->nbins * sizeof(unsigned int) : 0;
+    CK(cudaEventRecord(ctx->ev[2], ctx->s_compute));
+    if (ctx->fastq) {
+        if (ctx->smem_hist) k2_count<true, true><<<grid, kThreads, dyn, ctx->s_compute>>>(P);
+        else k2_count<true, false><<<grid, kThreads, 0, ctx->s_compute>>>(P);
+    } else {
+        if (ctx->smem_hist) k2_count<false, true><<<grid, kThreads, dyn, ctx->s_compute>>>(P);
+        else k2_count<false, false><<<grid, kThreads, 0, ctx->s_compute>>>(P);
+    }
+    CK(cudaGetLastError());
+    CK(cudaEventRecord(ctx->ev[3], ctx->s_compute));
+    const unsigned long long n_complete = n_entries - 1;
+    if (n_complete) {
+        const int g4 = (int)std::min<unsigned long long>((n_complete + 255) / 256, 148ull * 8);
+        if (ctx->fastq) k4_check_records<true><<<g4, 256, 0, ctx->s_compute>>>(ctx->rec_len, n_complete, rec_first, ctx->k, ctx->acc);
+        else k4_check_records<false><<<g4, 256, 0, ctx->s_compute>>>(ctx->rec_len, n_complete, rec_first, ctx->k, ctx->acc);
+        CK(cudaGetLastError());
+        ctx->timing.total_launches++;
+    }
+    if (any_record) {
+        CK(cudaMemcpyAsync(ctx->carry_len, ctx->rec_len + (n_entries - 1) * per, per * sizeof(unsigned long long), cudaMemcpyDeviceToDevice, ctx->s_compute));
+        ctx->have_carry = true; ctx->carry_rec_id = rec_last;
+    }
+    CK(cudaEventRecord(ctx->ev[4], ctx->s_compute));
+    CK(cudaEventSynchronize(ctx->ev[4]));
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1])); ctx->timing.scan_ms += ms;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3])); ctx->timing.count_ms += ms;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[3], ctx->ev[4])); ctx->timing.final_ms += ms;
+    ctx->timing.count_launches++;
+    ctx->timing.total_launches += 3;
+    ctx->bytes_since_fold += hi - lo;
+    return KDB_OK;
+}
+
+static int begin_feed(kdb_ctx* ctx) {
+    if (ctx->finished) { ctx->err = "kdb_feed after kdb_finish (call kdb_reset first)"; return KDB_E_STATE; }
+    if (!ctx->job_started) { CK(cudaEventRecord(ctx->ev_job0, ctx->s_compute)); ctx->job_started = true; }
+    // line indices restart with every fragment (fragments begin at a record boundary)
+    ctx->h_carry.ls_total = 0; ctx->h_carry.last = 0;
+    CK(cudaMemcpyAsync(ctx->carry, &ctx->h_carry, sizeof(ScanCarry), cudaMemcpyHostToDevice, ctx->s_compute));
+    return KDB_OK;
+}
+
+static int end_feed(kdb_ctx* ctx, size_t n) {
+    if (ctx->fastq) {
+        if (ctx->h_carry.ls_total % 4 != 0) ctx->host_layout = true;   // truncated / blank-line tail: host tokeniser decides
+        ctx->fq_rec_base += ctx->h_carry.ls_total / 4;
+    }
+    ctx->timing.bytes_fed += n;
+    return KDB_OK;
+}
+
+extern "C" int kdb_feed_device(kdb_ctx* ctx, const uint8_t* dev_bytes, size_t n) {
+    if (!ctx) return KDB_E_ARG;
+    if (int rc = set_device(ctx, ctx->device)) return rc;
+    if (n == 0) return KDB_OK;
+    if (!dev_bytes || ((uintptr_t)dev_bytes & 15)) { ctx->err = "device text must be 16-byte aligned"; return KDB_E_ARG; }
+    if (int rc = begin_feed(ctx)) return rc;
+    const unsigned long long pass = 1ull << 30;
+    for (unsigned long long lo = 0; lo < n; lo += pass)
+        if (int rc = run_pass(ctx, dev_bytes, lo, std::min<unsigned long long>(lo + pass, n), n)) return rc;
+    return end_feed(ctx, n);
+}
+
+extern "C" int kdb_feed_host(kdb_ctx* ctx, const uint8_t* bytes, size_t n) {
+    if (!ctx) return KDB_E_ARG;
+    if (int rc = set_device(ctx, ctx->device)) return rc;
+    if (n == 0) return KDB_OK;
+    if (!bytes) return KDB_E_ARG;
+    if (int rc = ensure(ctx, (void**)&ctx->feed_buf, &ctx->feed_cap, n + 16, 1)) return rc;
+    if (int rc = begin_feed(ctx)) return rc;
+    // stage pass by pass on the copy stream; the compute stream waits for the pass it needs, so the
+    // copy of pass i+1 overlaps the kernels of pass i
+    const unsigned long long pass = 256ull << 20;
+    const size_t n_pass = (size_t)((n + pass - 1) / pass);
+    while (ctx->ev_copy.size() < n_pass + 1) { cudaEvent_t e; CK(cudaEventCreate(&e)); ctx->ev_copy.push_back(e); }
+    CK(cudaEventRecord(ctx->ev_copy[n_pass], ctx->s_copy));
+    for (size_t i = 0; i < n_pass; i++) {
+        const unsigned long long lo = i * pass, hi = std::min<unsigned long long>(lo + pass, n);
+        CK(cudaMemcpyAsync(ctx->feed_buf + lo, bytes + lo, hi - lo, cudaMemcpyHostToDevice, ctx->s_copy));
+        CK(cudaEventRecord(ctx->ev_copy[i], ctx->s_copy));
+    }
+    for (size_t i = 0; i < n_pass; i++) {
+        const unsigned long long lo = i * pass, hi = std::min<unsigned long long>(lo + pass, n);
+        CK(cudaStreamWaitEvent(ctx->s_compute, ctx->ev_copy[i], 0));
+        if (int rc = run_pass(ctx, ctx->feed_buf, lo, hi, n)) return rc;
+    }
+    float ms = 0;
+    CK(cudaEventSynchronize(ctx->ev_copy[n_pass - 1]));
+    CK(cudaEventElapsedTime(&ms, ctx->ev_copy[n_pass], ctx->ev_copy[n_pass - 1]));
+    ctx->timing.h2d_ms += ms;
+    return end_feed(ctx, n);
+}
+
+static int compute_unique(kdb_ctx* ctx) {
+    CK(cudaMemsetAsync(&ctx->acc->unique, 0, sizeof(unsigned long long), ctx->s_compute));
+    const int grid = (int)std::min<unsigned long long>((ctx->nbins + 255) / 256, 148ull * 16);
+    k5_count_nonzero<<<grid, 256, 0, ctx->s_compute>>>(ctx->tab64, ctx->nbins, ctx->acc);
+    CK(cudaGetLastError());
+    ctx->timing.total_launches++;
+    return KDB_OK;
+}
+
+static int fill_stats(kdb_ctx* ctx) {
+    Accum a;
+    CK(cudaMemcpyAsync(&a, ctx->acc, sizeof a, cudaMemcpyDeviceToHost, ctx->s_compute));
+    CK(cudaStreamSynchronize(ctx->s_compute));
+    kdb_stats_t& s = ctx->stats;
+    s = kdb_stats_t{};
+    s.total_reads = ctx->fastq ? ctx->fq_rec_base : ctx->h_carry.hdr_total;
+    s.total_kmers = a.total_kmers; s.unique_kmers = a.unique; s.sum_len = a.sum_len;
+    s.min_len = a.min_len == ~0ull ? 0 : a.min_len; s.max_len = a.max_len;
+    for (int i = 0; i < 4; i++) s.mono[i] = a.mono[i];
+    s.n_windows_with_n = a.n_windows_with_n;
+    if (a.layout_flag || ctx->host_layout) s.status = KDB_E_LAYOUT;
+    else if (a.err_key != ~0ull) {
+        s.err_record = a.err_key >> 2;
+        const unsigned int pr = (unsigned int)(a.err_key & 3);
+        s.status = pr == P_ALPHABET ? KDB_E_ALPHABET : pr == P_SHORT ? KDB_E_SHORT : KDB_E_IUPAC;
+    } else if (s.total_reads == 0) s.status = KDB_E_EMPTY;
+    return KDB_OK;
+}
+
+extern "C" int kdb_finish(kdb_ctx* ctx) {
+    if (!ctx) return KDB_E_ARG;
+    if (int rc = set_device(ctx, ctx->device)) return rc;
+    if (ctx->finished) return ctx->stats.status;
+    if (!ctx->job_started) { CK(cudaEventRecord(ctx->ev_job0, ctx->s_compute)); ctx->job_started = true; }
+    CK(cudaEventRecord(ctx->ev[0], ctx->s_compute));
+    if (int rc = close_carry_record(ctx)) return rc;
+    if (int rc = fold_now(ctx)) return rc;
+    if (int rc = compute_unique(ctx)) return rc;
+    CK(cudaEventRecord(ctx->ev[1], ctx->s_compute));
+    CK(cudaEventRecord(ctx->ev_job1, ctx->s_compute));
+    if (int rc = fill_stats(ctx)) return rc;
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1])); ctx->timing.final_ms += ms;
+    CK(cudaEventElapsedTime(&ms, ctx->ev_job0, ctx->ev_job1)); ctx->timing.job_ms = ms;
+    ctx->finished = true;
+    return ctx->stats.status;
+}
+
+extern "C" int kdb_stats(kdb_ctx* ctx, kdb_stats_t* out) {
+    if (!ctx || !out) return KDB_E_ARG;
+    if (!ctx->finished) { ctx->err = "kdb_stats before kdb_finish"; return KDB_E_STATE; }
+    *out = ctx->stats;
+    return KDB_OK;
+}
+
+extern "C" int kdb_counts(kdb_ctx* ctx, uint64_t* out) {
+    if (!ctx || !out) return KDB_E_ARG;
+    if (!ctx->finished) { ctx->err = "kdb_counts before kdb_finish"; return KDB_E_STATE; }
+    if (int rc = set_device(ctx, ctx->device)) return rc;
+    CK(cudaMemcpyAsync(out, ctx->tab64, ctx->nbins * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->s_compute));
+    CK(cudaStreamSynchronize(ctx->s_compute));
+    return KDB_OK;
+}
+
+extern "C" int kdb_nullomers(kdb_ctx* ctx, uint64_t* out_ids, size_t cap, size_t* n) {
+    if (!ctx || !n) return KDB_E_ARG;
+    if (!ctx->finished) { ctx->err = "kdb_nullomers before kdb_finish"; return KDB_E_STATE; }
+    if (int rc = set_device(ctx, ctx->device)) return rc;
+    const unsigned int blocks = (unsigned int)((ctx->nbins + kNullBlock - 1) / kNullBlock);
+    unsigned int* d_cnt = nullptr; unsigned long long* d_off = nullptr; unsigned long long* d_out = nullptr;
+    CK(cudaMalloc(&d_cnt, blocks * sizeof(unsigned int)));
+    k6_null_count<<<blocks, 256, 0, ctx->s_compute>>>(ctx->tab64, ctx->nbins, d_cnt);
+    std::vector<unsigned int> h_cnt(blocks);
+    CK(cudaMemcpyAsync(h_cnt.data(), d_cnt, blocks * sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->s_compute));
+    CK(cudaStreamSynchronize(ctx->s_compute));
+    std::vector<unsigned long long> h_off(blocks);
+    unsigned long long total = 0;
+    for (unsigned int b = 0; b < blocks; b++) { h_off[b] = total; total += h_cnt[b]; }
+    *n = (size_t)total;
+    ctx->timing.total_launches++;
+    const size_t m = std::min<size_t>(cap, (size_t)total);
+    if (out_ids && m) {
+        CK(cudaMalloc(&d_off, blocks * sizeof(unsigned long long)));
+        CK(cudaMalloc(&d_out, m * sizeof(unsigned long long)));
+        CK(cudaMemcpyAsync(d_off, h_off.data(), blocks * sizeof(unsigned long long), cudaMemcpyHostToDevice, ctx->s_compute));
+        k6_null_write<<<blocks, 256, 0, ctx->s_compute>>>(ctx->tab64, ctx->nbins, d_off, d_out, m);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(out_ids, d_out, m * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->s_compute));
+        CK(cudaStreamSynchronize(ctx->s_compute));
+        ctx->timing.total_launches++;
+    }
+    cudaFree(d_cnt); cudaFree(d_off); cudaFree(d_out);
+    return KDB_OK;
+}
+
+extern "C" int kdb_timing(kdb_ctx* ctx, kdb_timing_t* out) {
+    if (!ctx || !out) return KDB_E_ARG;
+    *out = ctx->timing;
+    return KDB_OK;
+}
+
+// ---- multi-GPU support: expose the partial table and the additive scalars -------------------------
+extern "C" int kdb_device_table(kdb_ctx* ctx, void** dev_counts_u64, size_t* n_bins) {
+    if (!ctx || !dev_counts_u64 || !n_bins) return KDB_E_ARG;
+    if (!ctx->finished) { ctx->err = "kdb_device_table before kdb_finish"; return KDB_E_STATE; }
+    *dev_counts_u64 = ctx->tab64; *n_bins = (size_t)ctx->nbins;
+    return KDB_OK;
+}
+
+// out16: 0 reads, 1 kmers, 2 sum_len, 3..6 mono, 7 windows with N, 8 min_len (~0 = none), 9 max_len,
+//        10 err_key (~0 = none; min-reduce), 11 layout flag (max-reduce), 12..15 reserved
+extern "C" int kdb_export_partials(kdb_ctx* ctx, uint64_t* out16) {
+    if (!ctx || !out16) return KDB_E_ARG;
+    if (!ctx->finished) { ctx->err = "kdb_export_partials before kdb_finish"; return KDB_E_STATE; }
+    if (int rc = set_device(ctx, ctx->device)) return rc;
+    Accum a;
+    CK(cudaMemcpy(&a, ctx->acc, sizeof a, cudaMemcpyDeviceToHost));
+    memset(out16, 0, 16 * sizeof(uint64_t));
+    out16[0] = ctx->stats.total_reads; out16[1] = a.total_kmers; out16[2] = a.sum_len;
+    for (int i = 0; i < 4; i++) out16[3 + i] = a.mono[i];
+    out16[7] = a.n_windows_with_n; out16[8] = a.min_len; out16[9] = a.max_len; out16[10] = a.err_key;
+    out16[11] = (a.layout_flag || ctx->host_layout) ? 1 : 0;
+    return KDB_OK;
+}
+
+extern "C" int kdb_import_partials(kdb_ctx* ctx, const uint64_t* in16) {
+    if (!ctx || !in16) return KDB_E_ARG;
+    if (!ctx->finished) { ctx->err = "kdb_import_partials before kdb_finish"; return KDB_E_STATE; }
+    if (int rc = set_device(ctx, ctx->device)) return rc;
+    Accum a{};
+    a.total_kmers = in16[1]; a.sum_len = in16[2];
+    for (int i = 0; i < 4; i++) a.mono[i] = in16[3 + i];
+    a.n_windows_with_n = in16[7]; a.min_len = in16[8]; a.max_len = in16[9]; a.err_key = in16[10];
+    a.layout_flag = in16[11] ? 1 : 0;
+    CK(cudaMemcpy(ctx->acc, &a, sizeof a, cudaMemcpyHostToDevice));
+    if (ctx->fastq) ctx->fq_rec_base = in16[0]; else ctx->h_carry.hdr_total = in16[0];
+    ctx->host_layout = false;
+    return KDB_OK;
+}
+
+// unique_kmers / nullomers are not additive across GPUs: recompute them from the reduced table.
+extern "C" int kdb_refinalize(kdb_ctx* ctx) {
+    if (!ctx) return KDB_E_ARG;
+    if (!ctx->finished) { ctx->err = "kdb_refinalize before kdb_finish"; return KDB_E_STATE; }
+    if (int rc = set_device(ctx, ctx->device)) return rc;
+    CK(cudaDeviceSynchronize());   // the caller's collective ran on another stream
+    if (int rc = compute_unique(ctx)) return rc;
+    if (int rc = fill_stats(ctx)) return rc;
+    return ctx->stats.status;
+}
+
+// ---- batched kmer_to_id (kmerdb/kmer.py:234-317) ----------------------------------------------------
+__global__ void __launch_bounds__(256) k_kmer_to_id(const char* __restrict__ kmers, size_t n, int k, int canonical, unsigned long long* __restrict__ ids) {
+    const size_t i = (size_t)blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= n) return;
+    const char* s = kmers + i * (size_t)k;
+    unsigned long long fwd = 0, rc = 0;
+    bool has_n = false, bad = false;
+    for (int j = 0; j < k; j++) {
+        const uint8_t cl = c_class_lut[(uint8_t)s[j]];
+        if (cl == C_N) has_n = true;                          // kmer.py:287-289 -> None
+        else if (cl > C_T) bad = true;                        // kmer.py:309 KeyError
+        const unsigned long long code = cl <= C_T ? cl : 0;
+        fwd = (fwd << 2) | code;
+        rc |= (3ull - code) << (2 * j);
+    }
+    unsigned long long id = (canonical && rc < fwd) ? rc : fwd;
+    if (has_n) id = ~0ull; else if (bad) id = ~0ull - 1;
+    ids[i] = id;
+}
+
+extern "C" int kdb_kmer_to_id_batch(int device, const char* kmers, size_t n, int k, int canonical, uint64_t* ids) {
+    kdb_ctx* ctx = nullptr;
+    if (!kmers || !ids || k < 1 || k > 31) return KDB_E_ARG;
+    if (n == 0) return KDB_OK;
+    CK(cudaSetDevice(device));
+    uint8_t lut[256];
+    build_class_lut(lut);
+    CK(cudaMemcpyToSymbol(c_class_lut, lut, 256));
+    char* d_k = nullptr; unsigned long long* d_ids = nullptr;
+    CK(cudaMalloc(&d_k, n * (size_t)k));
+    CK(cudaMalloc(&d_ids, n * sizeof(unsigned long long)));
+    CK(cudaMemcpy(d_k, kmers, n * (size_t)k, cudaMemcpyHostToDevice));
+    k_kmer_to_id<<<(unsigned int)((n + 255) / 256), 256>>>(d_k, n, k, canonical, d_ids);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(ids, d_ids, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
+    cudaFree(d_k); cudaFree(d_ids);
+    return KDB_OK;
+}
+
+// ---- synthetic input ---------------------------------------------------------------------------------
+extern "C" size_t kdb_synth_record_bytes(int read_len, int fastq) { return synth_record_bytes(read_len, fastq); }
+
+extern "C" int kdb_synth_device(int device, uint8_t* dev_out, uint64_t first_read, uint64_t n_reads, int read_len, int fastq, uint64_t seed) {
+    kdb_ctx* ctx = nullptr;
+    if (!dev_out || read_len < 1) return KDB_E_ARG;
+    CK(cudaSetDevice(device));
+    k_synth<<<148 * 8, 256>>>(dev_out, first_read, n_reads, read_len, fastq, seed);
+    CK(cudaGetLastError());
+    CK(cudaDeviceSynchronize());
+    return KDB_OK;
+}
+
+extern "C" int kdb_synth_host(uint8_t* out, uint64_t first_read, uint64_t n_reads, int read_len, int fastq, uint64_t seed) {
+    if (!out || read_len < 1) return KDB_E_ARG;
+    const uint32_t rb = synth_record_bytes(read_len, fastq);
+    SynthCache cache; cache.valid = false; cache.read = 0; cache.blk = 0;
+    for (uint64_t r = 0; r < n_reads; r++)
+        for (uint32_t off = 0; off < rb; off++) out[r * rb + off] = synth_byte(first_read + r, off, read_len, fastq, seed, cache);
+    return KDB_OK;
+}
+
+// ---- microbenchmarks ---------------------------------------------------------------------------------
+extern "C" int kdb_microbench_atomics(int device, size_t table_bytes, uint64_t n_updates, int mode, double* updates_per_s) {
+    kdb_ctx* ctx = nullptr;
+    if (!updates_per_s) return KDB_E_ARG;
+    CK(cudaSetDevice(device));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    const int grid = 148 * 8, threads = 256;
+    const uint32_t per_thread = (uint32_t)std::max<uint64_t>(1, n_updates / ((uint64_t)grid * threads));
+    float ms = 0;
+    if (mode == 0) {
+        size_t words = 1; while (words * 2 * 4 <= table_bytes) words *= 2;
+        unsigned int* tab = nullptr;
+        CK(cudaMalloc(&tab, words * 4));
+        CK(cudaMemset(tab, 0, words * 4));
+        k_micro_red_global<<<grid, threads>>>(tab, (uint32_t)(words - 1), per_thread / 8 + 1);   // warm-up
+        CK(cudaEventRecord(e0));
+        k_micro_red_global<<<grid, threads>>>(tab, (uint32_t)(words - 1), per_thread);
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        cudaFree(tab);
+    } else {
+        unsigned int* sink = nullptr;
+        CK(cudaMalloc(&sink, 4));
+        CK(cudaFuncSetAttribute(k_micro_atoms_shared, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+        k_micro_atoms_shared<<<grid, threads, 65536>>>(sink, per_thread / 8 + 1);
+        CK(cudaEventRecord(e0));
+        k_micro_atoms_shared<<<grid, threads, 65536>>>(sink, per_thread);
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        cudaFree(sink);
+    }
+    CK(cudaGetLastError());
+    *updates_per_s = (double)per_thread * grid * threads / (ms * 1e-3);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    return KDB_OK;
+}
+
+// ---- raw memory helpers --------------------------------------------------------------------------------
+extern "C" int kdb_dev_alloc(int device, size_t n, void** out) {
+    kdb_ctx* ctx = nullptr;
+    if (!out) return KDB_E_ARG;
+    CK(cudaSetDevice(device));
+    CK(cudaMalloc(out, n ? n : 16));
+    return KDB_OK;
+}
+extern "C" int kdb_dev_free(int device, void* p) {
+    kdb_ctx* ctx = nullptr;
+    CK(cudaSetDevice(device));
+    CK(cudaFree(p));
+    return KDB_OK;
+}
+extern "C" int kdb_host_alloc_pinned(size_t n, void** out) {
+    kdb_ctx* ctx = nullptr;
+    if (!out) return KDB_E_ARG;
+    CK(cudaHostAlloc(out, n ? n : 16, cudaHostAllocDefault));
+    return KDB_OK;
+}
+extern "C" int kdb_host_free_pinned(void* p) {
+    kdb_ctx* ctx = nullptr;
+    CK(cudaFreeHost(p));
+    return KDB_OK;
+}
+extern "C" int kdb_memcpy_h2d(int device, void* dst, const void* src, size_t n) {
+    kdb_ctx* ctx = nullptr;
+    CK(cudaSetDevice(device));
+    CK(cudaMemcpy(dst, src, n, cudaMemcpyHostToDevice));
+    return KDB_OK;
+}
+extern "C" int kdb_memcpy_d2h(int device, void* dst, const void* src, size_t n) {
+    kdb_ctx* ctx = nullptr;
+    CK(cudaSetDevice(device));
+    CK(cudaMemcpy(dst, src, n, cudaMemcpyDeviceToHost));
+    return KDB_OK;
+}

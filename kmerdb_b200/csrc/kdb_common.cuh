@@ -1,0 +1,101 @@
+// kmerdb_b200 device-side common definitions (sm_100a only).
+//
+// Data layout in HBM:
+//   text      : the uncompressed FASTA/FASTQ bytes of one feed, contiguous, 16-byte aligned
+//   tile_state: one TileState per 16 KiB tile of the current pass (K1 output)
+//   tab32     : uint32[4^k] working histogram (red.global.add.u32 target; 64 MiB at k=12, L2-resident)
+//   tab64     : uint64[4^k] result histogram (tab32 is folded into it before it can overflow)
+//   rec_len   : uint64 per record of the current pass (letters; FASTQ: letters, quality chars)
+//   acc       : Accum, the fused scalar reductions
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+
+namespace kdb {
+
+constexpr int kThreads = 256;          // threads per CTA in the scan and count kernels
+constexpr int kChunk = 64;             // text bytes owned by one thread (4 x 16-byte loads)
+constexpr int kTile = kThreads * kChunk;  // 16 KiB of text per tile
+
+// Byte classes inside a sequence line.  kmerdb/kmer.py:44-49 (ACGT codes), :66-80 (permitted set).
+enum : uint8_t {
+    C_A = 0, C_C = 1, C_G = 2, C_T = 3,
+    C_N = 4,        // ambiguous: kmer.py:287-289 / :550-565
+    C_IUPAC = 5,    // RYSWKMBDHV: KeyError at kmer.py:309
+    C_ILLEGAL = 6,  // any other printable ASCII: NameError at kmer.py:168-170
+    C_SPACE = 7,    // dropped by the FASTA tokeniser (Bio.SeqIO: .replace(" ", ""))
+    C_LF = 8,
+    C_CR = 9,       // only legal directly before LF
+    C_WEIRD = 10    // control / DEL / >=0x80: host re-tokenises (KDB_E_LAYOUT)
+};
+
+// Line kinds.
+enum : uint32_t { K_HEADER = 0, K_SEQ = 1, K_IGNORE = 2, K_QUAL = 3 };
+
+// Priority of a raise inside one record, in the order the reference meets them:
+// is_sequence_na over the whole record (kmer.py:519) -> length check (:461-463) -> windows (:309).
+enum : uint32_t { P_ALPHABET = 0, P_SHORT = 1, P_IUPAC = 2 };
+
+struct TileState {
+    unsigned long long ls_base;   // line starts before this tile (within the feed)
+    unsigned long long hdr_base;  // FASTA title lines before this tile (within the file)
+    unsigned int last;            // class of the last line start before the tile: 0 none, 1 other, 2 '>'
+    unsigned int pad;
+};
+
+struct TileSummary {
+    unsigned int ls;    // line starts inside the tile
+    unsigned int hdr;   // of which begin with '>'
+    unsigned int last;  // 0 none, 1 other, 2 '>'  (right-most line start in the tile)
+    unsigned int pad;
+};
+
+// Running totals carried from pass to pass (device resident, updated by the K1 carry scan).
+struct ScanCarry {
+    unsigned long long ls_total;
+    unsigned long long hdr_total;
+    unsigned int last;
+    unsigned int pad;
+};
+
+// Fused scalar reductions (one instance per context, device resident).
+struct Accum {
+    unsigned long long total_kmers;
+    unsigned long long sum_len;
+    unsigned long long mono[4];
+    unsigned long long n_windows_with_n;
+    unsigned long long min_len;
+    unsigned long long max_len;
+    unsigned long long err_key;      // min over raises of (record index * 4 + priority); ~0 = none
+    unsigned long long unique;
+    unsigned int layout_flag;        // != 0: the text needs the host tokeniser
+    unsigned int pad;
+};
+
+struct CountParams {
+    const uint8_t* text;             // feed base
+    unsigned long long lo, hi;       // byte range of this pass inside the feed
+    unsigned long long n;            // feed length
+    const TileState* tiles;
+    unsigned int n_tiles;
+    int k;
+    int canonical;
+    int skip_n;
+    unsigned int* tab32;
+    unsigned long long* rec_len;     // indexed by (record id - rec_first), x2 for FASTQ
+    unsigned long long rec_first;    // record id of rec_len[0]
+    unsigned long long hdr_file_base;// FASTQ: records in earlier feeds of the same file (FASTA ids come from hdr_base)
+    Accum* acc;
+};
+
+__device__ __forceinline__ uint32_t revcomp32(uint32_t f, int k) {
+    uint32_t x = __brev(~f);
+    x = ((x >> 1) & 0x55555555u) | ((x & 0x55555555u) << 1);
+    return x >> (32 - 2 * k);
+}
+
+// Filled by the host at context creation (kdb_api.cu: build_class_lut).  One translation unit
+// includes every kernel header, so a plain __constant__ definition is enough.
+__constant__ uint8_t c_class_lut[256];
+
+}  // namespace kdb

@@ -1,0 +1,106 @@
+// Finalisation kernels: u32->u64 fold, per-record length checks, unique / nullomer reductions.
+// Replaces kmerdb/parse.py:139-146 (nullomer_array, unique_kmers, min/max read length) and the
+// record-length abort of kmerdb/kmer.py:461-463.
+#pragma once
+#include "kdb_common.cuh"
+
+namespace kdb {
+
+// tab64 += tab32; tab32 = 0.  Run before any bin of tab32 can wrap (see DESIGN.md "fold rule").
+__global__ void __launch_bounds__(256) k3_fold(unsigned int* __restrict__ tab32, unsigned long long* __restrict__ tab64,
+                                               unsigned long long nbins) {
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x * 4;
+    for (unsigned long long i = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < nbins; i += stride) {
+        if (i + 4 <= nbins) {
+            uint4 v = *reinterpret_cast<uint4*>(tab32 + i);
+            if (v.x | v.y | v.z | v.w) {
+                ulonglong2 a = *reinterpret_cast<ulonglong2*>(tab64 + i);
+                ulonglong2 b = *reinterpret_cast<ulonglong2*>(tab64 + i + 2);
+                a.x += v.x; a.y += v.y; b.x += v.z; b.y += v.w;
+                *reinterpret_cast<ulonglong2*>(tab64 + i) = a;
+                *reinterpret_cast<ulonglong2*>(tab64 + i + 2) = b;
+                *reinterpret_cast<uint4*>(tab32 + i) = make_uint4(0, 0, 0, 0);
+            }
+        } else {
+            for (unsigned long long j = i; j < nbins; j++) { tab64[j] += tab32[j]; tab32[j] = 0; }
+        }
+    }
+}
+
+// Records [0, n_complete) of rec_len are closed: min / max length, short-record raise, and for
+// FASTQ the sequence/quality length agreement (Bio.SeqIO raises ValueError otherwise -> host).
+template <bool FASTQ>
+__global__ void __launch_bounds__(256) k4_check_records(const unsigned long long* __restrict__ rec_len, unsigned long long n_complete,
+                                                        unsigned long long rec_first, int k, Accum* acc) {
+    unsigned long long mn = ~0ull, mx = 0, err = ~0ull;
+    unsigned int layout = 0;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_complete; i += stride) {
+        const unsigned long long len = FASTQ ? rec_len[2 * i] : rec_len[i];
+        if (FASTQ && rec_len[2 * i + 1] != len) layout = 1;
+        mn = len < mn ? len : mn;
+        mx = len > mx ? len : mx;
+        if (len < (unsigned long long)k) { const unsigned long long key = (rec_first + i) * 4 + P_SHORT; err = key < err ? key : err; }
+    }
+    for (int d = 16; d; d >>= 1) {
+        unsigned long long o = __shfl_xor_sync(0xffffffffu, mn, d); mn = o < mn ? o : mn;
+        o = __shfl_xor_sync(0xffffffffu, mx, d); mx = o > mx ? o : mx;
+        o = __shfl_xor_sync(0xffffffffu, err, d); err = o < err ? o : err;
+        layout |= __shfl_xor_sync(0xffffffffu, layout, d);
+    }
+    if ((threadIdx.x & 31) == 0) {
+        if (mn != ~0ull) atomicMin(&acc->min_len, mn);
+        if (mx) atomicMax(&acc->max_len, mx);
+        if (err != ~0ull) atomicMin(&acc->err_key, err);
+        if (layout) atomicOr(&acc->layout_flag, 1u);
+    }
+}
+
+// unique_kmers = count_nonzero(counts)  (parse.py:141)
+__global__ void __launch_bounds__(256) k5_count_nonzero(const unsigned long long* __restrict__ tab64, unsigned long long nbins, Accum* acc) {
+    unsigned long long c = 0;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
+    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < nbins; i += stride) c += tab64[i] != 0;
+    for (int d = 16; d; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(&acc->unique, c);
+}
+
+// nullomer_array = arange(4^k)[counts == 0]  (parse.py:139-140), ascending.  Two passes over
+// fixed 2048-bin blocks: per-block zero counts, host-side exclusive scan of the (small) block
+// counts, then an ordered write.
+constexpr int kNullBlock = 2048;
+__global__ void __launch_bounds__(256) k6_null_count(const unsigned long long* __restrict__ tab64, unsigned long long nbins,
+                                                     unsigned int* __restrict__ block_zero) {
+    __shared__ unsigned int s;
+    if (threadIdx.x == 0) s = 0;
+    __syncthreads();
+    const unsigned long long base = (unsigned long long)blockIdx.x * kNullBlock;
+    unsigned int c = 0;
+    for (int j = threadIdx.x; j < kNullBlock; j += 256) { const unsigned long long i = base + j; if (i < nbins && tab64[i] == 0) c++; }
+    for (int d = 16; d; d >>= 1) c += __shfl_xor_sync(0xffffffffu, c, d);
+    if ((threadIdx.x & 31) == 0 && c) atomicAdd(&s, c);
+    __syncthreads();
+    if (threadIdx.x == 0) block_zero[blockIdx.x] = s;
+}
+__global__ void __launch_bounds__(256) k6_null_write(const unsigned long long* __restrict__ tab64, unsigned long long nbins,
+                                                     const unsigned long long* __restrict__ block_off, unsigned long long* __restrict__ out,
+                                                     unsigned long long cap) {
+    __shared__ unsigned int s_warp[8];
+    const unsigned long long base = (unsigned long long)blockIdx.x * kNullBlock;
+    unsigned long long off = block_off[blockIdx.x];
+    for (int j0 = 0; j0 < kNullBlock; j0 += 256) {
+        const unsigned long long i = base + j0 + threadIdx.x;
+        const bool z = i < nbins && tab64[i] == 0;
+        const unsigned int bal = __ballot_sync(0xffffffffu, z);
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        if (lane == 0) s_warp[warp] = __popc(bal);
+        __syncthreads();
+        unsigned int before = 0, total = 0;
+        for (int w = 0; w < 8; w++) { const unsigned int x = s_warp[w]; if (w < warp) before += x; total += x; }
+        if (z) { const unsigned long long pos = off + before + __popc(bal & ((1u << lane) - 1u)); if (pos < cap) out[pos] = i; }
+        off += total;
+        __syncthreads();
+    }
+}
+
+}  // namespace kdb

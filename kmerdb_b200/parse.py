@@ -1,0 +1,253 @@
+"""Host-side mirror of kmerdb/parse.py for the `profile` hot path.
+
+`parsefile` keeps the reference's signature, return tuple, metadata keys and exception classes
+(kmerdb/parse.py:90-163); the per-window Python loop (parse.py:128-137 -> kmer.shred,
+kmerdb/kmer.py:489-577) is replaced by the CUDA kernels behind include/kmerdb_b200.h.  Host code
+only opens / gunzips the file (unchanged from the reference), checksums it and turns device status
+codes back into the reference's exceptions.  There is no CPU counting path."""
+import gzip
+import hashlib
+import io
+import os
+from collections import namedtuple
+
+import numpy as np
+
+from . import _native
+
+SeqRecord = namedtuple("SeqRecord", ["id", "seq", "description"])
+
+FASTA_SUFFIXES = (".fna", ".fna.gz", ".fa.gz", ".fa", ".fasta", ".fasta.gz")      # kmerdb/util.py:120-126
+FASTQ_SUFFIXES = (".fastq", ".fastq.gz", ".fq.gz", ".fq")                         # kmerdb/util.py:128-134
+
+
+def is_fasta(fname):
+    if type(fname) is not str:
+        raise TypeError("kmerdb.util.is_fasta() expects a str argument")
+    return fname.endswith(FASTA_SUFFIXES)
+
+
+def is_fastq(fname):
+    if type(fname) is not str:
+        raise TypeError("kmerdb.util.is_fasta() expects a str argument")
+    return fname.endswith(FASTQ_SUFFIXES)
+
+
+def is_gz_file(filepath):
+    """kmerdb/util.py:80-88: gzip is decided by trying to read, not by the suffix."""
+    try:
+        with gzip.open(filepath, "rb") as f:
+            f.readline()
+        return True
+    except OSError:
+        return False
+
+
+def checksum(filepath):
+    """kmerdb/util.py:35-50: md5 and sha256 of the raw (possibly compressed) file bytes."""
+    if type(filepath) is not str:
+        raise TypeError("kmerdb.util.checksum() expects a str as its argument")
+    elif not os.path.exists(filepath):
+        raise IOError("could not find '{}' on the filesystem".format(filepath))
+    md5, sha = hashlib.md5(), hashlib.sha256()
+    with open(filepath, "rb") as fh:
+        for chunk in iter(lambda: fh.read(1 << 20), b""):
+            md5.update(chunk)
+            sha.update(chunk)
+    return md5.hexdigest(), sha.hexdigest()
+
+
+def _read_text_bytes(filepath):
+    """Uncompressed file text (host gzip decode, as in kmerdb/parse.py:63-68)."""
+    if is_gz_file(filepath):
+        with gzip.open(filepath, "rb") as fh:
+            return fh.read()
+    with open(filepath, "rb") as fh:
+        return fh.read()
+
+
+def _file_format(filepath):
+    if is_fasta(filepath):
+        return "fasta"
+    if is_fastq(filepath):
+        return "fastq"
+    raise ValueError("Could not determine the format of file '{0}'".format(filepath))   # parse.py:74
+
+
+# ---- host tokeniser ---------------------------------------------------------------------------------
+# Used (a) by parse_sequence_file, which must yield records to Python callers, and (b) when the
+# device tokeniser answers KDB_E_LAYOUT (lone CR line breaks, multi-line FASTQ, "+title" repeats,
+# control or non-ASCII bytes): the records are re-laid out as plain one-line FASTA and counted on
+# the GPU all the same.  Semantics follow Biopython 1.83 (Pipfile.lock:28-60) as called at
+# kmerdb/parse.py:70-72: text mode, UTF-8, universal newlines.
+
+def _iter_fasta(handle):
+    title, lines = None, []
+    for line in handle:
+        if line[0] == ">":
+            if title is not None:
+                yield title, "".join(lines).replace(" ", "").replace("\r", "")
+            title, lines = line[1:].rstrip(), []
+        elif title is not None:
+            lines.append(line.rstrip())
+    if title is not None:
+        yield title, "".join(lines).replace(" ", "").replace("\r", "")
+
+
+def _iter_fastq(handle):
+    line = handle.readline()
+    while line:
+        if line[0] != "@":
+            raise ValueError("Records in Fastq files should start with '@' character")
+        title = line[1:].rstrip()
+        seq = handle.readline().rstrip()
+        while True:
+            line = handle.readline()
+            if not line:
+                raise ValueError("End of file without quality information.")
+            if line[0] == "+":
+                second = line[1:].rstrip()
+                if second and second != title:
+                    raise ValueError("Sequence and quality captions differ.")
+                break
+            seq += line.rstrip()
+        if " " in seq or "\t" in seq:
+            raise ValueError("Whitespace is not allowed in the sequence.")
+        qual = handle.readline().rstrip()
+        while True:
+            line = handle.readline()
+            if not line:
+                break
+            if line[0] == "@" and len(qual) >= len(seq):
+                break
+            qual += line.rstrip()
+        if len(seq) != len(qual):
+            raise ValueError("Lengths of sequence and quality values differs for %s (%i and %i)." % (title, len(seq), len(qual)))
+        for ch in qual:
+            if not 33 <= ord(ch) <= 126:
+                raise ValueError("Invalid character in quality string")
+        yield title, seq
+
+
+def _iter_records(data, fmt):
+    handle = io.TextIOWrapper(io.BytesIO(data), encoding="UTF-8", newline=None)
+    return _iter_fasta(handle) if fmt == "fasta" else _iter_fastq(handle)
+
+
+def parse_sequence_file(seq_filepath, return_tuple=True):
+    """kmerdb/parse.py:50-85.  Yields (seq_id, seq) tuples, or record objects with .id/.seq."""
+    if type(seq_filepath) is not str:
+        raise TypeError("kmerdb.graph.parse_sequence_file() expects a fasta/fastq sequence filepath as a str as its only positional_regument")
+    if os.path.exists(seq_filepath) is False or os.access(seq_filepath, os.R_OK) is False:
+        raise ValueError("kmerdb.graph.parse_sequence_file() expects the filepath to be be readable on the filesystem")
+    data = _read_text_bytes(seq_filepath)
+    fmt = _file_format(seq_filepath)
+    for title, seq in _iter_records(data, fmt):
+        parts = title.split(None, 1)
+        rid = parts[0] if parts else ""
+        yield (rid, seq) if return_tuple else SeqRecord(rid, seq, title)
+
+
+_PERMITTED = frozenset("ACGTRYSWKMBDHVN")
+
+
+def _plain_layout(data, fmt):
+    """Re-lay the records out as '>\\n' + letters + '\\n'.  Letters outside the permitted alphabet
+    become '?' (one per character, so record lengths are kept; the device raises NameError for it,
+    kmerdb/kmer.py:168-170).  Returns (bytes, pending_exception)."""
+    out, pending = [], None
+    try:
+        for _title, seq in _iter_records(data, fmt):
+            if not _PERMITTED.issuperset(seq):
+                seq = "".join(ch if ch in _PERMITTED else "?" for ch in seq)
+            out.append(">\n" + seq + "\n")
+    except ValueError as e:          # grammar violation (or UnicodeDecodeError): raised after the records before it
+        pending = e
+    return "".join(out).encode("ascii"), pending
+
+
+def _raise_for_status(status, st):
+    if status == _native.KDB_E_ALPHABET:
+        raise NameError("name 'permitted_AA_characters_extended' is not defined")        # kmer.py:170
+    if status == _native.KDB_E_IUPAC:
+        raise KeyError("non-ACGT IUPAC letter in record %d reached the 2-bit encoder" % st["err_record"])   # kmer.py:309
+    if status == _native.KDB_E_SHORT:
+        raise AttributeError("'Seq' object has no attribute 'id'")                        # kmer.py:461-463
+    if status == _native.KDB_E_EMPTY:
+        raise ValueError("max() iterable argument is empty")                              # parse.py:144
+    if status == _native.KDB_E_FORMAT:
+        raise ValueError("malformed sequence file")
+    if status != 0:
+        raise RuntimeError("kmerdb_b200: unexpected device status %d" % status)
+
+
+class Profile:
+    """Result of one file's profile: the attributes the reference spreads over parse.parsefile's
+    return tuple and the .kdb header (counts, total/unique k-mers, nullomers, mononucleotides)."""
+
+    def __init__(self, k, counts, stats, nullomer_array, timing=None):
+        self.k = k
+        self.counts = counts
+        self.nullomer_array = nullomer_array
+        self.total_reads = stats["total_reads"]
+        self.total_kmers = stats["total_kmers"]
+        self.unique_kmers = stats["unique_kmers"]
+        self.nullomers = 4 ** k - stats["unique_kmers"]                        # parse.py:143
+        self.min_read_length = stats["min_len"]
+        self.max_read_length = stats["max_len"]
+        self.avg_read_length = int(stats["sum_len"] / stats["total_reads"])      # int(np.mean(...)) parse.py:146
+        self.mononucleotides = dict(zip("ACGT", stats["mono"]))
+        self.timing = timing
+
+    def file_metadata(self, filename, md5, sha256):
+        return {
+            "filename": filename, "md5": md5, "sha256": sha256,
+            "total_reads": self.total_reads, "total_kmers": self.total_kmers, "unique_kmers": self.unique_kmers,
+            "nullomers": self.nullomers, "min_read_length": self.min_read_length,
+            "max_read_length": self.max_read_length, "avg_read_length": self.avg_read_length,
+        }
+
+
+def profile_bytes(data, k, fmt="fasta", replace_with_none=True, canonicalize=True, device=0, want_nullomers=True):
+    """Profile uncompressed FASTA/FASTQ text held in host memory.  Raises the reference's exceptions."""
+    with _native.Profiler(k, canonical=canonicalize, skip_n=replace_with_none, fastq=(fmt == "fastq"), device=device) as p:
+        p.feed(data)
+        status = p.finish()
+        if status == _native.KDB_E_LAYOUT:
+            plain, pending = _plain_layout(bytes(data), fmt)
+            p.close()
+            with _native.Profiler(k, canonical=canonicalize, skip_n=replace_with_none, fastq=False, device=device) as q:
+                q.feed(plain)
+                status = q.finish()
+                st = q.stats()
+                if status not in (0, _native.KDB_E_EMPTY) or pending is None:
+                    _raise_for_status(status, st)
+                if pending is not None:
+                    raise pending
+                return Profile(k, q.counts(), st, q.nullomers() if want_nullomers else None, q.timing())
+        st = p.stats()
+        _raise_for_status(status, st)
+        return Profile(k, p.counts(), st, p.nullomers() if want_nullomers else None, p.timing())
+
+
+def parsefile(filepath, k, replace_with_none=True, canonicalize=True, device=0, with_mononucleotides=False):
+    """Drop-in for kmerdb.parse.parsefile (kmerdb/parse.py:90-163).
+
+    :returns: (counts uint64[4**k], file_metadata dict, nullomer_array uint64)"""
+    if filepath is None or type(filepath) is not str:
+        raise TypeError("kmerdb.parse.parsefile expects a str as its first positional argument")
+    elif not os.path.exists(filepath):
+        raise OSError("kmerdb.parse.parsefile could not find the file '{0}' on the filesystem".format(filepath))
+    elif k is None or type(k) is not int:
+        raise TypeError("kmerdb.parse.parsefile expects an int as its second positional argument")
+    elif type(replace_with_none) is not bool:
+        raise TypeError("kmerdb.parse.parsefile expects the keyword argument 'replace_with_none' to be a bool")
+    md5, sha256 = checksum(filepath)
+    data = _read_text_bytes(filepath)
+    fmt = _file_format(filepath)
+    prof = profile_bytes(data, k, fmt, replace_with_none, bool(canonicalize), device)
+    assert prof.nullomers == len(prof.nullomer_array), "Internal Error: kmerdb.parse.parsefile() found inconsistencies between two ways of counting nullomers. Internal error."
+    meta = prof.file_metadata(filepath, md5, sha256)
+    if with_mononucleotides:
+        meta["mononucleotides"] = prof.mononucleotides        # legacy header field (README.md:31)
+    return prof.counts, meta, prof.nullomer_array

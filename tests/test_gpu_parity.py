@@ -1,0 +1,187 @@
+"""Parity tests proper: the CUDA path (through the C-ABI, kmerdb_b200._native / kmerdb_b200.parse)
+against the golden vectors of the unmodified reference and against the CPU oracle on the same
+seeded inputs.  Bit-exact: integer work only."""
+import gzip
+import hashlib
+import os
+
+import numpy as np
+import pytest
+
+import oracle
+from kmerdb_b200 import _native, parse
+from test_oracle import _golden_cases, _case_id
+
+pytestmark = pytest.mark.gpu
+
+EXC = {"NameError": NameError, "KeyError": KeyError, "AttributeError": AttributeError, "ValueError": ValueError}
+
+
+@pytest.mark.parametrize("c", _golden_cases(), ids=_case_id)
+def test_parsefile_matches_reference_golden(c, tmp_path):
+    path = str(tmp_path / ("input" + c["suffix"] + (".gz" if c["gz"] else "")))
+    with (gzip.open(path, "wb") if c["gz"] else open(path, "wb")) as fh:
+        fh.write(c["text"].encode())
+    e = c["expect"]
+    if "raises" in e:
+        with pytest.raises(EXC[e["raises"]]) as ei:
+            parse.parsefile(path, c["k"], replace_with_none=c["replace_with_none"], canonicalize=c["canonicalize"])
+        assert type(ei.value).__name__ == e["raises"] or e["raises"] == "ValueError"   # UnicodeDecodeError etc. are ValueErrors
+        return
+    counts, meta, nullomers = parse.parsefile(path, c["k"], replace_with_none=c["replace_with_none"], canonicalize=c["canonicalize"])
+    assert counts.dtype == np.uint64 and counts.shape == (4 ** c["k"],)
+    assert meta["filename"] == path
+    assert meta["md5"] == hashlib.md5(open(path, "rb").read()).hexdigest()
+    assert meta["sha256"] == hashlib.sha256(open(path, "rb").read()).hexdigest()
+    got = {a: b for a, b in meta.items() if a not in ("filename", "md5", "sha256")}
+    assert got == e["meta"]
+    assert hashlib.sha256(counts.astype("<u8").tobytes()).hexdigest() == e["counts_sha256"]
+    assert nullomers.dtype == np.uint64 and len(nullomers) == e["n_nullomers"]
+    assert hashlib.sha256(nullomers.astype("<u8").tobytes()).hexdigest() == e["nullomers_sha256"]
+
+
+def _cmp_oracle(data, k, fastq=False, skip_n=True, canonical=True, threads=8):
+    rc, ocounts, ost = oracle.profile(data, k, fastq=fastq, skip_n=skip_n, canonical=canonical, threads=threads)
+    with _native.Profiler(k, canonical=canonical, skip_n=skip_n, fastq=fastq) as p:
+        p.feed(data)
+        status = p.finish()
+        st = p.stats()
+        if rc != 0:
+            assert status == {1: 1, 2: 2, 3: 3, 4: 7, 5: 5}[rc]
+            return
+        assert status == 0
+        counts = p.counts()
+        assert np.array_equal(counts, ocounts)
+        for a, b in (("total_reads", "total_reads"), ("total_kmers", "total_kmers"), ("unique_kmers", "unique_kmers"),
+                     ("sum_len", "sum_len"), ("min_len", "min_len"), ("max_len", "max_len"), ("mono", "mono")):
+            assert st[a] == ost[b], a
+        nul = p.nullomers()
+        assert np.array_equal(nul, np.nonzero(ocounts == 0)[0].astype(np.uint64))
+
+
+def _random_fasta(rng, n_rec, min_len, max_len, width, alphabet="ACGT", p=None, crlf=False):
+    eol = "\r\n" if crlf else "\n"
+    letters = np.array(list(alphabet))
+    out = []
+    for i in range(n_rec):
+        L = int(rng.integers(min_len, max_len + 1))
+        s = "".join(letters[rng.choice(len(letters), size=L, p=p)])
+        out.append(">rec%d some text > with symbols" % i + eol)
+        if width:
+            for j in range(0, L, width):
+                out.append(s[j:j + width] + eol)
+        else:
+            out.append(s + eol)
+    return "".join(out).encode()
+
+
+@pytest.mark.parametrize("k", [1, 2, 3, 5, 7, 8, 9, 11, 12, 13])
+@pytest.mark.parametrize("canonical", [True, False])
+def test_random_fasta_all_k(k, canonical):
+    rng = np.random.default_rng(100 + k)
+    data = _random_fasta(rng, 400, 20, 900, 70)
+    _cmp_oracle(data, k, canonical=canonical)
+
+
+@pytest.mark.parametrize("width", [0, 1, 7, 60, 61, 64, 1000])
+def test_line_widths_cross_chunks_and_tiles(width):
+    rng = np.random.default_rng(7 + width)
+    data = _random_fasta(rng, 60, 1000, 40000, width, crlf=(width == 61))
+    _cmp_oracle(data, 9)
+
+
+@pytest.mark.parametrize("skip_n", [True, False])
+@pytest.mark.parametrize("k", [3, 6, 8, 10])
+def test_n_windows(k, skip_n):
+    rng = np.random.default_rng(5)
+    data = _random_fasta(rng, 300, 30, 400, 80, alphabet="ACGTN", p=[0.2475, 0.2475, 0.2475, 0.2475, 0.01])
+    _cmp_oracle(data, k, skip_n=skip_n)
+    _cmp_oracle(data, k, skip_n=skip_n, canonical=False)
+
+
+def test_long_n_runs_expand():
+    data = b">a\nACGTNNNNNNACGTACGTNNACGTTTGACNACGT\n>b\nNNNNNNNNNNNN\n>c\nACGTACGTACGTACGT\n"
+    for k in (4, 6):
+        _cmp_oracle(data, k, skip_n=False)
+        _cmp_oracle(data, k, skip_n=False, canonical=False)
+
+
+def _random_fastq(rng, n_rec, min_len, max_len, crlf=False):
+    eol = "\r\n" if crlf else "\n"
+    out = []
+    for i in range(n_rec):
+        L = int(rng.integers(min_len, max_len + 1))
+        s = "".join(np.array(list("ACGT"))[rng.integers(0, 4, size=L)])
+        q = "".join("@+I5#>"[(i + j) % 6] for j in range(L))
+        out.append("@read%d/1 x" % i + eol + s + eol + "+" + eol + q + eol)
+    return "".join(out).encode()
+
+
+@pytest.mark.parametrize("k", [4, 8, 12])
+def test_random_fastq(k):
+    rng = np.random.default_rng(11)
+    _cmp_oracle(_random_fastq(rng, 3000, 30, 260), k, fastq=True)
+    _cmp_oracle(_random_fastq(rng, 500, 30, 260, crlf=True), k, fastq=True, canonical=False)
+
+
+def test_error_record_order_matches_oracle():
+    rng = np.random.default_rng(3)
+    base = _random_fasta(rng, 200, 50, 300, 60).decode()
+    recs = base.split(">")[1:]
+    for bad_at, bad in ((150, "ACGTacgtACGTACGTAAAA"), (20, "ACGTRCGTACGTACGTAAAA"), (77, "ACG")):
+        r = list(recs)
+        r[bad_at] = "bad\n" + bad + "\n"
+        r[180] = "bad2\nAC\n"
+        _cmp_oracle((">" + ">".join(r)).encode(), 8)
+
+
+def test_synthetic_generator_host_equals_device():
+    n = 5000
+    host = _native.synth_host(n)
+    buf = _native.DeviceBuffer(host.size)
+    _native.synth_device(buf, n)
+    assert np.array_equal(buf.download(), host)
+    hq = _native.synth_host(n, fastq=True)
+    bq = _native.DeviceBuffer(hq.size)
+    _native.synth_device(bq, n, fastq=True)
+    assert np.array_equal(bq.download(), hq)
+    assert host[0] == ord(">") and hq[0] == ord("@")
+
+
+def test_synthetic_reads_k12_vs_oracle_and_device_feed():
+    n = 200000
+    host = _native.synth_host(n)
+    _cmp_oracle(host, 12)
+    buf = _native.DeviceBuffer(host.size)
+    _native.synth_device(buf, n)
+    rc, ocounts, ost = oracle.profile(host, 12, threads=8)
+    with _native.Profiler(12) as p:
+        p.feed_device(buf.ptr, host.size)
+        assert p.finish() == 0
+        assert np.array_equal(p.counts(), ocounts)
+        assert p.stats()["total_kmers"] == n * 139 == ost["total_kmers"]
+
+
+def test_fragment_feeds_equal_single_feed():
+    n = 30000
+    host = _native.synth_host(n)
+    rb = _native.synth_record_bytes()
+    with _native.Profiler(10) as p:
+        p.feed(host)
+        assert p.finish() == 0
+        whole, wst = p.counts(), p.stats()
+    with _native.Profiler(10) as p:
+        cuts = [0, 1 * rb, 7777 * rb, 20000 * rb, n * rb]
+        for a, b in zip(cuts, cuts[1:]):
+            p.feed(host[a:b])
+        assert p.finish() == 0
+        assert np.array_equal(p.counts(), whole)
+        assert p.stats() == wst
+
+
+def test_kmer_to_id_batch(golden):
+    two = "".join(a + b for a in "ACGT" for b in "ACGT").encode()
+    assert _native.kmer_to_id_batch(two, 2, canonical=False).tolist() == golden["scalars"]["kmer_to_id_2mers_noncanonical"]
+    assert _native.kmer_to_id_batch(two, 2, canonical=True).tolist() == golden["scalars"]["kmer_to_id_2mers_canonical"]
+    ids = _native.kmer_to_id_batch(b"ATCNATCACGRACG", 7)
+    assert ids[0] == np.uint64(2 ** 64 - 1) and ids[1] == np.uint64(2 ** 64 - 2)
