@@ -127,3 +127,206 @@ def workload_config(args, n_gpus):
             "k": args.k, "reads_per_gpu": args.reads, "read_len": READ_LEN, "canonical": True, "format": "fasta", "seed": SEED,
             "l2": "input (%.2f GB per GPU) is larger than L2; no flush needed" % (args.reads * 162 / 1e9),
             "parallelism": "reads sharded over %d GPU(s); partial 4^k tables sum-reduced to rank 0 with NCCL" % n_gpus if n_gpus > 1 else "1 GPU"}
+
+
+class CudaArray:
+    """Zero-copy view of a device allocation for torch (CUDA array interface)."""
+
+    def __init__(self, ptr, n, typestr="<i8"):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+def run_b200(args):
+    import torch
+    import torch.distributed as dist
+    from kmerdb_b200 import _native
+
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    if world != args.gpus:
+        if world == 1 and args.gpus > 1:
+            raise SystemExit("bench.py --gpus %d must be launched with torch.distributed.run --nproc-per-node %d" % (args.gpus, args.gpus))
+    if not torch.cuda.is_available():
+        raise SystemExit("bench.py needs a CUDA device: the profile path has no CPU fallback")
+    torch.cuda.set_device(local)
+    if world > 1:
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local))
+
+    k, n_reads = args.k, args.reads
+    rb = _native.synth_record_bytes(READ_LEN)
+    nbytes = n_reads * rb
+    n_bases = n_reads * READ_LEN
+    dev_text = _native.DeviceBuffer(nbytes + 16, device=local)
+    _native.synth_device(dev_text, n_reads, READ_LEN, seed=SEED, first_read=rank * n_reads)
+    prof = _native.Profiler(k, canonical=True, skip_n=True, fastq=False, device=local)
+    tab_ptr = None
+    red_tensor = None
+
+    def barrier():
+        if world > 1:
+            dist.barrier()
+        torch.cuda.synchronize()
+
+    def reduce_to_rank0():
+        """NCCL sum-reduce of the 4^k uint64 partials (as int64: two's complement sums are the same bits)
+        and of the additive scalars; min/max go through their own reductions."""
+        nonlocal tab_ptr, red_tensor
+        if world == 1:
+            return
+        if tab_ptr is None:
+            tab_ptr, nb = prof.device_table()
+            red_tensor = torch.as_tensor(CudaArray(tab_ptr, nb), device=torch.device("cuda", local))
+        dist.reduce(red_tensor, dst=0, op=dist.ReduceOp.SUM)
+        part = prof.export_partials().astype(np.int64)
+        sums = torch.from_numpy(part[:8].copy()).cuda(local)
+        mins = torch.from_numpy(part[[8, 10]].copy().view(np.uint64).astype(np.float64)).cuda(local)  # min_len, err_key (exact below 2^53; ~0 stays largest)
+        maxs = torch.from_numpy(part[[9, 11]].copy()).cuda(local)
+        dist.reduce(sums, dst=0, op=dist.ReduceOp.SUM)
+        dist.reduce(mins, dst=0, op=dist.ReduceOp.MIN)
+        dist.reduce(maxs, dst=0, op=dist.ReduceOp.MAX)
+        torch.cuda.synchronize()
+        if rank == 0:
+            out = np.zeros(16, dtype=np.uint64)
+            out[:8] = sums.cpu().numpy().view(np.uint64)
+            mn = mins.cpu().numpy()
+            out[8] = np.uint64(mn[0]) if mn[0] < 2.0 ** 63 else np.uint64(2 ** 64 - 1)
+            out[10] = np.uint64(mn[1]) if mn[1] < 2.0 ** 63 else np.uint64(2 ** 64 - 1)
+            mx = maxs.cpu().numpy().view(np.uint64)
+            out[9], out[11] = mx[0], mx[1]
+            prof.import_partials(out)
+            prof.refinalize()
+
+    def step_device():
+        prof.reset()
+        prof.feed_device(dev_text.ptr, nbytes)
+        status = prof.finish()
+        assert status == 0, "device status %d" % status
+        reduce_to_rank0()
+        return prof.timing()
+
+    # ---- value: device-resident input ------------------------------------------------------------
+    for _ in range(args.warmup):
+        step_device()
+    sampler = ClockSampler(local)
+    if rank == 0:
+        sampler.start()
+    barrier()
+    ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    t0 = time.perf_counter()
+    ev0.record()
+    job_ms = count_ms = scan_ms = fold_ms = final_ms = 0.0
+    count_launches = launches = 0
+    for _ in range(args.steps):
+        t = step_device()
+        job_ms += t["job_ms"]; count_ms += t["count_ms"]; scan_ms += t["scan_ms"]; fold_ms += t["fold_ms"]; final_ms += t["final_ms"]
+        count_launches += t["count_launches"]; launches += t["total_launches"]
+    ev1.record()
+    barrier()
+    wall = time.perf_counter() - t0
+    clocks = sampler.stop() if rank == 0 else None
+    # every call of the C-ABI is synchronous, so the wall clock between the two barriers is the device
+    # time of the K steps plus launch gaps; job_ms is the CUDA-event time on the context's own stream
+    tt = torch.tensor([wall, job_ms * 1e-3], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(tt, op=dist.ReduceOp.MAX)
+    wall_max, job_max = tt.tolist()
+    stats = prof.stats()
+
+    # ---- e2e: host buffers through the C-ABI, copies inside the timed region ----------------------
+    pin_text = _native.PinnedBuffer(nbytes)
+    _native.lib().kdb_memcpy_d2h(local, pin_text.ptr, dev_text.ptr, nbytes)
+    pin_counts = _native.PinnedBuffer(8 * 4 ** k)
+    counts_view = pin_counts.array.view(np.uint64)
+
+    def step_host():
+        prof.reset()
+        prof.feed(pin_text.array)
+        status = prof.finish()
+        assert status == 0
+        reduce_to_rank0()
+        if rank == 0:
+            prof.counts(out=counts_view)
+            return prof.stats()
+        return None
+
+    for _ in range(max(1, args.warmup // 2)):
+        step_host()
+    barrier()
+    t0 = time.perf_counter()
+    e2e_steps = max(1, min(args.steps, 5))
+    for _ in range(e2e_steps):
+        st_host = step_host()
+    barrier()
+    e2e_wall = time.perf_counter() - t0
+    te = torch.tensor([e2e_wall], dtype=torch.float64, device="cuda")
+    if world > 1:
+        dist.all_reduce(te, op=dist.ReduceOp.MAX)
+    e2e_wall = te.item()
+
+    if rank == 0:
+        assert stats["total_kmers"] == world * n_reads * (READ_LEN - k + 1), stats
+        assert st_host["total_kmers"] == stats["total_kmers"] and int(counts_view.sum()) == stats["total_kmers"]
+        peak, peak_src = peaks()
+        per_launch_bytes = nbytes / (count_launches / args.steps)
+        avg_launch_s = count_ms * 1e-3 / count_launches
+        achieved = per_launch_bytes / avg_launch_s / 1e9
+        traffic = None
+        tpath = os.path.join(ROOT, "profiles", "traffic_k2_count.json")
+        if os.path.exists(tpath):
+            try:
+                traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+            except Exception:
+                traffic = None
+        line = {
+            "metric": METRIC, "value": world * n_bases * args.steps / job_max if world == 1 else world * n_bases * args.steps / wall_max,
+            "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": 1e3 * (job_max if world == 1 else wall_max) / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "u32", "data": "synthetic", "config": workload_config(args, world),
+            "wall_ms_per_step": 1e3 * wall_max / args.steps,
+            "e2e": {"value": world * n_bases * e2e_steps / e2e_wall, "unit": UNIT, "h2d_bytes_per_step": nbytes,
+                    "d2h_bytes_per_step": 8 * 4 ** k + 112, "steps": e2e_steps},
+            "gpu_launches": int(launches),
+            "roofline": {"bound": "hbm", "kernel": "k2_count", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+                         "traffic": traffic, "peak_source": peak_src,
+                         "algorithmic_bytes_per_base": rb / READ_LEN, "bytes_per_launch": per_launch_bytes,
+                         "avg_launch_ms": 1e3 * avg_launch_s,
+                         "whole_job_frac": (nbytes * args.steps / (job_max if world == 1 else wall_max) / 1e9) / peak,
+                         "note": "k>=8 is bound by scattered 32-bit atomics, not HBM: see DESIGN.md (atomic roofline) and profiles/"},
+            "kernel_ms_per_step": {"scan": scan_ms / args.steps, "count": count_ms / args.steps, "fold": fold_ms / args.steps, "final": final_ms / args.steps},
+            "clocks": clocks,
+            "result_check": {"total_kmers": stats["total_kmers"], "unique_kmers": stats["unique_kmers"], "total_reads": stats["total_reads"]},
+        }
+        if not args.no_cpu_baseline:
+            threads = host_threads()
+            text = pin_text.array[: args.cpu_reads * rb]
+            dt, ost = time_oracle(text, k, threads)
+            line["cpu_baseline"] = {"value": args.cpu_reads * READ_LEN / dt, "unit": UNIT, "cores": threads, "kind": "port",
+                                    "sample": "first %d reads of the same stream, oracle/kmerdb_oracle.c on %d threads, %.1f s" % (args.cpu_reads, threads, dt)}
+        print(json.dumps(line), flush=True)
+    if world > 1:
+        dist.barrier()
+        dist.destroy_process_group()
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
+    ap.add_argument("--reads", type=int, default=10_000_000, help="reads per GPU (configs[1]: 10M x 150 bp)")
+    ap.add_argument("--k", type=int, default=12)
+    ap.add_argument("--cpu-reads", type=int, default=2_000_000, help="bounded sample for the CPU legs")
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    args = ap.parse_args()
+    if args.warmup < 3 and args.impl == "b200":
+        args.warmup = 3
+    if args.impl == "reference":
+        run_reference(args)
+    else:
+        run_b200(args)
+
+
+if __name__ == "__main__":
+    main()
