@@ -215,11 +215,11 @@ def run_b200(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     ev0.record()
-    job_ms = count_ms = scan_ms = fold_ms = final_ms = 0.0
+    job_ms = count_ms = scan_ms = fold_ms = final_ms = encode_ms = 0.0
     count_launches = launches = 0
     for _ in range(args.steps):
         t = step_device()
-        job_ms += t["job_ms"]; count_ms += t["count_ms"]; scan_ms += t["scan_ms"]; fold_ms += t["fold_ms"]; final_ms += t["final_ms"]
+        job_ms += t["job_ms"]; count_ms += t["count_ms"]; encode_ms += t["encode_ms"]; scan_ms += t["scan_ms"]; fold_ms += t["fold_ms"]; final_ms += t["final_ms"]
         count_launches += t["count_launches"]; launches += t["total_launches"]
     ev1.record()
     barrier()
@@ -287,13 +287,13 @@ def run_b200(args):
             "e2e": {"value": world * n_bases * e2e_steps / e2e_wall, "unit": UNIT, "h2d_bytes_per_step": nbytes,
                     "d2h_bytes_per_step": 8 * 4 ** k + 112, "steps": e2e_steps},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k2_count", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "roofline": {"bound": "hbm", "kernel": "k3_count", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_base": rb / READ_LEN, "bytes_per_launch": per_launch_bytes,
                          "avg_launch_ms": 1e3 * avg_launch_s,
                          "whole_job_frac": (nbytes * args.steps / (job_max if world == 1 else wall_max) / 1e9) / peak,
                          "note": "k>=8 is bound by scattered 32-bit atomics, not HBM: see DESIGN.md (atomic roofline) and profiles/"},
-            "kernel_ms_per_step": {"scan": scan_ms / args.steps, "count": count_ms / args.steps, "fold": fold_ms / args.steps, "final": final_ms / args.steps},
+            "kernel_ms_per_step": {"scan": scan_ms / args.steps, "count": count_ms / args.steps, "fold": fold_ms / args.steps, "final": final_ms / args.steps, "encode": encode_ms / args.steps},
             "clocks": clocks,
             "result_check": {"total_kmers": stats["total_kmers"], "unique_kmers": stats["unique_kmers"], "total_reads": stats["total_reads"]},
         }

@@ -61,7 +61,8 @@ typedef struct {
 /* Device timing of the passes run so far (CUDA events on the context's stream). */
 typedef struct {
     float scan_ms;    /* K1: line/record boundary scan (tile summaries + carry scan)        */
-    float count_ms;   /* K2+K3: 2-bit encode, rolling id, histogram, fused reductions        */
+    float encode_ms;  /* K2: tokenise + 2-bit encode into the packed letter stream           */
+    float count_ms;   /* K3: rolling id + histogram (the dominant kernel)                    */
     float fold_ms;    /* u32 -> u64 fold of the count table                                  */
     float final_ms;   /* record-length check, unique/nullomer reductions                     */
     float h2d_ms;     /* host -> device staging                                              */

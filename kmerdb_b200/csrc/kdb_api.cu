@@ -11,7 +11,8 @@
 
 #include "kdb_common.cuh"
 #include "kdb_scan.cuh"
-#include "kdb_count.cuh"
+#include "kdb_encode.cuh"
+#include "kdb_hist.cuh"
 #include "kdb_final.cuh"
 #include "kdb_synth.cuh"
 
@@ -24,7 +25,7 @@ struct kdb_ctx {
     bool fastq = false, canonical = false, skip_n = false, smem_hist = false;
     unsigned long long nbins = 0;
     cudaStream_t s_compute = nullptr, s_copy = nullptr;
-    cudaEvent_t ev[6] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
+    cudaEvent_t ev[8] = {nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr, nullptr};
     cudaEvent_t ev_job0 = nullptr, ev_job1 = nullptr;
     std::vector<cudaEvent_t> ev_copy;
     unsigned int* tab32 = nullptr;
@@ -39,6 +40,11 @@ struct kdb_ctx {
     size_t rec_cap = 0;
     uint8_t* feed_buf = nullptr;
     size_t feed_cap = 0;
+    uint32_t* packed = nullptr;                 // K2 output / K3 input, one region per tile of the pass
+    size_t packed_cap = 0;
+    k3_fn hist_kernel = nullptr;
+    size_t hist_dyn = 0;
+    int encode_grid = 0, hist_grid = 0;
     // host mirrors
     ScanCarry h_carry{};
     bool have_carry = false;
@@ -84,12 +90,12 @@ static int set_device(kdb_ctx* ctx, int device) {
 }
 
 template <typename K>
-static int occupancy_grid(K kernel, size_t dyn_smem, int* grid) {
+static int occupancy_grid(K kernel, int threads, size_t dyn_smem, int* grid) {
     kdb_ctx* ctx = nullptr;
     int per_sm = 0, sms = 0, dev = 0;
     CK(cudaGetDevice(&dev));
     CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev));
-    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, kThreads, dyn_smem));
+    CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kernel, threads, dyn_smem));
     *grid = std::max(1, per_sm) * sms;   // persistent CTAs: a whole number of CTAs per SM
     return KDB_OK;
 }
@@ -100,7 +106,7 @@ extern "C" void kdb_destroy(kdb_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaFree(ctx->tab32); cudaFree(ctx->tab64); cudaFree(ctx->acc); cudaFree(ctx->carry); cudaFree(ctx->carry_len);
-    cudaFree(ctx->tile_sum); /* tile_state lives inside the tile_sum allocation */ cudaFree(ctx->rec_len); cudaFree(ctx->feed_buf);
+    cudaFree(ctx->tile_sum); /* tile_state lives inside the tile_sum allocation */ cudaFree(ctx->rec_len); cudaFree(ctx->feed_buf); cudaFree(ctx->packed);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     for (auto& e : ctx->ev_copy) cudaEventDestroy(e);
     if (ctx->ev_job0) cudaEventDestroy(ctx->ev_job0);
@@ -160,17 +166,15 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
     if ((e = cudaMalloc(&ctx->acc, sizeof(Accum))) != cudaSuccess) return fail("cudaMalloc acc", e);
     if ((e = cudaMalloc(&ctx->carry, sizeof(ScanCarry))) != cudaSuccess) return fail("cudaMalloc carry", e);
     if ((e = cudaMalloc(&ctx->carry_len, 2 * sizeof(unsigned long long))) != cudaSuccess) return fail("cudaMalloc carry_len", e);
-    // launch geometry of the count kernel: persistent CTAs, a whole number per SM
+    // launch geometry: persistent CTAs, a whole number per SM
     int rc;
-    const size_t dyn = ctx->smem_hist ? ctx->nbins * sizeof(unsigned int) : 0;
-    if (ctx->smem_hist) {
-        auto kern = ctx->fastq ? k2_count<true, true> : k2_count<false, true>;
-        if ((e = cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)) != cudaSuccess) return fail("smem attr", e);
-        rc = occupancy_grid(kern, dyn, &ctx->count_grid);
-    } else {
-        auto kern = ctx->fastq ? k2_count<true, false> : k2_count<false, false>;
-        rc = occupancy_grid(kern, 0, &ctx->count_grid);
-    }
+    ctx->hist_kernel = k3_kernel(k, ctx->canonical);
+    ctx->hist_dyn = ctx->smem_hist ? ctx->nbins * sizeof(unsigned int) : 0;
+    if (ctx->hist_dyn > 48 * 1024 &&
+        (e = cudaFuncSetAttribute((const void*)ctx->hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->hist_dyn)) != cudaSuccess)
+        return fail("smem attr", e);
+    rc = occupancy_grid(ctx->hist_kernel, kHistThreads, ctx->hist_dyn, &ctx->hist_grid);
+    if (!rc) rc = ctx->fastq ? occupancy_grid(k2_encode<true>, kThreads, 0, &ctx->encode_grid) : occupancy_grid(k2_encode<false>, kThreads, 0, &ctx->encode_grid);
     if (rc) { kdb_destroy(ctx); return nullptr; }
     if (reset_state(ctx)) { g_last_error = ctx->err; kdb_destroy(ctx); return nullptr; }
     if ((e = cudaGetLastError()) != cudaSuccess) return fail("kdb_create", e);
@@ -256,21 +260,26 @@ static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, un
     if (ctx->have_carry)
         CK(cudaMemcpyAsync(ctx->rec_len, ctx->carry_len, per * sizeof(unsigned long long), cudaMemcpyDeviceToDevice, ctx->s_compute));
 
-    CountParams P{};
+    if (int rc = ensure(ctx, (void**)&ctx->packed, &ctx->packed_cap, (size_t)n_tiles * kPackStride, sizeof(uint32_t))) return rc;
+    EncodeParams P{};
     P.text = text; P.lo = lo; P.hi = hi; P.n = n; P.tiles = ctx->tile_state; P.n_tiles = n_tiles; P.k = ctx->k;
-    P.canonical = ctx->canonical; P.skip_n = ctx->skip_n; P.tab32 = ctx->tab32; P.rec_len = ctx->rec_len;
-    P.rec_first = rec_first; P.hdr_file_base = ctx->fq_rec_base; P.acc = ctx->acc;
-    const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->count_grid);
-    const size_t dyn = ctx->smem_hist ? ctx->nbins * sizeof(unsigned int) : 0;
+    P.skip_n = ctx->skip_n; P.packed = ctx->packed; P.rec_len = ctx->rec_len;
+    P.rec_first = rec_first; P.fq_rec_base = ctx->fq_rec_base; P.acc = ctx->acc;
     CK(cudaEventRecord(ctx->ev[2], ctx->s_compute));
-    if (ctx->fastq) {
-        if (ctx->smem_hist) k2_count<true, true><<<grid, kThreads, dyn, ctx->s_compute>>>(P);
-        else k2_count<true, false><<<grid, kThreads, 0, ctx->s_compute>>>(P);
-    } else {
-        if (ctx->smem_hist) k2_count<false, true><<<grid, kThreads, dyn, ctx->s_compute>>>(P);
-        else k2_count<false, false><<<grid, kThreads, 0, ctx->s_compute>>>(P);
+    {
+        const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->encode_grid);
+        if (ctx->fastq) k2_encode<true><<<grid, kThreads, 0, ctx->s_compute>>>(P);
+        else k2_encode<false><<<grid, kThreads, 0, ctx->s_compute>>>(P);
+        CK(cudaGetLastError());
     }
-    CK(cudaGetLastError());
+    CK(cudaEventRecord(ctx->ev[6], ctx->s_compute));
+    {
+        HistParams H{};
+        H.packed = ctx->packed; H.n_tiles = n_tiles; H.skip_n = ctx->skip_n; H.tab32 = ctx->tab32; H.acc = ctx->acc;
+        const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->hist_grid);
+        ctx->hist_kernel<<<grid, kHistThreads, ctx->hist_dyn, ctx->s_compute>>>(H);
+        CK(cudaGetLastError());
+    }
     CK(cudaEventRecord(ctx->ev[3], ctx->s_compute));
     const unsigned long long n_complete = n_entries - 1;
     if (n_complete) {
@@ -288,10 +297,11 @@ static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, un
     CK(cudaEventSynchronize(ctx->ev[4]));
     float ms = 0;
     CK(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1])); ctx->timing.scan_ms += ms;
-    CK(cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[3])); ctx->timing.count_ms += ms;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[6])); ctx->timing.encode_ms += ms;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[6], ctx->ev[3])); ctx->timing.count_ms += ms;
     CK(cudaEventElapsedTime(&ms, ctx->ev[3], ctx->ev[4])); ctx->timing.final_ms += ms;
     ctx->timing.count_launches++;
-    ctx->timing.total_launches += 3;
+    ctx->timing.total_launches += 4;
     ctx->bytes_since_fold += hi - lo;
     return KDB_OK;
 }

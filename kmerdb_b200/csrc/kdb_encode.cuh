@@ -1,0 +1,424 @@
+// K2 — tokenise + 2-bit encode (FASTA / FASTQ text -> packed letter stream), sm_100a.
+//
+// Replaces the tokenising half of kmer.shred (kmerdb/kmer.py:517-534: alphabet check, N / IUPAC
+// detection, window completeness) and the record bookkeeping of parse.parsefile
+// (kmerdb/parse.py:128-137: seq_lengths).  For every 16 KiB text tile it writes a packed region
+//   [0] n_letters  [1] halo codes  [2] halo N bits  [3] -
+//   codes : 2 bits / letter, 16 letters per u32, first letter in the top bits (kmer.py:44-49 codes)
+//   W     : 1 bit / letter — the window ENDING at this letter is complete (k letters of one record)
+//           and free of RYSWKMBDHV; in skip mode (replace_with_none) also free of N
+//   NN    : 1 bit / letter — the letter is N (only consumed in expansion mode)
+// so that the count kernel (K3) runs with uniform control flow on clean 2-bit data.
+#pragma once
+#include "kdb_common.cuh"
+#include "kdb_scan.cuh"
+
+namespace kdb {
+
+constexpr int kPackHdr = 4;
+constexpr int kPackCodes = kTile / 16;                 // 1024 words
+constexpr int kPackBits = kTile / 32;                  // 512 words (W) + 512 words (NN)
+constexpr int kPackStride = kPackHdr + kPackCodes + 2 * kPackBits;   // 2052 words per tile
+
+struct EncodeParams {
+    const uint8_t* text;
+    unsigned long long lo, hi, n;
+    const TileState* tiles;
+    unsigned int n_tiles;
+    int k, skip_n;
+    uint32_t* packed;                 // n_tiles * kPackStride words
+    unsigned long long* rec_len;
+    unsigned long long rec_first;
+    unsigned long long fq_rec_base;
+    Accum* acc;
+};
+
+// 0x80 in every byte of w that equals the byte replicated in pat4 (exact, no false positives).
+__device__ __forceinline__ uint32_t eqmask(uint32_t w, uint32_t pat4) {
+    const uint32_t x = w ^ pat4;
+    return ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x | 0x7F7F7F7Fu);
+}
+
+// Window-tracking state of one thread (no ids here: K3 builds them from the packed stream).
+struct Track {
+    uint32_t nmask, imask;   // bit j: the letter j positions back is N / RYSWKMBDHV (or illegal)
+    uint32_t have;           // letters of the current record so far, saturated at k
+};
+
+// Per-thread output accumulators: letters right-aligned, most recent letter in the low bits.
+struct Emit {
+    unsigned long long chi, clo;   // 2-bit codes
+    unsigned long long wacc, nacc; // W / NN bits
+    uint32_t n;
+};
+
+struct Tally {
+    unsigned int mono[4];
+    unsigned int nwin;       // complete windows holding N
+    unsigned int err;        // bit P_ALPHABET / bit P_IUPAC for the current record
+};
+
+__device__ __forceinline__ void emit1(Emit& e, uint32_t code, uint32_t wbit, uint32_t nbit) {
+    e.chi = (e.chi << 2) | (e.clo >> 62);
+    e.clo = (e.clo << 2) | code;
+    e.wacc = (e.wacc << 1) | wbit;
+    e.nacc = (e.nacc << 1) | nbit;
+    e.n++;
+}
+
+// One sequence letter of class cl (C_A..C_ILLEGAL) through the window tracker.
+template <bool EMIT>
+__device__ __forceinline__ void track_letter(Track& t, Emit& e, Tally& y, uint32_t cl, int k, uint32_t kmask, int skip_n) {
+    const uint32_t isn = cl == C_N ? 1u : 0u;
+    t.nmask = ((t.nmask << 1) | isn) & kmask;
+    t.imask = ((t.imask << 1) | (cl >= C_IUPAC ? 1u : 0u)) & kmask;
+    t.have = t.have < (uint32_t)k ? t.have + 1 : t.have;
+    if (!EMIT) return;
+    uint32_t wbit = 0;
+    if (cl <= C_T) y.mono[cl]++;
+    if (t.have >= (uint32_t)k) {
+        if (t.nmask) y.nwin++;
+        if (t.nmask && skip_n) wbit = 0;                                  // kmer.py:542-544
+        else if (t.imask) y.err |= 1u << P_IUPAC;                         // kmer.py:309
+        else wbit = 1;
+    }
+    emit1(e, cl <= C_T ? cl : 0u, wbit, isn);
+}
+
+// Classes of the up-to-(k-1) letters that precede byte `a` inside the same record, oldest first.
+template <bool FASTQ>
+__device__ __noinline__ int halo_classes(const uint8_t* text, unsigned long long a, int k, uint8_t* out) {
+    uint8_t cls[16];
+    int cnt = 0;
+    unsigned long long p = a;
+    while (cnt < k - 1 && p > 0) {
+        const uint8_t ch = text[p - 1];
+        if (ch == '\n') {
+            if (FASTQ) break;
+            unsigned long long s = p - 1;                       // start of the line this LF ends
+            while (s > 0 && text[s - 1] != '\n') s--;
+            if (text[s] == '>') break;                          // title line: the record starts after it
+            p--;
+            continue;
+        }
+        const uint8_t cl = c_class_lut[ch];
+        if (cl <= C_ILLEGAL) cls[cnt++] = cl;
+        p--;
+    }
+    for (int i = 0; i < cnt; i++) out[i] = cls[cnt - 1 - i];
+    return cnt;
+}
+
+}  // namespace kdb
+
+namespace kdb {
+
+// OR a left-aligned bit string (x[0] holds the first bits; nwords words) into the big-endian bit
+// array `dst` at bit offset `bitoff`.  Shared-memory atomics: neighbouring threads share words.
+template <int NW>
+__device__ __forceinline__ void or_bits(uint32_t* dst, uint32_t bitoff, const uint32_t (&x)[NW], uint32_t nbits) {
+    if (nbits == 0) return;
+    const uint32_t w0 = bitoff >> 5, b = bitoff & 31;
+    const uint32_t last = (bitoff + nbits - 1) >> 5;
+#pragma unroll
+    for (int q = 0; q <= NW; q++) {
+        if (w0 + q > last) break;
+        const uint32_t cur = q < NW ? x[q < NW ? q : 0] : 0u;
+        const uint32_t prv = q > 0 ? x[q > 0 ? q - 1 : 0] : 0u;
+        const uint32_t v = __funnelshift_r(cur, prv, b);     // (prv:cur) >> b, low word
+        if (v) atomicOr(dst + w0 + q, v);
+    }
+}
+
+template <bool FASTQ>
+__global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
+    __shared__ uint32_t s_text[(kChunk / 4) * (kThreads + 1)];   // transposed: word i of thread t at [i*(T+1)+t]
+    __shared__ uint32_t s_out[kPackCodes + 2 * kPackBits];
+    __shared__ uint8_t s_lut[256];
+    __shared__ LineAgg s_scan[kThreads / 32];
+    __shared__ uint32_t s_cnt[kThreads / 32];
+    __shared__ unsigned long long s_red[kThreads / 32][8];
+
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int k = P.k, skip_n = P.skip_n;
+    const uint32_t kmask = (1u << k) - 1u;
+    s_lut[tid] = c_class_lut[tid];
+
+    Tally Y;
+    Y.mono[0] = Y.mono[1] = Y.mono[2] = Y.mono[3] = 0; Y.nwin = 0; Y.err = 0;
+    unsigned long long letters_total = 0, err_key = ~0ull;
+    unsigned int layout = 0;
+
+    for (unsigned int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+        const unsigned long long tile0 = P.lo + (unsigned long long)tile * kTile;
+        __syncthreads();
+        // ---- stage the tile: coalesced 16-byte loads, transposed into shared memory ----------
+#pragma unroll
+        for (int r = 0; r < kChunk / 16; r++) {
+            const int q = tid + kThreads * r;
+            const unsigned long long g = tile0 + 16ull * q;
+            uint4 v = make_uint4(0, 0, 0, 0);
+            if (g + 16 <= P.hi) v = __ldcs(reinterpret_cast<const uint4*>(P.text + g));
+            else if (g < P.hi) {
+                uint32_t t4[4] = {0, 0, 0, 0};
+                for (int j = 0; j < (int)(P.hi - g); j++) t4[j >> 2] |= (uint32_t)P.text[g + j] << (8 * (j & 3));
+                v = make_uint4(t4[0], t4[1], t4[2], t4[3]);
+            }
+            const int owner = q >> 2, w0 = (q & 3) * 4;
+            s_text[(w0 + 0) * (kThreads + 1) + owner] = v.x;
+            s_text[(w0 + 1) * (kThreads + 1) + owner] = v.y;
+            s_text[(w0 + 2) * (kThreads + 1) + owner] = v.z;
+            s_text[(w0 + 3) * (kThreads + 1) + owner] = v.w;
+        }
+        for (int i = tid; i < kPackCodes + 2 * kPackBits; i += kThreads) s_out[i] = 0;
+        __syncthreads();
+
+        const unsigned long long a = tile0 + (unsigned long long)tid * kChunk;
+        const int lim = a >= P.hi ? 0 : (P.hi - a >= (unsigned long long)kChunk ? kChunk : (int)(P.hi - a));
+        uint8_t prev = '\n';
+        if (lim > 0 && a > 0) prev = tid > 0 ? (uint8_t)(s_text[(kChunk / 4 - 1) * (kThreads + 1) + tid - 1] >> 24) : P.text[a - 1];
+
+        // ---- line starts in my chunk (SWAR), CTA scan -> line / record index and kind at `a` ---
+        LineAgg g{0, 0, 0};
+        if (lim == kChunk) {
+            uint32_t nl_prev = prev == '\n' ? 0x80000000u : 0u;
+#pragma unroll
+            for (int i = 0; i < kChunk / 4; i++) {
+                const uint32_t wv = s_text[i * (kThreads + 1) + tid];
+                const uint32_t nl = eqmask(wv, 0x0A0A0A0Au);
+                const uint32_t lsm = (nl << 8) | (nl_prev >> 24);
+                if (lsm) {
+                    const uint32_t hm = lsm & eqmask(wv, 0x3E3E3E3Eu);
+                    g.ls += __popc(lsm);
+                    g.hdr += __popc(hm);
+                    g.last = (hm & (0x80000000u >> __clz(lsm))) ? 2u : 1u;
+                }
+                nl_prev = nl;
+            }
+        } else {
+            uint8_t pv = prev;
+            for (int j = 0; j < lim; j++) {
+                const uint8_t ch = (uint8_t)(s_text[(j >> 2) * (kThreads + 1) + tid] >> (8 * (j & 3)));
+                if (pv == '\n') { g.ls++; const unsigned int cl = ch == '>' ? 2u : 1u; g.hdr += cl >> 1; g.last = cl; }
+                pv = ch;
+            }
+        }
+        LineAgg total;
+        const LineAgg inc = block_scan_inclusive(g, s_scan, &total);
+        const TileState ts = P.tiles[tile];
+        const unsigned long long ls_before = ts.ls_base + (inc.ls - g.ls);
+        unsigned long long hdr_before = ts.hdr_base + (inc.hdr - g.hdr);
+        unsigned int last_before;
+        {
+            LineAgg e = shfl_up_agg(inc, 1);
+            if (lane == 0) e = warp ? s_scan[warp - 1] : LineAgg{0, 0, 0};
+            last_before = e.last ? e.last : ts.last;
+        }
+
+        Emit E; E.chi = E.clo = E.wacc = E.nacc = 0; E.n = 0;
+        if (lim > 0) {
+            unsigned long long line = ls_before;      // FASTQ: index of the next line start
+            uint32_t kind;
+            if (FASTQ) kind = ls_before ? (uint32_t)((ls_before - 1) & 3) : K_HEADER;
+            else kind = last_before == 2 ? K_HEADER : (hdr_before ? K_SEQ : K_IGNORE);
+            unsigned long long rec = FASTQ ? P.fq_rec_base + (ls_before ? (ls_before - 1) >> 2 : 0) : (hdr_before ? hdr_before - 1 : 0);
+            Track T; T.nmask = T.imask = T.have = 0;
+            bool need_halo;
+            if (FASTQ) need_halo = prev != '\n' && kind == 1;
+            else if (prev != '\n') need_halo = kind == K_SEQ;
+            else need_halo = hdr_before != 0 && (uint8_t)s_text[tid] != '>';
+            uint32_t halo_codes = 0, halo_nn = 0;
+            if (need_halo) {
+                uint8_t hc[16];
+                const int cnt = halo_classes<FASTQ>(P.text, a, k, hc);
+                Emit dummyE; Tally dummyY;
+                for (int i = 0; i < cnt; i++) {
+                    track_letter<false>(T, dummyE, dummyY, hc[i], k, kmask, skip_n);
+                    halo_codes = (halo_codes << 2) | (hc[i] <= C_T ? hc[i] : 0u);
+                    halo_nn = (halo_nn << 1) | (hc[i] == C_N ? 1u : 0u);
+                }
+            }
+            if (tid == 0) {
+                uint32_t* hdr = P.packed + (size_t)tile * kPackStride;
+                hdr[1] = halo_codes; hdr[2] = halo_nn; hdr[3] = 0;
+            }
+            unsigned long long len = 0, qlen = 0;
+            Y.err = 0;
+            uint32_t m_lo = 0, m_hi = 0, m_both = 0, n_fast = 0;
+
+            auto flush = [&]() {
+                if (len | qlen | Y.err) {
+                    const unsigned long long idx = rec - P.rec_first;
+                    if (FASTQ) { if (len) atomicAdd(P.rec_len + 2 * idx, len); if (qlen) atomicAdd(P.rec_len + 2 * idx + 1, qlen); }
+                    else if (len) atomicAdd(P.rec_len + idx, len);
+                    letters_total += len;
+                    if (Y.err) {
+                        const unsigned long long key = rec * 4 + ((Y.err & 1u) ? P_ALPHABET : P_IUPAC);
+                        err_key = key < err_key ? key : err_key;
+                    }
+                }
+                len = 0; qlen = 0; Y.err = 0;
+            };
+
+            for (int i = 0; i < kChunk / 4; i++) {
+                if (4 * i >= lim) break;
+                const uint32_t wv = s_text[i * (kThreads + 1) + tid];
+                if (4 * i + 4 <= lim && prev != '\n' && prev != '\r') {
+                    if (kind == 1) {                              // sequence line (K_SEQ == FASTQ kind 1)
+                        const uint32_t t = ((wv >> 1) ^ (wv >> 2)) & 0x03030303u;     // A0 C1 G2 T3
+                        const uint32_t s = t | (t >> 4);
+                        const uint32_t sel = (s & 0xFFu) | ((s >> 8) & 0xFF00u);
+                        if (__byte_perm(0x54474341u, 0u, sel) == wv) {              // all four are ACGT
+                            const uint32_t bad = T.nmask | T.imask;
+                            uint32_t w4;
+                            if (T.have + 1 >= (uint32_t)k && ((bad << 1) & kmask) == 0) w4 = 0xFu;
+                            else {
+                                w4 = 0;
+#pragma unroll
+                                for (int j = 0; j < 4; j++) {
+                                    const bool complete = T.have + j + 1 >= (uint32_t)k;
+                                    const uint32_t nm = (T.nmask << (j + 1)) & kmask, im = (T.imask << (j + 1)) & kmask;
+                                    uint32_t wb = 0;
+                                    if (complete) {
+                                        if (nm) Y.nwin++;
+                                        if (nm && skip_n) wb = 0;
+                                        else if (im) Y.err |= 1u << P_IUPAC;
+                                        else wb = 1;
+                                    }
+                                    w4 = (w4 << 1) | wb;
+                                }
+                            }
+                            T.nmask = (T.nmask << 4) & kmask; T.imask = (T.imask << 4) & kmask;
+                            T.have = T.have + 4 < (uint32_t)k ? T.have + 4 : (uint32_t)k;
+                            const uint32_t v = (t * 0x40100401u) >> 24;              // c0<<6 | c1<<4 | c2<<2 | c3
+                            E.chi = (E.chi << 8) | (E.clo >> 56);
+                            E.clo = (E.clo << 8) | v;
+                            E.wacc = (E.wacc << 4) | w4;
+                            E.nacc <<= 4;
+                            E.n += 4;
+                            len += 4;
+                            m_lo += t & 0x01010101u; m_hi += (t >> 1) & 0x01010101u; m_both += t & (t >> 1) & 0x01010101u;
+                            n_fast += 4;
+                            prev = (uint8_t)(wv >> 24);
+                            continue;
+                        }
+                    } else {
+                        const uint32_t special = eqmask(wv, 0x0A0A0A0Au) | eqmask(wv, 0x0D0D0D0Du) | (wv & 0x80808080u);
+                        if (!special) {
+                            if (FASTQ && kind == 3) {                // quality line: Bio.SeqIO accepts chr 33..126 only
+                                if (((wv - 0x21212121u) & ~wv & 0x80808080u) | eqmask(wv, 0x7F7F7F7Fu)) layout |= 1;
+                                qlen += 4;
+                            } else if (FASTQ && kind == 2) layout |= 1;   // "+title" repeats go to the host tokeniser
+                            prev = (uint8_t)(wv >> 24);
+                            continue;
+                        }
+                    }
+                }
+                // ---- byte-wise path: line feeds, line starts, N / IUPAC / other letters ----------
+#pragma unroll
+                for (int b = 0; b < 4; b++) {
+                    if (4 * i + b >= lim) break;
+                    const uint8_t ch = (uint8_t)(wv >> (8 * b));
+                    const bool at_ls = prev == '\n';
+                    if (at_ls) {
+                        if (FASTQ) {
+                            kind = (uint32_t)(line & 3);
+                            if (kind == 0) { flush(); rec = P.fq_rec_base + (line >> 2); T.have = 0; T.nmask = T.imask = 0; if (ch != '@') layout |= 1; }
+                            else if (kind == 2 && ch != '+') layout |= 1;
+                            line++;
+                        } else {
+                            if (ch == '>') { flush(); hdr_before++; rec = hdr_before - 1; kind = K_HEADER; T.have = 0; T.nmask = T.imask = 0; }
+                            else kind = hdr_before ? K_SEQ : K_IGNORE;
+                        }
+                    } else if (prev == '\r' && ch != '\n') layout |= 1;   // lone CR is a line break in text mode
+                    prev = ch;
+                    if (ch & 0x80) layout |= 1;                           // UTF-8 decoding is the host tokeniser's business
+                    if (kind == 1) {
+                        const uint8_t cl = s_lut[ch];
+                        if (cl <= C_ILLEGAL) { if (cl == C_ILLEGAL) Y.err |= 1u << P_ALPHABET; len++; track_letter<true>(T, E, Y, cl, k, kmask, skip_n); }
+                        else if (cl == C_WEIRD || (FASTQ && cl == C_SPACE)) layout |= 1;
+                    } else if (FASTQ && kind == 3) {
+                        const uint8_t cl = s_lut[ch];
+                        if (cl <= C_ILLEGAL) qlen++; else if (cl == C_SPACE || cl == C_WEIRD) layout |= 1;
+                    } else if (FASTQ && kind == 2) {
+                        if (!at_ls && ch != '\n' && ch != '\r') layout |= 1;
+                    }
+                }
+            }
+            flush();
+            if (a + lim == P.n && prev == '\r') layout |= 1;              // file ends in a lone CR
+            const uint32_t s_l = (m_lo * 0x01010101u) >> 24, s_h = (m_hi * 0x01010101u) >> 24, s_b = (m_both * 0x01010101u) >> 24;
+            Y.mono[3] += s_b; Y.mono[2] += s_h - s_b; Y.mono[1] += s_l - s_b; Y.mono[0] += n_fast - s_l - s_h + s_b;
+        }
+
+        // ---- exclusive prefix of the letter counts over the CTA -> where my letters go ---------
+        uint32_t incn = E.n;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t o = __shfl_up_sync(0xffffffffu, incn, d); if (lane >= d) incn += o; }
+        if (lane == 31) s_cnt[warp] = incn;
+        __syncthreads();
+        uint32_t woff = 0, tile_letters = 0;
+#pragma unroll
+        for (int wq = 0; wq < kThreads / 32; wq++) { const uint32_t c = s_cnt[wq]; if (wq < warp) woff += c; tile_letters += c; }
+        const uint32_t off = woff + incn - E.n;
+        if (E.n) {
+            // left-align the right-aligned accumulators, then OR them in at my letter offset
+            const uint32_t sh = 128 - 2 * E.n;                      // 0..126
+            uint32_t r[4] = {(uint32_t)(E.chi >> 32), (uint32_t)E.chi, (uint32_t)(E.clo >> 32), (uint32_t)E.clo};
+            if (sh & 64) { r[0] = r[2]; r[1] = r[3]; r[2] = 0; r[3] = 0; }
+            if (sh & 32) { r[0] = r[1]; r[1] = r[2]; r[2] = r[3]; r[3] = 0; }
+            const uint32_t c5 = sh & 31;
+            uint32_t x[4];
+            x[0] = __funnelshift_l(r[1], r[0], c5); x[1] = __funnelshift_l(r[2], r[1], c5);
+            x[2] = __funnelshift_l(r[3], r[2], c5); x[3] = r[3] << c5;
+            or_bits<4>(s_out, 2 * off, x, 2 * E.n);
+            const uint32_t sh1 = 64 - E.n;                          // 0..63
+            uint32_t y[2], z[2];
+            {
+                const unsigned long long wl = sh1 < 64 ? E.wacc << sh1 : 0ull, nl = sh1 < 64 ? E.nacc << sh1 : 0ull;
+                y[0] = (uint32_t)(wl >> 32); y[1] = (uint32_t)wl; z[0] = (uint32_t)(nl >> 32); z[1] = (uint32_t)nl;
+            }
+            or_bits<2>(s_out + kPackCodes, off, y, E.n);
+            or_bits<2>(s_out + kPackCodes + kPackBits, off, z, E.n);
+        }
+        __syncthreads();
+        // ---- write the packed region: only the words the letters of this tile occupy ------------
+        {
+            uint32_t* dst = P.packed + (size_t)tile * kPackStride;
+            if (tid == 0) dst[0] = tile_letters;
+            const uint32_t cw = (tile_letters + 15) >> 4, bw = (tile_letters + 31) >> 5;
+            for (uint32_t i = tid; i < cw; i += kThreads) dst[kPackHdr + i] = s_out[i];
+            for (uint32_t i = tid; i < bw; i += kThreads) {
+                dst[kPackHdr + kPackCodes + i] = s_out[kPackCodes + i];
+                dst[kPackHdr + kPackCodes + kPackBits + i] = s_out[kPackCodes + kPackBits + i];
+            }
+        }
+    }
+
+    // ---- CTA reduction of the fused scalars --------------------------------------------------------
+    unsigned long long v[8] = {0, letters_total, Y.mono[0], Y.mono[1], Y.mono[2], Y.mono[3], Y.nwin, 0};
+#pragma unroll
+    for (int i = 1; i < 7; i++)
+        for (int d = 16; d; d >>= 1) v[i] += __shfl_xor_sync(0xffffffffu, v[i], d);
+    for (int d = 16; d; d >>= 1) {
+        const unsigned long long o = __shfl_xor_sync(0xffffffffu, err_key, d);
+        err_key = o < err_key ? o : err_key;
+        layout |= __shfl_xor_sync(0xffffffffu, layout, d);
+    }
+    __syncthreads();
+    if (lane == 0) { for (int i = 1; i < 7; i++) s_red[warp][i] = v[i]; s_red[warp][7] = err_key; }
+    __syncthreads();
+    if (tid >= 1 && tid < 7) {
+        unsigned long long s = 0;
+        for (int wp = 0; wp < kThreads / 32; wp++) s += s_red[wp][tid];
+        unsigned long long* dst = tid == 1 ? &P.acc->sum_len : tid <= 5 ? &P.acc->mono[tid - 2] : &P.acc->n_windows_with_n;
+        if (s) atomicAdd(dst, s);
+    } else if (tid == 7) {
+        unsigned long long m = ~0ull;
+        for (int wp = 0; wp < kThreads / 32; wp++) m = s_red[wp][7] < m ? s_red[wp][7] : m;
+        if (m != ~0ull) atomicMin(&P.acc->err_key, m);
+    }
+    if (layout && lane == 0) atomicOr(&P.acc->layout_flag, 1u);
+}
+
+}  // namespace kdb
