@@ -130,6 +130,85 @@ __device__ __forceinline__ void or_bits(uint32_t* dst, uint32_t bitoff, const ui
     }
 }
 
+// 4-bit gather of the 0x80 byte flags of m (byte j -> bit j)
+__device__ __forceinline__ uint32_t nib(uint32_t m) { return (((m >> 7) * 0x00204081u) >> 21) & 0xFu; }
+__device__ __forceinline__ unsigned long long ones64(uint32_t n) { return n >= 64 ? ~0ull : ((1ull << n) - 1ull); }
+// x | x>>1 | ... | x>>(n-1)   (n >= 1)
+__device__ __forceinline__ unsigned long long smear_down(unsigned long long x, uint32_t n) {
+    uint32_t w = 1;
+    while (2 * w <= n) { x |= x >> w; w *= 2; }
+    if (n > w) x |= x >> (n - w);
+    return x;
+}
+
+// Everything the bit-parallel path knows about one 64-byte chunk (bit i <-> byte i).
+struct ChunkMasks {
+    unsigned long long lf;      // byte == LF
+    unsigned long long acgt;    // byte in ACGT
+    uint32_t x[4];              // 2-bit codes of all 64 bytes, byte 0 in the top bits of x[0] (garbage for non-letters, 0 for N)
+    uint32_t any_cr, any_hi;    // some byte is CR / >= 0x80
+};
+
+template <typename ByteWord>
+__device__ __forceinline__ ChunkMasks chunk_masks(ByteWord word) {
+    ChunkMasks M;
+    M.lf = 0; M.acgt = 0; M.any_cr = 0; M.any_hi = 0;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        uint32_t xc = 0, lf16 = 0, ok16 = 0;
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const uint32_t wv = word(4 * q + r);
+            const uint32_t t = ((wv >> 1) ^ (wv >> 2)) & 0x03030303u;              // A0 C1 G2 T3 (N -> 0)
+            const uint32_t s = t | (t >> 4);
+            const uint32_t sel = (s & 0xFFu) | ((s >> 8) & 0xFF00u);
+            const uint32_t d = __byte_perm(0x54474341u, 0u, sel) ^ wv;            // zero byte <=> ACGT
+            const uint32_t z = ~(((d & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | d | 0x7F7F7F7Fu);
+            ok16 |= nib(z) << (4 * r);
+            lf16 |= nib(eqmask(wv, 0x0A0A0A0Au)) << (4 * r);
+            xc = (xc << 8) | ((t * 0x40100401u) >> 24);
+            M.any_cr |= eqmask(wv, 0x0D0D0D0Du);
+            M.any_hi |= wv;
+        }
+        M.x[q] = xc;
+        M.lf |= (unsigned long long)lf16 << (16 * q);
+        M.acgt |= (unsigned long long)ok16 << (16 * q);
+    }
+    M.any_hi &= 0x80808080u;
+    return M;
+}
+
+// 64-bit byte-equality mask, computed only when needed (N letters, CR).
+template <typename ByteWord>
+__device__ __noinline__ unsigned long long lazy_eq_mask(ByteWord word, uint32_t pat4) {
+    unsigned long long m = 0;
+    for (int i = 0; i < kChunk / 4; i++) m |= (unsigned long long)nib(eqmask(word(i), pat4)) << (4 * i);
+    return m;
+}
+// FASTQ quality bytes outside chr 33..126 (Bio.SeqIO raises ValueError)
+template <typename ByteWord>
+__device__ __noinline__ unsigned long long lazy_qbad_mask(ByteWord word) {
+    unsigned long long m = 0;
+    for (int i = 0; i < kChunk / 4; i++) {
+        const uint32_t wv = word(i);
+        const uint32_t lo = ~(((wv & 0x7F7F7F7Fu) + 0x5F5F5F5Fu) | wv) & 0x80808080u;     // byte < 0x21 (and < 0x80)
+        m |= (unsigned long long)nib(lo | (wv & 0x80808080u) | eqmask(wv, 0x7F7F7F7Fu)) << (4 * i);
+    }
+    return m;
+}
+
+// bits [2*(s+len)-1 .. 2*s] counted from the top of the 128-bit code string x, right-aligned
+__device__ __forceinline__ void extract_codes(const uint32_t (&x)[4], uint32_t s, uint32_t len, unsigned long long* hi, unsigned long long* lo) {
+    unsigned long long h = ((unsigned long long)x[0] << 32) | x[1], l = ((unsigned long long)x[2] << 32) | x[3];
+    const uint32_t sh = 128 - 2 * (s + len);                 // right shift, 0..126
+    if (sh >= 64) { l = h >> (sh - 64); h = 0; }
+    else if (sh) { l = (l >> sh) | (h << (64 - sh)); h >>= sh; }
+    const uint32_t nb = 2 * len;                              // keep the low nb bits
+    if (nb < 64) { h = 0; l &= (1ull << nb) - 1ull; }
+    else if (nb < 128) h &= (1ull << (nb - 64)) - 1ull;
+    *hi = h; *lo = l;
+}
+
 template <bool FASTQ>
 __global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
     __shared__ uint32_t s_text[(kChunk / 4) * (kThreads + 1)];   // transposed: word i of thread t at [i*(T+1)+t]
@@ -148,6 +227,8 @@ __global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
     Y.mono[0] = Y.mono[1] = Y.mono[2] = Y.mono[3] = 0; Y.nwin = 0; Y.err = 0;
     unsigned long long letters_total = 0, err_key = ~0ull;
     unsigned int layout = 0;
+    auto word = [&](int i) -> uint32_t { return s_text[i * (kThreads + 1) + tid]; };
+    auto byte_at = [&](uint32_t p) -> uint8_t { return (uint8_t)(s_text[(p >> 2) * (kThreads + 1) + tid] >> (8 * (p & 3))); };
 
     for (unsigned int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
         const unsigned long long tile0 = P.lo + (unsigned long long)tile * kTile;
@@ -178,30 +259,17 @@ __global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
         uint8_t prev = '\n';
         if (lim > 0 && a > 0) prev = tid > 0 ? (uint8_t)(s_text[(kChunk / 4 - 1) * (kThreads + 1) + tid - 1] >> 24) : P.text[a - 1];
 
-        // ---- line starts in my chunk (SWAR), CTA scan -> line / record index and kind at `a` ---
+        // ---- phase A: bit masks of my chunk; phase B: line starts -> CTA scan ---------------------
+        const ChunkMasks M = chunk_masks(word);      // zero fill beyond lim is neither LF nor a letter
         LineAgg g{0, 0, 0};
-        if (lim == kChunk) {
-            uint32_t nl_prev = prev == '\n' ? 0x80000000u : 0u;
-#pragma unroll
-            for (int i = 0; i < kChunk / 4; i++) {
-                const uint32_t wv = s_text[i * (kThreads + 1) + tid];
-                const uint32_t nl = eqmask(wv, 0x0A0A0A0Au);
-                const uint32_t lsm = (nl << 8) | (nl_prev >> 24);
-                if (lsm) {
-                    const uint32_t hm = lsm & eqmask(wv, 0x3E3E3E3Eu);
-                    g.ls += __popc(lsm);
-                    g.hdr += __popc(hm);
-                    g.last = (hm & (0x80000000u >> __clz(lsm))) ? 2u : 1u;
-                }
-                nl_prev = nl;
-            }
-        } else {
-            uint8_t pv = prev;
-            for (int j = 0; j < lim; j++) {
-                const uint8_t ch = (uint8_t)(s_text[(j >> 2) * (kThreads + 1) + tid] >> (8 * (j & 3)));
-                if (pv == '\n') { g.ls++; const unsigned int cl = ch == '>' ? 2u : 1u; g.hdr += cl >> 1; g.last = cl; }
-                pv = ch;
-            }
+        if (lim > 0) {
+            unsigned long long lsm = ((M.lf << 1) | (prev == '\n' ? 1ull : 0ull)) & ones64((uint32_t)lim);
+            g.ls = __popcll(lsm);
+            if (!FASTQ && lsm) {
+                const uint32_t top = 63 - __clzll(lsm);
+                g.last = byte_at(top) == '>' ? 2u : 1u;
+                while (lsm) { const uint32_t p = __ffsll(lsm) - 1; lsm &= lsm - 1; g.hdr += byte_at(p) == '>' ? 1u : 0u; }
+            } else if (lsm) g.last = 1u;
         }
         LineAgg total;
         const LineAgg inc = block_scan_inclusive(g, s_scan, &total);
@@ -244,7 +312,6 @@ __global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
             }
             unsigned long long len = 0, qlen = 0;
             Y.err = 0;
-            uint32_t m_lo = 0, m_hi = 0, m_both = 0, n_fast = 0;
 
             auto flush = [&]() {
                 if (len | qlen | Y.err) {
@@ -259,80 +326,115 @@ __global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
                 }
                 len = 0; qlen = 0; Y.err = 0;
             };
-
-            for (int i = 0; i < kChunk / 4; i++) {
-                if (4 * i >= lim) break;
-                const uint32_t wv = s_text[i * (kThreads + 1) + tid];
-                if (4 * i + 4 <= lim && prev != '\n' && prev != '\r') {
-                    if (kind == 1) {                              // sequence line (K_SEQ == FASTQ kind 1)
-                        const uint32_t t = ((wv >> 1) ^ (wv >> 2)) & 0x03030303u;     // A0 C1 G2 T3
-                        const uint32_t s = t | (t >> 4);
-                        const uint32_t sel = (s & 0xFFu) | ((s >> 8) & 0xFF00u);
-                        if (__byte_perm(0x54474341u, 0u, sel) == wv) {              // all four are ACGT
-                            const uint32_t bad = T.nmask | T.imask;
-                            uint32_t w4;
-                            if (T.have + 1 >= (uint32_t)k && ((bad << 1) & kmask) == 0) w4 = 0xFu;
-                            else {
-                                w4 = 0;
-#pragma unroll
-                                for (int j = 0; j < 4; j++) {
-                                    const bool complete = T.have + j + 1 >= (uint32_t)k;
-                                    const uint32_t nm = (T.nmask << (j + 1)) & kmask, im = (T.imask << (j + 1)) & kmask;
-                                    uint32_t wb = 0;
-                                    if (complete) {
-                                        if (nm) Y.nwin++;
-                                        if (nm && skip_n) wb = 0;
-                                        else if (im) Y.err |= 1u << P_IUPAC;
-                                        else wb = 1;
-                                    }
-                                    w4 = (w4 << 1) | wb;
-                                }
-                            }
-                            T.nmask = (T.nmask << 4) & kmask; T.imask = (T.imask << 4) & kmask;
-                            T.have = T.have + 4 < (uint32_t)k ? T.have + 4 : (uint32_t)k;
-                            const uint32_t v = (t * 0x40100401u) >> 24;              // c0<<6 | c1<<4 | c2<<2 | c3
-                            E.chi = (E.chi << 8) | (E.clo >> 56);
-                            E.clo = (E.clo << 8) | v;
-                            E.wacc = (E.wacc << 4) | w4;
-                            E.nacc <<= 4;
-                            E.n += 4;
-                            len += 4;
-                            m_lo += t & 0x01010101u; m_hi += (t >> 1) & 0x01010101u; m_both += t & (t >> 1) & 0x01010101u;
-                            n_fast += 4;
-                            prev = (uint8_t)(wv >> 24);
-                            continue;
-                        }
-                    } else {
-                        const uint32_t special = eqmask(wv, 0x0A0A0A0Au) | eqmask(wv, 0x0D0D0D0Du) | (wv & 0x80808080u);
-                        if (!special) {
-                            if (FASTQ && kind == 3) {                // quality line: Bio.SeqIO accepts chr 33..126 only
-                                if (((wv - 0x21212121u) & ~wv & 0x80808080u) | eqmask(wv, 0x7F7F7F7Fu)) layout |= 1;
-                                qlen += 4;
-                            } else if (FASTQ && kind == 2) layout |= 1;   // "+title" repeats go to the host tokeniser
-                            prev = (uint8_t)(wv >> 24);
-                            continue;
-                        }
-                    }
+            // line-start bookkeeping shared by both paths; ch is the first byte of the line
+            auto begin_line = [&](uint8_t ch) {
+                if (FASTQ) {
+                    kind = (uint32_t)(line & 3);
+                    if (kind == 0) { flush(); rec = P.fq_rec_base + (line >> 2); T.have = 0; T.nmask = T.imask = 0; if (ch != '@') layout |= 1; }
+                    else if (kind == 2 && ch != '+') layout |= 1;
+                    line++;
+                } else {
+                    if (ch == '>') { flush(); hdr_before++; rec = hdr_before - 1; kind = K_HEADER; T.have = 0; T.nmask = T.imask = 0; }
+                    else kind = hdr_before ? K_SEQ : K_IGNORE;
                 }
-                // ---- byte-wise path: line feeds, line starts, N / IUPAC / other letters ----------
-#pragma unroll
-                for (int b = 0; b < 4; b++) {
-                    if (4 * i + b >= lim) break;
-                    const uint8_t ch = (uint8_t)(wv >> (8 * b));
-                    const bool at_ls = prev == '\n';
+            };
+
+            // ---- phase C: bit-parallel walk over the line segments of my chunk ------------------
+            uint32_t pos = 0;
+            bool slow = lim != kChunk || T.imask != 0;
+            if (M.any_hi) layout |= 1;                                  // UTF-8 decoding is the host tokeniser's business
+            const uint32_t have0 = T.have, nmask0 = T.nmask;
+            uint32_t have_run = T.have;                                 // letters of the current record so far (not saturated)
+            bool seen_rs = false, pending_rs = false;
+            unsigned long long rs_acc = 0;                              // record-start marks, accumulator orientation
+            unsigned long long nm = 0, crm = 0, qbad = 0;
+            bool have_nm = false, have_q = false;
+            if (!slow) {
+                if (M.any_cr) {
+                    crm = lazy_eq_mask(word, 0x0D0D0D0Du);
+                    if (crm & ~(M.lf >> 1) & ~(1ull << 63)) layout |= 1;   // CR not followed by LF: a line break in text mode
+                }
+                if (prev == '\r' && !(M.lf & 1ull)) layout |= 1;
+                unsigned long long m = M.lf;
+                bool at_ls = prev == '\n';
+                while (true) {
+                    const uint32_t e = m ? (uint32_t)__ffsll(m) - 1 : 64u;      // segment [pos, e), LF at e
                     if (at_ls) {
-                        if (FASTQ) {
-                            kind = (uint32_t)(line & 3);
-                            if (kind == 0) { flush(); rec = P.fq_rec_base + (line >> 2); T.have = 0; T.nmask = T.imask = 0; if (ch != '@') layout |= 1; }
-                            else if (kind == 2 && ch != '+') layout |= 1;
-                            line++;
-                        } else {
-                            if (ch == '>') { flush(); hdr_before++; rec = hdr_before - 1; kind = K_HEADER; T.have = 0; T.nmask = T.imask = 0; }
-                            else kind = hdr_before ? K_SEQ : K_IGNORE;
+                        const uint8_t ch = byte_at(pos);
+                        begin_line(ch);
+                        if (FASTQ ? kind == 0 : (ch == '>')) pending_rs = true;
+                        prev = 0;                                           // line start consumed (the byte-wise path must not redo it)
+                    }
+                    const unsigned long long seg = (ones64(e) & ~ones64(pos)) & ~crm;
+                    if (kind == 1) {                                        // sequence line
+                        const unsigned long long bad = seg & ~M.acgt;
+                        if (bad) {
+                            if (!have_nm) { nm = lazy_eq_mask(word, 0x4E4E4E4Eu); have_nm = true; }
+                            if (bad & ~nm) { slow = true; break; }          // IUPAC / lowercase / space / ...: byte-wise
                         }
-                    } else if (prev == '\r' && ch != '\n') layout |= 1;   // lone CR is a line break in text mode
+                        const uint32_t L = __popcll(seg);
+                        if (L) {
+                            unsigned long long h, l;
+                            extract_codes(M.x, pos, L, &h, &l);
+                            const unsigned long long nrun = have_nm ? (__brevll((nm >> pos) & ones64(L)) >> (64 - L)) : 0ull;
+                            if (L == 64) { E.chi = h; E.clo = l; E.nacc = nrun; rs_acc = 0; }
+                            else {
+                                if (2 * L >= 64) { E.chi = (E.clo << (2 * L - 64)) | h; E.clo = l; }      // 32 <= L < 64
+                                else { E.chi = (E.chi << (2 * L)) | (E.clo >> (64 - 2 * L)); E.clo = (E.clo << (2 * L)) | l; }
+                                E.nacc = (E.nacc << L) | nrun;
+                                rs_acc <<= L;
+                            }
+                            if (pending_rs) { rs_acc |= 1ull << (L - 1); pending_rs = false; seen_rs = true; have_run = 0; }
+                            have_run += L;
+                            E.n += L;
+                            len += L;
+                        }
+                    } else if (FASTQ && kind == 3) {
+                        if (!have_q) { qbad = lazy_qbad_mask(word); have_q = true; }
+                        if (seg & qbad) layout |= 1;
+                        qlen += __popcll(seg);
+                    } else if (FASTQ && kind == 2) {
+                        if (__popcll(seg) > (at_ls ? 1 : 0)) layout |= 1;  // "+title" repeats go to the host tokeniser
+                    }
+                    if (e >= 64) { prev = byte_at(63); break; }
+                    m &= m - 1;
+                    pos = e + 1;
+                    at_ls = true;
+                    prev = '\n';
+                    if (pos >= 64) break;
+                }
+            }
+            // ---- W bits of the letters appended so far (all ACGT / N) ---------------------------------
+            if (E.n) {
+                const uint32_t n = E.n;
+                unsigned long long incp = k > 1 ? smear_down(rs_acc, (uint32_t)k - 1) : 0ull;
+                if (have0 + 1 < (uint32_t)k) { const uint32_t c = min(n, (uint32_t)k - 1 - have0); incp |= ones64(c) << (n - c); }
+                unsigned long long nsm = smear_down(E.nacc, (uint32_t)k);
+                if (nmask0) { const uint32_t c2 = min(n, (uint32_t)k - 1 - (uint32_t)(__ffs(nmask0) - 1)); nsm |= ones64(c2) << (n - c2); }
+                const unsigned long long complete = ones64(n) & ~incp;
+                Y.nwin += __popcll(complete & nsm);
+                E.wacc = skip_n ? complete & ~nsm : complete;
+                const unsigned long long o5 = 0x5555555555555555ull;
+                const uint32_t lo = __popcll(E.clo & o5) + __popcll(E.chi & o5), hi = __popcll(E.clo & (o5 << 1)) + __popcll(E.chi & (o5 << 1));
+                const uint32_t both = __popcll(E.clo & (E.clo >> 1) & o5) + __popcll(E.chi & (E.chi >> 1) & o5);
+                Y.mono[3] += both; Y.mono[2] += hi - both; Y.mono[1] += lo - both; Y.mono[0] += n - lo - hi + both - __popcll(E.nacc);
+            }
+            if (slow) {
+                // ---- byte-wise path from `pos`: anything the masks do not describe ------------------
+                if (pos > 0 || E.n) {
+                    T.have = have_run < (uint32_t)k ? have_run : (uint32_t)k;
+                    const unsigned long long n64 = E.nacc | (seen_rs || E.n >= 32 ? 0ull : ((unsigned long long)nmask0 << E.n));
+                    T.nmask = (uint32_t)n64 & kmask & (uint32_t)ones64(T.have);
+                    T.imask = 0;
+                    if (pending_rs) { T.have = 0; T.nmask = 0; }
+                }
+                for (uint32_t j = pos; j < (uint32_t)lim; j++) {
+                    const uint8_t ch = byte_at(j);
+                    const bool at_ls = prev == '\n';
+                    if (at_ls) begin_line(ch);
+                    else if (prev == '\r' && ch != '\n') layout |= 1;
                     prev = ch;
-                    if (ch & 0x80) layout |= 1;                           // UTF-8 decoding is the host tokeniser's business
+                    if (ch & 0x80) layout |= 1;
                     if (kind == 1) {
                         const uint8_t cl = s_lut[ch];
                         if (cl <= C_ILLEGAL) { if (cl == C_ILLEGAL) Y.err |= 1u << P_ALPHABET; len++; track_letter<true>(T, E, Y, cl, k, kmask, skip_n); }
@@ -347,8 +449,6 @@ __global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
             }
             flush();
             if (a + lim == P.n && prev == '\r') layout |= 1;              // file ends in a lone CR
-            const uint32_t s_l = (m_lo * 0x01010101u) >> 24, s_h = (m_hi * 0x01010101u) >> 24, s_b = (m_both * 0x01010101u) >> 24;
-            Y.mono[3] += s_b; Y.mono[2] += s_h - s_b; Y.mono[1] += s_l - s_b; Y.mono[0] += n_fast - s_l - s_h + s_b;
         }
 
         // ---- exclusive prefix of the letter counts over the CTA -> where my letters go ---------
