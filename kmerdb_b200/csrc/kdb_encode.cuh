@@ -209,13 +209,85 @@ __device__ __forceinline__ void extract_codes(const uint32_t (&x)[4], uint32_t s
     *hi = h; *lo = l;
 }
 
+// What a chunk hands to the chunks after it: the last (up to 15) letters of the record that is open
+// at its end.  Associative, so the start state of every thread is one CTA scan away.
+struct TailAgg {
+    uint32_t codes;    // 2-bit codes, most recent letter in the low bits
+    uint32_t ni;       // N flags (low 16) and RYSWKMBDHV/illegal flags (high 16), most recent letter at bit 0
+    uint32_t meta;     // letters held (0..15) | reset << 8 (a record started inside the span)
+    uint32_t letters;  // all letters emitted by the span (for the output offsets)
+};
+__device__ __forceinline__ TailAgg tail_combine(const TailAgg a, const TailAgg b) {
+    TailAgg r;
+    r.letters = a.letters + b.letters;
+    if (b.meta >> 8) { r.codes = b.codes; r.ni = b.ni; r.meta = b.meta; return r; }
+    const uint32_t bc = b.meta & 0xFF, ac = a.meta & 0xFF;
+    const uint32_t tot = ac + bc < 15 ? ac + bc : 15;
+    r.codes = ((a.codes << (2 * bc)) | b.codes) & 0x3FFFFFFFu;
+    const uint32_t an = a.ni & 0xFFFF, ai = a.ni >> 16, bn = b.ni & 0xFFFF, bi = b.ni >> 16;
+    r.ni = (((an << bc) | bn) & 0x7FFFu) | ((((ai << bc) | bi) & 0x7FFFu) << 16);
+    r.meta = tot | (a.meta & 0x100);
+    return r;
+}
+__device__ __forceinline__ TailAgg tail_shfl_up(const TailAgg v, int d) {
+    TailAgg r;
+    r.codes = __shfl_up_sync(0xffffffffu, v.codes, d); r.ni = __shfl_up_sync(0xffffffffu, v.ni, d);
+    r.meta = __shfl_up_sync(0xffffffffu, v.meta, d); r.letters = __shfl_up_sync(0xffffffffu, v.letters, d);
+    return r;
+}
+// Exclusive scan over the CTA; *total receives the CTA aggregate.  sm: kThreads/32 entries.
+__device__ __forceinline__ TailAgg tail_scan_exclusive(TailAgg v, TailAgg* sm, TailAgg* total) {
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const TailAgg ident{0, 0, 0, 0};
+#pragma unroll
+    for (int d = 1; d < 32; d <<= 1) { const TailAgg o = tail_shfl_up(v, d); if (lane >= d) v = tail_combine(o, v); }
+    if (lane == 31) sm[warp] = v;
+    __syncthreads();
+    TailAgg pre = ident;
+    for (int w = 0; w < warp; w++) pre = tail_combine(pre, sm[w]);
+    TailAgg tot = pre;
+    for (int w = warp; w < kThreads / 32; w++) tot = tail_combine(tot, sm[w]);
+    *total = tot;
+    TailAgg e = tail_shfl_up(v, 1);
+    if (lane == 0) e = ident;
+    return tail_combine(pre, e);
+}
+
+// W bits of the E.n letters gathered by the bit-parallel path (all ACGT or N), given the state the
+// record was in when the chunk began.  Returns true when a window must raise KeyError (kmer.py:309).
+__device__ __forceinline__ bool finalize_w(Emit& E, Tally& Y, unsigned long long rs_acc, uint32_t have0, uint32_t nmask0, uint32_t imask0, int k, int skip_n) {
+    const uint32_t n = E.n;
+    nmask0 &= (1u << (k - 1)) - 1u; imask0 &= (1u << (k - 1)) - 1u;     // only the k-1 letters before the chunk matter
+    unsigned long long incp = k > 1 ? smear_down(rs_acc, (uint32_t)k - 1) : 0ull;
+    if (have0 + 1 < (uint32_t)k) { const uint32_t c = min(n, (uint32_t)k - 1 - have0); incp |= ones64(c) << (n - c); }
+    unsigned long long nsm = smear_down(E.nacc, (uint32_t)k);
+    if (nmask0) { const uint32_t c2 = min(n, (uint32_t)k - 1 - (uint32_t)(__ffs(nmask0) - 1)); nsm |= ones64(c2) << (n - c2); }
+    const unsigned long long complete = ones64(n) & ~incp;
+    Y.nwin += __popcll(complete & nsm);
+    unsigned long long w = skip_n ? complete & ~nsm : complete;
+    bool raise = false;
+    if (imask0) {                         // a RYSWKMBDHV letter sits in the k-1 letters before the chunk
+        const uint32_t c3 = min(n, (uint32_t)k - 1 - (uint32_t)(__ffs(imask0) - 1));
+        const unsigned long long aff = (ones64(c3) << (n - c3)) & w;
+        raise = aff != 0;
+        w &= ~aff;
+    }
+    E.wacc = w;
+    const unsigned long long o5 = 0x5555555555555555ull;
+    const uint32_t lo = __popcll(E.clo & o5) + __popcll(E.chi & o5), hi = __popcll(E.clo & (o5 << 1)) + __popcll(E.chi & (o5 << 1));
+    const uint32_t both = __popcll(E.clo & (E.clo >> 1) & o5) + __popcll(E.chi & (E.chi >> 1) & o5);
+    Y.mono[3] += both; Y.mono[2] += hi - both; Y.mono[1] += lo - both; Y.mono[0] += n - lo - hi + both - __popcll(E.nacc);
+    return raise;
+}
+
 template <bool FASTQ>
 __global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
     __shared__ uint32_t s_text[(kChunk / 4) * (kThreads + 1)];   // transposed: word i of thread t at [i*(T+1)+t]
     __shared__ uint32_t s_out[kPackCodes + 2 * kPackBits];
     __shared__ uint8_t s_lut[256];
     __shared__ LineAgg s_scan[kThreads / 32];
-    __shared__ uint32_t s_cnt[kThreads / 32];
+    __shared__ TailAgg s_tail[kThreads / 32];
+    __shared__ TailAgg s_seed;
     __shared__ unsigned long long s_red[kThreads / 32][8];
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -284,6 +356,9 @@ __global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
         }
 
         Emit E; E.chi = E.clo = E.wacc = E.nacc = 0; E.n = 0;
+        unsigned long long rs_acc = 0, rec0 = 0;        // record-start marks (accumulator orientation); record open at `a`
+        bool finalized = true;                          // W bits still to be derived after the tail scan?
+        TailAgg tail{0, 0, 0, 0}, seed{0, 0, 0x100, 0};
         if (lim > 0) {
             unsigned long long line = ls_before;      // FASTQ: index of the next line start
             uint32_t kind;
@@ -296,7 +371,14 @@ __global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
             else if (prev != '\n') need_halo = kind == K_SEQ;
             else need_halo = hdr_before != 0 && (uint8_t)s_text[tid] != '>';
             uint32_t halo_codes = 0, halo_nn = 0;
-            if (need_halo) {
+            bool walked = false;
+            rec0 = rec;
+            // k-1 letters before my chunk, read back from the text: only the first thread of a tile, ragged
+            // tail chunks and chunks that fall to the byte-wise path need it; everyone else gets the same
+            // state from the CTA scan of the chunk tails below
+            auto walk = [&]() {
+                walked = true;
+                if (!need_halo) return;
                 uint8_t hc[16];
                 const int cnt = halo_classes<FASTQ>(P.text, a, k, hc);
                 Emit dummyE; Tally dummyY;
@@ -305,10 +387,12 @@ __global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
                     halo_codes = (halo_codes << 2) | (hc[i] <= C_T ? hc[i] : 0u);
                     halo_nn = (halo_nn << 1) | (hc[i] == C_N ? 1u : 0u);
                 }
-            }
+            };
+            if (tid == 0 || lim != kChunk) walk();
             if (tid == 0) {
                 uint32_t* hdr = P.packed + (size_t)tile * kPackStride;
                 hdr[1] = halo_codes; hdr[2] = halo_nn; hdr[3] = 0;
+                seed.codes = halo_codes; seed.ni = T.nmask | (T.imask << 16); seed.meta = T.have | 0x100; seed.letters = 0;
             }
             unsigned long long len = 0, qlen = 0;
             Y.err = 0;
@@ -327,7 +411,9 @@ __global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
                 len = 0; qlen = 0; Y.err = 0;
             };
             // line-start bookkeeping shared by both paths; ch is the first byte of the line
+            bool rs_in_chunk = false;
             auto begin_line = [&](uint8_t ch) {
+                if (FASTQ ? (line & 3) == 0 : ch == '>') rs_in_chunk = true;
                 if (FASTQ) {
                     kind = (uint32_t)(line & 3);
                     if (kind == 0) { flush(); rec = P.fq_rec_base + (line >> 2); T.have = 0; T.nmask = T.imask = 0; if (ch != '@') layout |= 1; }
@@ -341,12 +427,10 @@ __global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
 
             // ---- phase C: bit-parallel walk over the line segments of my chunk ------------------
             uint32_t pos = 0;
-            bool slow = lim != kChunk || T.imask != 0;
+            bool slow = lim != kChunk;
             if (M.any_hi) layout |= 1;                                  // UTF-8 decoding is the host tokeniser's business
-            const uint32_t have0 = T.have, nmask0 = T.nmask;
-            uint32_t have_run = T.have;                                 // letters of the current record so far (not saturated)
+            uint32_t have_run = 0;                                      // letters gathered since the last record start in the chunk
             bool seen_rs = false, pending_rs = false;
-            unsigned long long rs_acc = 0;                              // record-start marks, accumulator orientation
             unsigned long long nm = 0, crm = 0, qbad = 0;
             bool have_nm = false, have_q = false;
             if (!slow) {
@@ -404,29 +488,18 @@ __global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
                     if (pos >= 64) break;
                 }
             }
-            // ---- W bits of the letters appended so far (all ACGT / N) ---------------------------------
-            if (E.n) {
-                const uint32_t n = E.n;
-                unsigned long long incp = k > 1 ? smear_down(rs_acc, (uint32_t)k - 1) : 0ull;
-                if (have0 + 1 < (uint32_t)k) { const uint32_t c = min(n, (uint32_t)k - 1 - have0); incp |= ones64(c) << (n - c); }
-                unsigned long long nsm = smear_down(E.nacc, (uint32_t)k);
-                if (nmask0) { const uint32_t c2 = min(n, (uint32_t)k - 1 - (uint32_t)(__ffs(nmask0) - 1)); nsm |= ones64(c2) << (n - c2); }
-                const unsigned long long complete = ones64(n) & ~incp;
-                Y.nwin += __popcll(complete & nsm);
-                E.wacc = skip_n ? complete & ~nsm : complete;
-                const unsigned long long o5 = 0x5555555555555555ull;
-                const uint32_t lo = __popcll(E.clo & o5) + __popcll(E.chi & o5), hi = __popcll(E.clo & (o5 << 1)) + __popcll(E.chi & (o5 << 1));
-                const uint32_t both = __popcll(E.clo & (E.clo >> 1) & o5) + __popcll(E.chi & (E.chi >> 1) & o5);
-                Y.mono[3] += both; Y.mono[2] += hi - both; Y.mono[1] += lo - both; Y.mono[0] += n - lo - hi + both - __popcll(E.nacc);
-            }
             if (slow) {
                 // ---- byte-wise path from `pos`: anything the masks do not describe ------------------
-                if (pos > 0 || E.n) {
-                    T.have = have_run < (uint32_t)k ? have_run : (uint32_t)k;
-                    const unsigned long long n64 = E.nacc | (seen_rs || E.n >= 32 ? 0ull : ((unsigned long long)nmask0 << E.n));
-                    T.nmask = (uint32_t)n64 & kmask & (uint32_t)ones64(T.have);
-                    T.imask = 0;
-                    if (pending_rs) { T.have = 0; T.nmask = 0; }
+                if (!walked) walk();
+                const uint32_t have0 = T.have, nmask0 = T.nmask, imask0 = T.imask;
+                if (E.n && finalize_w(E, Y, rs_acc, have0, nmask0, imask0, k, skip_n)) { const unsigned long long key = rec0 * 4 + P_IUPAC; err_key = key < err_key ? key : err_key; }
+                if (pos > 0 || E.n) {                                   // window state after the gathered letters
+                    const bool carry = !seen_rs && !pending_rs && E.n < 32;
+                    const uint32_t hv = seen_rs ? have_run : have0 + E.n;
+                    T.have = hv < (uint32_t)k ? hv : (uint32_t)k;
+                    T.nmask = (uint32_t)(E.nacc | (carry ? ((unsigned long long)nmask0 << E.n) : 0ull)) & kmask & (uint32_t)ones64(T.have);
+                    T.imask = (uint32_t)(carry ? ((unsigned long long)imask0 << E.n) : 0ull) & kmask & (uint32_t)ones64(T.have);
+                    if (pending_rs) { T.have = 0; T.nmask = T.imask = 0; }
                 }
                 for (uint32_t j = pos; j < (uint32_t)lim; j++) {
                     const uint8_t ch = byte_at(j);
@@ -447,20 +520,30 @@ __global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
                     }
                 }
             }
+            // ---- what the chunks after me need to know about the record open at my end ------------
+            {
+                const uint32_t since = slow ? T.have : (pending_rs ? 0u : have_run);
+                const uint32_t cnt = min(15u, rs_in_chunk ? since : E.n);
+                tail.codes = (uint32_t)E.clo & (uint32_t)ones64(2 * cnt);
+                tail.ni = ((uint32_t)E.nacc & (uint32_t)ones64(cnt)) | (slow ? (T.imask & (uint32_t)ones64(cnt)) << 16 : 0u);
+                tail.meta = cnt | (rs_in_chunk ? 0x100u : 0u);
+                tail.letters = E.n;
+            }
+            finalized = slow || E.n == 0;
             flush();
             if (a + lim == P.n && prev == '\r') layout |= 1;              // file ends in a lone CR
         }
 
-        // ---- exclusive prefix of the letter counts over the CTA -> where my letters go ---------
-        uint32_t incn = E.n;
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { const uint32_t o = __shfl_up_sync(0xffffffffu, incn, d); if (lane >= d) incn += o; }
-        if (lane == 31) s_cnt[warp] = incn;
-        __syncthreads();
-        uint32_t woff = 0, tile_letters = 0;
-#pragma unroll
-        for (int wq = 0; wq < kThreads / 32; wq++) { const uint32_t c = s_cnt[wq]; if (wq < warp) woff += c; tile_letters += c; }
-        const uint32_t off = woff + incn - E.n;
+        // ---- CTA scan of the chunk tails: start state of every chunk + output offsets -------------
+        if (tid == 0) s_seed = seed;
+        TailAgg tile_total;
+        TailAgg start = tail_scan_exclusive(tail, s_tail, &tile_total);      // (syncs: s_seed is visible after it)
+        const uint32_t off = start.letters, tile_letters = tile_total.letters;
+        if (!finalized) {
+            if (tid) start = tail_combine(s_seed, start); else start = s_seed;
+            const uint32_t have0 = start.meta & 0xFF, nmask0 = start.ni & 0xFFFF, imask0 = start.ni >> 16;
+            if (finalize_w(E, Y, rs_acc, have0, nmask0, imask0, k, skip_n)) { const unsigned long long key = rec0 * 4 + P_IUPAC; err_key = key < err_key ? key : err_key; }
+        }
         if (E.n) {
             // left-align the right-aligned accumulators, then OR them in at my letter offset
             const uint32_t sh = 128 - 2 * E.n;                      // 0..126
