@@ -33,12 +33,6 @@ struct EncodeParams {
     Accum* acc;
 };
 
-// 0x80 in every byte of w that equals the byte replicated in pat4 (exact, no false positives).
-__device__ __forceinline__ uint32_t eqmask(uint32_t w, uint32_t pat4) {
-    const uint32_t x = w ^ pat4;
-    return ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x | 0x7F7F7F7Fu);
-}
-
 // Window-tracking state of one thread (no ids here: K3 builds them from the packed stream).
 struct Track {
     uint32_t nmask, imask;   // bit j: the letter j positions back is N / RYSWKMBDHV (or illegal)
@@ -281,7 +275,7 @@ __device__ __forceinline__ bool finalize_w(Emit& E, Tally& Y, unsigned long long
 }
 
 template <bool FASTQ>
-__global__ void __launch_bounds__(kThreads) k2_encode(const EncodeParams P) {
+__global__ void __launch_bounds__(kThreads, 3) k2_encode(const EncodeParams P) {
     __shared__ uint32_t s_text[(kChunk / 4) * (kThreads + 1)];   // transposed: word i of thread t at [i*(T+1)+t]
     __shared__ uint32_t s_out[kPackCodes + 2 * kPackBits];
     __shared__ uint8_t s_lut[256];

@@ -55,9 +55,32 @@ __device__ __forceinline__ LineAgg block_scan_inclusive(LineAgg v, LineAgg* sm, 
     return v;
 }
 
-// Line aggregate of the bytes [a, a+lim) given the byte before them.
+// 0x80 in every byte of w that equals the byte replicated in pat4 (exact, no false positives).
+__device__ __forceinline__ uint32_t eqmask(uint32_t w, uint32_t pat4) {
+    const uint32_t x = w ^ pat4;
+    return ~(((x & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | x | 0x7F7F7F7Fu);
+}
+
+// Line aggregate of the bytes [a, a+lim) given the byte before them.  Full chunks go four bytes at a
+// time (SWAR byte compares), ragged tails byte by byte.
 __device__ __forceinline__ LineAgg chunk_lines(const uint32_t (&w)[kChunk / 4], int lim, uint8_t prev) {
     LineAgg g{0, 0, 0};
+    if (lim == kChunk) {
+        uint32_t nl_prev = prev == '\n' ? 0x80000000u : 0u;
+#pragma unroll
+        for (int i = 0; i < kChunk / 4; i++) {
+            const uint32_t nl = eqmask(w[i], 0x0A0A0A0Au);
+            const uint32_t lsm = (nl << 8) | (nl_prev >> 24);          // 0x80 flags of the bytes that begin a line
+            if (lsm) {
+                const uint32_t hm = lsm & eqmask(w[i], 0x3E3E3E3Eu);   // ... with '>'
+                g.ls += __popc(lsm);
+                g.hdr += __popc(hm);
+                g.last = (hm & (0x80000000u >> __clz(lsm))) ? 2u : 1u;
+            }
+            nl_prev = nl;
+        }
+        return g;
+    }
 #pragma unroll
     for (int j = 0; j < kChunk; j++) {
         const uint8_t c = (uint8_t)(w[j >> 2] >> (8 * (j & 3)));
