@@ -63,6 +63,7 @@ typedef struct {
     float scan_ms;    /* K1: line/record boundary scan (tile summaries + carry scan)        */
     float encode_ms;  /* K2: tokenise + 2-bit encode into the packed letter stream           */
     float count_ms;   /* K3: rolling id + histogram (the dominant kernel)                    */
+    float partition_ms; /* part of count_ms: first kernel of K3 (the whole of it when k is not partitioned) */
     float fold_ms;    /* u32 -> u64 fold of the count table                                  */
     float final_ms;   /* record-length check, unique/nullomer reductions                     */
     float h2d_ms;     /* host -> device staging                                              */

@@ -30,7 +30,7 @@ class Stats(ctypes.Structure):
 
 
 class Timing(ctypes.Structure):
-    _fields_ = [("scan_ms", ctypes.c_float), ("encode_ms", ctypes.c_float), ("count_ms", ctypes.c_float), ("fold_ms", ctypes.c_float),
+    _fields_ = [("scan_ms", ctypes.c_float), ("encode_ms", ctypes.c_float), ("count_ms", ctypes.c_float), ("partition_ms", ctypes.c_float), ("fold_ms", ctypes.c_float),
                 ("final_ms", ctypes.c_float), ("h2d_ms", ctypes.c_float), ("job_ms", ctypes.c_float), ("count_launches", ctypes.c_uint64),
                 ("total_launches", ctypes.c_uint64), ("bytes_fed", ctypes.c_uint64)]
 

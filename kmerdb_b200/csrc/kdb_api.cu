@@ -13,6 +13,7 @@
 #include "kdb_scan.cuh"
 #include "kdb_encode.cuh"
 #include "kdb_hist.cuh"
+#include "kdb_part.cuh"
 #include "kdb_final.cuh"
 #include "kdb_synth.cuh"
 
@@ -45,6 +46,13 @@ struct kdb_ctx {
     k3_fn hist_kernel = nullptr;
     size_t hist_dyn = 0;
     int encode_grid = 0, hist_grid = 0;
+    // bucket-partitioned count (8 <= k <= 12)
+    bool partitioned = false;
+    k3p_fn part_kernel = nullptr;
+    int part_grid = 0, n_buckets = 0, parts = 1;
+    uint16_t* stream = nullptr;
+    size_t stream_cap = 0;
+    unsigned int* cursor = nullptr;             // n_buckets cursors + n_buckets fail bases
     // host mirrors
     ScanCarry h_carry{};
     bool have_carry = false;
@@ -106,7 +114,7 @@ extern "C" void kdb_destroy(kdb_ctx* ctx) {
     if (!ctx) return;
     cudaSetDevice(ctx->device);
     cudaFree(ctx->tab32); cudaFree(ctx->tab64); cudaFree(ctx->acc); cudaFree(ctx->carry); cudaFree(ctx->carry_len);
-    cudaFree(ctx->tile_sum); /* tile_state lives inside the tile_sum allocation */ cudaFree(ctx->rec_len); cudaFree(ctx->feed_buf); cudaFree(ctx->packed);
+    cudaFree(ctx->tile_sum); /* tile_state lives inside the tile_sum allocation */ cudaFree(ctx->rec_len); cudaFree(ctx->feed_buf); cudaFree(ctx->packed); cudaFree(ctx->stream); cudaFree(ctx->cursor);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     for (auto& e : ctx->ev_copy) cudaEventDestroy(e);
     if (ctx->ev_job0) cudaEventDestroy(ctx->ev_job0);
@@ -174,6 +182,17 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
         (e = cudaFuncSetAttribute((const void*)ctx->hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->hist_dyn)) != cudaSuccess)
         return fail("smem attr", e);
     rc = occupancy_grid(ctx->hist_kernel, kHistThreads, ctx->hist_dyn, &ctx->hist_grid);
+    ctx->partitioned = k >= 8 && k <= 12 && !getenv("KDB_NO_PARTITION");
+    if (ctx->partitioned) {
+        ctx->part_kernel = k3p_kernel(k, ctx->canonical);
+        ctx->n_buckets = 1 << (2 * k - kPayloadBits);
+        ctx->parts = std::max(1, (1776 + ctx->n_buckets - 1) / ctx->n_buckets);
+        const size_t dyn = k3p_smem_bytes(k);
+        if ((e = cudaFuncSetAttribute((const void*)ctx->part_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)) != cudaSuccess) return fail("smem attr", e);
+        if ((e = cudaFuncSetAttribute((const void*)k3p_count, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << kPayloadBits)) != cudaSuccess) return fail("smem attr", e);
+        if (!rc) rc = occupancy_grid(ctx->part_kernel, kPartThreads, dyn, &ctx->part_grid);
+        if ((e = cudaMalloc(&ctx->cursor, 2 * ctx->n_buckets * sizeof(unsigned int))) != cudaSuccess) return fail("cudaMalloc cursor", e);
+    }
     if (!rc) rc = ctx->fastq ? occupancy_grid(k2_encode<true>, kThreads, 0, &ctx->encode_grid) : occupancy_grid(k2_encode<false>, kThreads, 0, &ctx->encode_grid);
     if (rc) { kdb_destroy(ctx); return nullptr; }
     if (reset_state(ctx)) { g_last_error = ctx->err; kdb_destroy(ctx); return nullptr; }
@@ -273,12 +292,31 @@ static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, un
         CK(cudaGetLastError());
     }
     CK(cudaEventRecord(ctx->ev[6], ctx->s_compute));
-    {
+    if (ctx->partitioned) {
+        // every window ends on a text byte, so (hi - lo) bounds the entries of the pass; canonical ids of
+        // uniform sequence load the lowest bucket with 2x the average, hence the 3x head room
+        const unsigned long long avg = (hi - lo) / ctx->n_buckets + 1;
+        const unsigned int cap = (unsigned int)((3 * avg + 4096 + 7) & ~7ull);
+        if (int rc = ensure(ctx, (void**)&ctx->stream, &ctx->stream_cap, (size_t)cap * ctx->n_buckets, sizeof(uint16_t))) return rc;
+        CK(cudaMemsetAsync(ctx->cursor, 0, ctx->n_buckets * sizeof(unsigned int), ctx->s_compute));
+        CK(cudaMemsetAsync(ctx->cursor + ctx->n_buckets, 0xFF, ctx->n_buckets * sizeof(unsigned int), ctx->s_compute));
+        PartParams Q{};
+        Q.packed = ctx->packed; Q.n_tiles = n_tiles; Q.skip_n = ctx->skip_n; Q.tab32 = ctx->tab32; Q.stream = ctx->stream;
+        Q.cursor = ctx->cursor; Q.fail_base = ctx->cursor + ctx->n_buckets; Q.cap = cap; Q.acc = ctx->acc;
+        const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->part_grid);
+        ctx->part_kernel<<<grid, kPartThreads, k3p_smem_bytes(ctx->k), ctx->s_compute>>>(Q);
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(ctx->ev[7], ctx->s_compute));
+        k3p_count<<<ctx->n_buckets * ctx->parts, kBucketThreads, 4 << kPayloadBits, ctx->s_compute>>>(ctx->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->tab32);
+        CK(cudaGetLastError());
+        ctx->timing.total_launches++;
+    } else {
         HistParams H{};
         H.packed = ctx->packed; H.n_tiles = n_tiles; H.skip_n = ctx->skip_n; H.tab32 = ctx->tab32; H.acc = ctx->acc;
         const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->hist_grid);
         ctx->hist_kernel<<<grid, kHistThreads, ctx->hist_dyn, ctx->s_compute>>>(H);
         CK(cudaGetLastError());
+        CK(cudaEventRecord(ctx->ev[7], ctx->s_compute));
     }
     CK(cudaEventRecord(ctx->ev[3], ctx->s_compute));
     const unsigned long long n_complete = n_entries - 1;
@@ -299,6 +337,7 @@ static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, un
     CK(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1])); ctx->timing.scan_ms += ms;
     CK(cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[6])); ctx->timing.encode_ms += ms;
     CK(cudaEventElapsedTime(&ms, ctx->ev[6], ctx->ev[3])); ctx->timing.count_ms += ms;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[6], ctx->ev[7])); ctx->timing.partition_ms += ms;
     CK(cudaEventElapsedTime(&ms, ctx->ev[3], ctx->ev[4])); ctx->timing.final_ms += ms;
     ctx->timing.count_launches++;
     ctx->timing.total_launches += 4;

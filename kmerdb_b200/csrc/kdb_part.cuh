@@ -1,0 +1,228 @@
+// K3p — bucket-partitioned histogram for 8 <= k <= 12, sm_100a.
+//
+// Same job as K3 (kmerdb/kmer.py:297-317 ids, kmerdb/parse.py:133-136 counts) but built to get past
+// the scattered-RED ceiling (1.9e11 updates/s): shared-memory atomics are ~11x faster
+// than global ones, so ids are first partitioned by their high bits and each bucket is then counted
+// in a 64 KiB shared-memory table.
+//   k3p_partition : one CTA per packed tile.  ids -> tile-local counting sort by bucket
+//                   (rank = shared atomicAdd on a bucket histogram, CTA scan, scatter into a sorted
+//                   shared array), one global cursor bump per non-empty bucket, then the sorted
+//                   array leaves as 14-bit payloads in runs of consecutive 2-byte stores.
+//   k3p_count     : work item = (bucket, part): zero a 16384-bin shared table, stream the bucket's
+//                   payloads with 16-byte loads, ATOMS each, flush the table into tab32 with RED.
+// A bucket stream that would overflow its capacity falls back to direct REDs, so the result is exact
+// whatever the id distribution.
+#pragma once
+#include "kdb_common.cuh"
+#include "kdb_encode.cuh"
+#include "kdb_hist.cuh"
+
+namespace kdb {
+
+constexpr int kPayloadBits = 14;                       // 16384 bins x 4 B = 64 KiB shared table per bucket
+constexpr int kPartThreads = 512;                      // 512 threads x 32 letters = one full tile
+constexpr int kBucketThreads = 256;
+
+struct PartParams {
+    const uint32_t* packed;
+    unsigned int n_tiles;
+    int skip_n;
+    unsigned int* tab32;
+    uint16_t* stream;            // n_buckets * cap entries
+    unsigned int* cursor;        // n_buckets: entries claimed so far
+    unsigned int* fail_base;     // n_buckets: lowest base of a run that did not fit (0xFFFFFFFF = none)
+    unsigned int cap;            // entries per bucket (multiple of 8)
+    Accum* acc;
+};
+
+__device__ __forceinline__ uint32_t shr96_rt(uint32_t w2, uint32_t w1, uint32_t w0, int s) {
+    return s < 32 ? __funnelshift_r(w0, w1, s) : (s < 64 ? __funnelshift_r(w1, w2, s - 32) : (w2 >> (s - 64)));
+}
+
+template <int K, bool CANON>
+__global__ void __launch_bounds__(kPartThreads, 2) k3p_partition(const PartParams P) {
+    constexpr int NB = 1 << (2 * K - kPayloadBits);                 // buckets
+    constexpr int RBITS = 32 - 2 * K;                               // rank bits kept beside the id in one register
+    constexpr uint32_t RCAP = (1u << RBITS) - 1u;                   // ranks >= RCAP take the direct RED path
+    constexpr uint32_t mask = (1u << (2 * K)) - 1u;
+    constexpr int PER = (NB + kPartThreads - 1) / kPartThreads;     // buckets per thread in the scan
+    extern __shared__ uint32_t s_dyn_part[];                        // (kTile + 3 NB) words, see k3p_smem_bytes
+    uint32_t* const s_sorted = s_dyn_part;                          // ids of the tile, grouped by bucket
+    uint32_t* const s_hist = s_dyn_part + kTile;
+    uint32_t* const s_off = s_hist + NB;
+    uint32_t* const s_gbase = s_off + NB;
+    __shared__ uint32_t s_warp[kPartThreads / 32];
+    __shared__ unsigned long long s_red[kPartThreads / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned long long kmers = 0;
+
+    for (unsigned int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+        const uint32_t* reg = P.packed + (size_t)tile * kPackStride;
+        const uint32_t n = reg[0];
+        __syncthreads();
+        for (int i = tid; i < NB; i += kPartThreads) s_hist[i] = 0;
+        __syncthreads();
+
+        // ---- phase 1: ids of my 32 letters, rank inside their bucket ------------------------------
+        uint32_t item[32];                                           // id | rank << 2K, or ~0 = nothing to store
+        const bool active = (uint32_t)tid * 32 < n;
+        bool generic = false;
+        uint32_t cur0 = 0, cur1 = 0, prev = 0, wb = 0, nn_cur = 0, nn_prev = 0;
+        if (active) {
+            const uint32_t* codes = reg + kPackHdr;
+            cur0 = codes[2 * tid];
+            cur1 = (uint32_t)tid * 32 + 16 < n ? codes[2 * tid + 1] : 0u;
+            prev = tid ? codes[2 * tid - 1] : reg[1];
+            wb = reg[kPackHdr + kPackCodes + tid];
+            if (!P.skip_n) {
+                const uint32_t* nnw = reg + kPackHdr + kPackCodes + kPackBits;
+                nn_cur = nnw[tid];
+                nn_prev = tid ? nnw[tid - 1] : reg[2];
+                generic = (nn_cur | (nn_prev & ((1u << (K - 1)) - 1u))) != 0;
+            }
+        }
+        if (active && !generic) {
+            const uint32_t r2 = CANON ? rc_word(cur1) : 0u, r1 = CANON ? rc_word(cur0) : 0u, r0 = CANON ? rc_word(prev) : 0u;
+#pragma unroll
+            for (int e = 0; e < 32; e++) {
+                uint32_t it = 0xFFFFFFFFu;
+                if (wb & (0x80000000u >> e)) {
+                    uint32_t id = (e < 16 ? __funnelshift_r(cur0, prev, 30 - 2 * (e & 15)) : __funnelshift_r(cur1, cur0, 30 - 2 * (e & 15))) & mask;
+                    if (CANON) { const uint32_t rc = shr96_rt(r2, r1, r0, 34 + 2 * e - 2 * K) & mask; id = rc < id ? rc : id; }
+                    const uint32_t rank = atomicAdd(&s_hist[id >> kPayloadBits], 1u);
+                    if (rank < RCAP) it = id | (rank << (2 * K));
+                    else atomicAdd(P.tab32 + id, 1u);                // a bucket this crowded inside one tile: count directly
+                }
+                item[e] = it;
+            }
+            kmers += __popc(wb);
+        } else {
+#pragma unroll
+            for (int e = 0; e < 32; e++) item[e] = 0xFFFFFFFFu;
+            if (active) {                                            // expansion mode with N near by: generic path, direct REDs
+                const unsigned long long S0 = ((unsigned long long)prev << 32) | cur0, S1 = ((unsigned long long)cur0 << 32) | cur1;
+                const unsigned long long NS = ((unsigned long long)nn_prev << 32) | nn_cur;
+                for (int e = 0; e < 32; e++) {
+                    if (!(wb & (0x80000000u >> e))) continue;
+                    const uint32_t f = (uint32_t)((e < 16 ? S0 : S1) >> (30 - 2 * (e & 15))) & mask;
+                    const uint32_t nm = (uint32_t)(NS >> (31 - e)) & ((1u << K) - 1u);
+                    if (nm) kmers += expand_window(P.tab32, K, CANON, f, nm);
+                    else {
+                        uint32_t id = f;
+                        if (CANON) { const uint32_t r = revcomp32(f, K); id = r < f ? r : f; }
+                        atomicAdd(P.tab32 + id, 1u);
+                        kmers++;
+                    }
+                }
+            }
+        }
+        __syncthreads();
+
+        // ---- phase 2: exclusive scan of the bucket counts; claim room in the global streams ----------
+        uint32_t cnt[PER], sum = 0;
+#pragma unroll
+        for (int j = 0; j < PER; j++) {
+            const int b = tid * PER + j;
+            cnt[j] = b < NB ? min(s_hist[b], RCAP) : 0u;
+            sum += cnt[j];
+        }
+        uint32_t inc = sum;
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const uint32_t o = __shfl_up_sync(0xffffffffu, inc, d); if (lane >= d) inc += o; }
+        if (lane == 31) s_warp[warp] = inc;
+        __syncthreads();
+        uint32_t base = inc - sum, total = 0;
+#pragma unroll
+        for (int w = 0; w < kPartThreads / 32; w++) { const uint32_t c = s_warp[w]; if (w < warp) base += c; total += c; }
+#pragma unroll
+        for (int j = 0; j < PER; j++) {
+            const int b = tid * PER + j;
+            if (b < NB) {
+                s_off[b] = base;
+                base += cnt[j];
+                uint32_t gb = 0xFFFFFFFFu;
+                if (cnt[j]) {
+                    gb = atomicAdd(P.cursor + b, cnt[j]);
+                    if (gb + cnt[j] > P.cap) { atomicMin(P.fail_base + b, gb); gb = 0xFFFFFFFFu; }   // does not fit: RED path
+                }
+                s_gbase[b] = gb;
+            }
+        }
+        __syncthreads();
+
+        // ---- phase 3: scatter my ids to their sorted place ----------------------------------------------
+#pragma unroll
+        for (int e = 0; e < 32; e++) {
+            const uint32_t it = item[e];
+            if (it != 0xFFFFFFFFu) {
+                const uint32_t id = it & mask;
+                s_sorted[s_off[id >> kPayloadBits] + (it >> (2 * K))] = id;
+            }
+        }
+        __syncthreads();
+
+        // ---- phase 4: the sorted array leaves as payload runs, one entry per thread ----------------------
+        for (uint32_t j = tid; j < total; j += kPartThreads) {
+            const uint32_t id = s_sorted[j];
+            const uint32_t b = id >> kPayloadBits;
+            const uint32_t gb = s_gbase[b];
+            if (gb != 0xFFFFFFFFu) P.stream[(size_t)b * P.cap + gb + (j - s_off[b])] = (uint16_t)(id & ((1u << kPayloadBits) - 1u));
+            else atomicAdd(P.tab32 + id, 1u);
+        }
+    }
+    for (int d = 16; d; d >>= 1) kmers += __shfl_xor_sync(0xffffffffu, kmers, d);
+    __syncthreads();
+    if (lane == 0) s_red[warp] = kmers;
+    __syncthreads();
+    if (tid == 0) {
+        unsigned long long s = 0;
+        for (int w = 0; w < kPartThreads / 32; w++) s += s_red[w];
+        if (s) atomicAdd(&P.acc->total_kmers, s);
+    }
+}
+
+// One work item = (bucket, part).  grid = n_buckets * parts.
+__global__ void __launch_bounds__(kBucketThreads) k3p_count(const uint16_t* __restrict__ stream, const unsigned int* __restrict__ cursor,
+                                                            const unsigned int* __restrict__ fail_base, unsigned int cap, int parts,
+                                                            unsigned int* __restrict__ tab32) {
+    extern __shared__ unsigned int s_tab[];
+    const int tid = threadIdx.x;
+    const uint32_t b = blockIdx.x / parts, part = blockIdx.x % parts;
+    uint32_t end = cursor[b];
+    { const uint32_t fb = fail_base[b]; end = end < fb ? end : fb; end = end < cap ? end : cap; }
+    if (end == 0) return;
+    // split [0, end) into `parts` ranges on 8-entry boundaries
+    const uint32_t units = (end + 7) >> 3, per = (units + parts - 1) / parts;
+    const uint32_t u0 = part * per, u1 = min(units, u0 + per);
+    if (u0 >= u1) return;
+    for (int i = tid; i < (1 << kPayloadBits); i += kBucketThreads) s_tab[i] = 0;
+    __syncthreads();
+    const uint4* src = reinterpret_cast<const uint4*>(stream + (size_t)b * cap);
+    for (uint32_t u = u0 + tid; u < u1; u += kBucketThreads) {
+        const uint4 v = __ldcs(src + u);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        const uint32_t valid = min(8u, end - 8 * u);
+#pragma unroll
+        for (int q = 0; q < 8; q++)
+            if ((uint32_t)q < valid) atomicAdd(&s_tab[(w[q >> 1] >> (16 * (q & 1))) & 0x3FFFu], 1u);
+    }
+    __syncthreads();
+    unsigned int* dst = tab32 + ((size_t)b << kPayloadBits);
+    for (int i = tid; i < (1 << kPayloadBits); i += kBucketThreads) { const unsigned int x = s_tab[i]; if (x) atomicAdd(dst + i, x); }
+}
+
+__host__ inline size_t k3p_smem_bytes(int k) { return (size_t)(kTile + 3 * (1 << (2 * k - kPayloadBits))) * sizeof(uint32_t); }
+
+typedef void (*k3p_fn)(const PartParams);
+template <int K>
+__host__ inline k3p_fn k3p_select(bool canon) { return canon ? (k3p_fn)k3p_partition<K, true> : (k3p_fn)k3p_partition<K, false>; }
+__host__ inline k3p_fn k3p_kernel(int k, bool canon) {
+    switch (k) {
+        case 8: return k3p_select<8>(canon);   case 9: return k3p_select<9>(canon);
+        case 10: return k3p_select<10>(canon); case 11: return k3p_select<11>(canon);
+        case 12: return k3p_select<12>(canon);
+    }
+    return nullptr;
+}
+
+}  // namespace kdb
