@@ -38,7 +38,10 @@ enum {
 enum {
     KDB_CANONICAL = 1, /* id = min(fwd, revcomp)  kmerdb/kmer.py:310-317 (reference default)               */
     KDB_SKIP_N = 2,    /* replace_with_none=True  kmerdb/kmer.py:542-544; absent: 4^n expansion :550-565    */
-    KDB_FASTQ = 4      /* input is FASTQ (kmerdb/util.py:128-134), else FASTA (:120-126)                    */
+    KDB_FASTQ = 4,     /* input is FASTQ (kmerdb/util.py:128-134), else FASTA (:120-126)                    */
+    KDB_EDGE_KPLUS1 = 8 /* the context counts forward (k+1)-mers for kdb_edge_weights: k passed to kdb_create
+                           is k+1, records of exactly k letters are legal (kmerdb/kmer.py:461-463 with the
+                           graph's k), so the short-record raise uses k-1                                   */
 };
 
 typedef struct kdb_ctx kdb_ctx;
@@ -112,6 +115,33 @@ int kdb_timing(kdb_ctx* ctx, kdb_timing_t* out);
  * n k-mers of k letters each, packed back to back.  ids[i] = id, or UINT64_MAX for a k-mer
  * holding N (None), UINT64_MAX-1 for other non-ACGT letters (KeyError). */
 int kdb_kmer_to_id_batch(int device, const char* kmers, size_t n, int k, int canonical, uint64_t* ids);
+
+/* ---- graph (kmerdb/graph.py:108-354) ------------------------------------------------------------------
+ * kdb_edge_rows: the rows graph.make_edges_from_kmerids builds (graph.py:150-214) for records already
+ * tokenised by the host (graph.make_edges_from_fasta -> parse.parse_sequence_file, graph.py:261): `letters`
+ * holds the records back to back, record r = letters[rec_off[r] .. rec_off[r+1]).  Row e = (record index,
+ * pos i-1, id[i-1], pos i, id[i]); the two k-mer strings of the .kdbg row (kmerdb/__init__.py:1756-1762) are
+ * id_to_kmer of the ids and are rendered by the host writer.  *n_edges receives the edge count (pass cap = 0
+ * to size the outputs).  Returns KDB_OK or the class of the first raise: KDB_E_ALPHABET (NameError),
+ * KDB_E_SHORT (AttributeError), KDB_E_FORMAT (ValueError: N in graph mode), KDB_E_IUPAC (KeyError),
+ * KDB_E_EMPTY; *err_record = index of that record. */
+int kdb_edge_rows(int device, const uint8_t* letters, size_t n_letters, const uint64_t* rec_off, size_t n_recs, int k, int canonical,
+                  uint64_t* rec, uint64_t* pos1, uint64_t* id1, uint64_t* pos2, uint64_t* id2, size_t cap, size_t* n_edges,
+                  uint64_t* err_record);
+/* Aggregated edge list (legacy .kdbg columns n1, n2, weight): weight = multiplicity of the ordered
+ * id pair over the whole input = Counter of the kdb_edge_rows rows.  `ctx` is a finished context created with
+ * k+1, KDB_EDGE_KPLUS1 and without KDB_CANONICAL (it holds the forward (k+1)-mer histogram); `canonical`
+ * selects canonical ids for n1/n2.  Rows come in ascending order of their smallest (k+1)-mer. */
+int kdb_edge_weights(kdb_ctx* ctx, int canonical, uint64_t* n1, uint64_t* n2, uint64_t* weight, size_t cap, size_t* n);
+
+/* ---- minimizers (kmerdb/minimizer.py:31-85) -------------------------------------------------------------
+ * kdb_minimizers_compat: the reference's rows for one sequence: row i = (canonical id of seq[i:i+k] or
+ * UINT64_MAX for None, i % window == 0) for i < 4^k - k + 1 (minimizer.py:65); KDB_E_FORMAT = the
+ * ValueError("WHOOPS") it raises whenever len(seq) < 4^k (minimizer.py:76-78).
+ * kdb_minimizers: true windowed minimizers (extension): for every w consecutive k-mers the position and
+ * canonical id of the smallest id, leftmost on ties, consecutive repeats collapsed. */
+int kdb_minimizers_compat(int device, const uint8_t* seq, size_t len, int k, uint64_t window, uint64_t* ids, uint8_t* is_min, size_t cap, size_t* n_rows);
+int kdb_minimizers(int device, const uint8_t* seq, size_t len, int k, int w, uint64_t* pos, uint64_t* ids, size_t cap, size_t* n);
 
 /* Synthetic benchmark input: n_reads records of read_len i.i.d. uniform ACGT letters,
  * FASTA framing ">%09d\n" + letters + "\n" (or FASTQ framing), written straight into HBM.

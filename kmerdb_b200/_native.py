@@ -11,7 +11,7 @@ _HERE = os.path.dirname(os.path.abspath(__file__))
 SO_PATH = os.path.join(_HERE, "libkmerdb_b200.so")
 
 KDB_OK, KDB_E_ALPHABET, KDB_E_IUPAC, KDB_E_SHORT, KDB_E_FORMAT, KDB_E_EMPTY, KDB_E_ARG, KDB_E_LAYOUT, KDB_E_CUDA, KDB_E_STATE = range(10)
-KDB_CANONICAL, KDB_SKIP_N, KDB_FASTQ = 1, 2, 4
+KDB_CANONICAL, KDB_SKIP_N, KDB_FASTQ, KDB_EDGE_KPLUS1 = 1, 2, 4, 8
 
 EXPORTS = [
     "kdb_create", "kdb_destroy", "kdb_last_error", "kdb_feed_host", "kdb_feed_device", "kdb_finish", "kdb_stats",
@@ -19,6 +19,7 @@ EXPORTS = [
     "kdb_reset", "kdb_timing", "kdb_kmer_to_id_batch", "kdb_synth_record_bytes", "kdb_synth_device",
     "kdb_synth_host", "kdb_microbench_atomics", "kdb_dev_alloc", "kdb_dev_free", "kdb_host_alloc_pinned",
     "kdb_host_free_pinned", "kdb_memcpy_h2d", "kdb_memcpy_d2h",
+    "kdb_edge_rows", "kdb_edge_weights", "kdb_minimizers_compat", "kdb_minimizers",
 ]
 
 
@@ -71,6 +72,10 @@ def lib():
         ("kdb_dev_alloc", [ci, sz, ctypes.POINTER(vp)]), ("kdb_dev_free", [ci, vp]),
         ("kdb_host_alloc_pinned", [sz, ctypes.POINTER(vp)]), ("kdb_host_free_pinned", [vp]),
         ("kdb_memcpy_h2d", [ci, vp, vp, sz]), ("kdb_memcpy_d2h", [ci, vp, vp, sz]),
+        ("kdb_edge_rows", [ci, vp, sz, vp, sz, ci, ci, vp, vp, vp, vp, vp, sz, ctypes.POINTER(sz), ctypes.POINTER(u64)]),
+        ("kdb_edge_weights", [vp, ci, vp, vp, vp, sz, ctypes.POINTER(sz)]),
+        ("kdb_minimizers_compat", [ci, vp, sz, ci, u64, vp, vp, sz, ctypes.POINTER(sz)]),
+        ("kdb_minimizers", [ci, vp, sz, ci, ci, vp, vp, sz, ctypes.POINTER(sz)]),
     ]:
         fn = getattr(L, name)
         fn.restype = ci
@@ -147,8 +152,8 @@ class PinnedBuffer:
 class Profiler:
     """One device context (kdb_ctx): feed text fragments, finish, read counts and reductions."""
 
-    def __init__(self, k, canonical=True, skip_n=True, fastq=False, device=0):
-        flags = (KDB_CANONICAL if canonical else 0) | (KDB_SKIP_N if skip_n else 0) | (KDB_FASTQ if fastq else 0)
+    def __init__(self, k, canonical=True, skip_n=True, fastq=False, device=0, edge_kplus1=False):
+        flags = (KDB_CANONICAL if canonical else 0) | (KDB_SKIP_N if skip_n else 0) | (KDB_FASTQ if fastq else 0) | (KDB_EDGE_KPLUS1 if edge_kplus1 else 0)
         self.k, self.device = int(k), device
         self._ctx = lib().kdb_create(device, self.k, flags)
         if not self._ctx:
@@ -221,6 +226,16 @@ class Profiler:
         a = np.ascontiguousarray(arr, dtype=np.uint64)
         self._check(lib().kdb_import_partials(self._ctx, a.ctypes.data), "kdb_import_partials")
 
+    def edge_weights(self, canonical=True):
+        """(n1, n2, weight) uint64 arrays from a finished (k+1)-mer context (kdb_edge_weights)."""
+        n = ctypes.c_size_t()
+        self._check(lib().kdb_edge_weights(self._ctx, int(canonical), None, None, None, 0, ctypes.byref(n)), "kdb_edge_weights")
+        out = [np.empty(n.value, dtype=np.uint64) for _ in range(3)]
+        if n.value:
+            self._check(lib().kdb_edge_weights(self._ctx, int(canonical), out[0].ctypes.data, out[1].ctypes.data, out[2].ctypes.data,
+                                               n.value, ctypes.byref(n)), "kdb_edge_weights")
+        return out
+
     def close(self):
         if getattr(self, "_ctx", None):
             lib().kdb_destroy(self._ctx)
@@ -270,3 +285,51 @@ def kmer_to_id_batch(kmers, k, canonical=True, device=0):
     if lib().kdb_kmer_to_id_batch(device, kmers, n, k, int(canonical), out.ctypes.data):
         raise NativeError("kdb_kmer_to_id_batch: " + _err())
     return out
+
+
+def edge_rows(letters, rec_off, k, canonical=True, device=0):
+    """kdb_edge_rows: returns (status, err_record, rows) with rows = uint64[n_edges, 5] (rec, pos1, id1, pos2, id2)."""
+    a = np.ascontiguousarray(np.frombuffer(letters, dtype=np.uint8) if not isinstance(letters, np.ndarray) else letters, dtype=np.uint8)
+    off = np.ascontiguousarray(rec_off, dtype=np.uint64)
+    n_recs = off.size - 1
+    n, err = ctypes.c_size_t(), ctypes.c_uint64()
+    args = (device, a.ctypes.data if a.size else None, a.size, off.ctypes.data, n_recs, int(k), int(canonical))
+    rc = lib().kdb_edge_rows(*args, None, None, None, None, None, 0, ctypes.byref(n), ctypes.byref(err))
+    if rc in (KDB_E_CUDA, KDB_E_ARG):
+        raise NativeError("kdb_edge_rows failed (%d): %s" % (rc, _err()))
+    if rc:
+        return rc, int(err.value), None
+    cols = [np.empty(n.value, dtype=np.uint64) for _ in range(5)]
+    if n.value:
+        rc = lib().kdb_edge_rows(*args, *[c.ctypes.data for c in cols], n.value, ctypes.byref(n), ctypes.byref(err))
+        if rc:
+            raise NativeError("kdb_edge_rows failed (%d): %s" % (rc, _err()))
+    return 0, 0, np.stack(cols, axis=1) if n.value else np.zeros((0, 5), dtype=np.uint64)
+
+
+def minimizers_compat(seq, k, window, device=0):
+    """kdb_minimizers_compat: (status, ids uint64[L], is_min uint8[L])."""
+    a = np.frombuffer(seq if isinstance(seq, (bytes, bytearray)) else seq.encode("ascii"), dtype=np.uint8)
+    n = ctypes.c_size_t()
+    rc = lib().kdb_minimizers_compat(device, a.ctypes.data, a.size, int(k), int(window), None, None, 0, ctypes.byref(n))
+    if rc in (KDB_E_CUDA, KDB_E_ARG):
+        raise NativeError("kdb_minimizers_compat failed (%d): %s" % (rc, _err()))
+    if rc:
+        return rc, None, None
+    ids, flags = np.empty(n.value, dtype=np.uint64), np.empty(n.value, dtype=np.uint8)
+    rc = lib().kdb_minimizers_compat(device, a.ctypes.data, a.size, int(k), int(window), ids.ctypes.data, flags.ctypes.data, n.value, ctypes.byref(n))
+    if rc in (KDB_E_CUDA, KDB_E_ARG):
+        raise NativeError("kdb_minimizers_compat failed (%d): %s" % (rc, _err()))
+    return rc, ids, flags
+
+
+def minimizers(seq, k, w, device=0):
+    """kdb_minimizers: (status, positions uint64, ids uint64) of the true windowed minimizers."""
+    a = np.frombuffer(seq if isinstance(seq, (bytes, bytearray)) else seq.encode("ascii"), dtype=np.uint8)
+    cap = max(a.size, 1)
+    pos, ids = np.empty(cap, dtype=np.uint64), np.empty(cap, dtype=np.uint64)
+    n = ctypes.c_size_t()
+    rc = lib().kdb_minimizers(device, a.ctypes.data, a.size, int(k), int(w), pos.ctypes.data, ids.ctypes.data, cap, ctypes.byref(n))
+    if rc in (KDB_E_CUDA, KDB_E_ARG):
+        raise NativeError("kdb_minimizers failed (%d): %s" % (rc, _err()))
+    return rc, pos[:n.value], ids[:n.value]

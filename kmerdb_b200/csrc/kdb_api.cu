@@ -16,6 +16,7 @@
 #include "kdb_part.cuh"
 #include "kdb_final.cuh"
 #include "kdb_synth.cuh"
+#include "kdb_graph.cuh"
 
 using namespace kdb;
 
@@ -23,6 +24,7 @@ static thread_local std::string g_last_error;
 
 struct kdb_ctx {
     int device = 0, k = 0, flags = 0;
+    int short_k = 0;                            // records shorter than this raise (k, or k-1 for a KDB_EDGE_KPLUS1 context)
     bool fastq = false, canonical = false, skip_n = false, smem_hist = false;
     unsigned long long nbins = 0;
     cudaStream_t s_compute = nullptr, s_copy = nullptr;
@@ -153,6 +155,7 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
     ctx->device = device; ctx->k = k; ctx->flags = flags;
     ctx->fastq = flags & KDB_FASTQ; ctx->canonical = flags & KDB_CANONICAL; ctx->skip_n = flags & KDB_SKIP_N;
     ctx->smem_hist = k <= 7;
+    ctx->short_k = (flags & KDB_EDGE_KPLUS1) ? k - 1 : k;
     ctx->nbins = 1ull << (2 * k);
     auto fail = [&](const char* what, cudaError_t e) -> kdb_ctx* {
         g_last_error = std::string(what) + ": " + cudaGetErrorString(e);
@@ -231,8 +234,8 @@ static int fold_now(kdb_ctx* ctx) {
 // The last record seen so far is complete: run the record check on it alone.
 static int close_carry_record(kdb_ctx* ctx) {
     if (!ctx->have_carry) return KDB_OK;
-    if (ctx->fastq) k4_check_records<true><<<1, 32, 0, ctx->s_compute>>>(ctx->carry_len, 1, ctx->carry_rec_id, ctx->k, ctx->acc);
-    else k4_check_records<false><<<1, 32, 0, ctx->s_compute>>>(ctx->carry_len, 1, ctx->carry_rec_id, ctx->k, ctx->acc);
+    if (ctx->fastq) k4_check_records<true><<<1, 32, 0, ctx->s_compute>>>(ctx->carry_len, 1, ctx->carry_rec_id, ctx->short_k, ctx->acc);
+    else k4_check_records<false><<<1, 32, 0, ctx->s_compute>>>(ctx->carry_len, 1, ctx->carry_rec_id, ctx->short_k, ctx->acc);
     CK(cudaGetLastError());
     ctx->timing.total_launches++;
     CK(cudaMemsetAsync(ctx->carry_len, 0, 2 * sizeof(unsigned long long), ctx->s_compute));
@@ -322,8 +325,8 @@ static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, un
     const unsigned long long n_complete = n_entries - 1;
     if (n_complete) {
         const int g4 = (int)std::min<unsigned long long>((n_complete + 255) / 256, 148ull * 8);
-        if (ctx->fastq) k4_check_records<true><<<g4, 256, 0, ctx->s_compute>>>(ctx->rec_len, n_complete, rec_first, ctx->k, ctx->acc);
-        else k4_check_records<false><<<g4, 256, 0, ctx->s_compute>>>(ctx->rec_len, n_complete, rec_first, ctx->k, ctx->acc);
+        if (ctx->fastq) k4_check_records<true><<<g4, 256, 0, ctx->s_compute>>>(ctx->rec_len, n_complete, rec_first, ctx->short_k, ctx->acc);
+        else k4_check_records<false><<<g4, 256, 0, ctx->s_compute>>>(ctx->rec_len, n_complete, rec_first, ctx->short_k, ctx->acc);
         CK(cudaGetLastError());
         ctx->timing.total_launches++;
     }
@@ -692,5 +695,178 @@ extern "C" int kdb_memcpy_d2h(int device, void* dst, const void* src, size_t n) 
     kdb_ctx* ctx = nullptr;
     CK(cudaSetDevice(device));
     CK(cudaMemcpy(dst, src, n, cudaMemcpyDeviceToHost));
+    return KDB_OK;
+}
+
+// ---- K4: graph edge rows, aggregated edge weights, minimizers (kdb_graph.cuh) -----------------------------
+namespace {
+struct DevBuf {                      // scoped device allocation for the stateless K4 entry points
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t n) { return cudaMalloc(&p, n ? n : 16); }
+    template <typename T> T* as() { return static_cast<T*>(p); }
+};
+int upload_lut(kdb_ctx* ctx) {
+    uint8_t lut[256];
+    build_class_lut(lut);
+    CK(cudaMemcpyToSymbol(c_class_lut, lut, 256));
+    return KDB_OK;
+}
+// exclusive scan of per-block counts on the host (a few thousand entries), uploaded for the write kernel
+int scan_blocks(kdb_ctx* ctx, const unsigned int* d_cnt, unsigned int blocks, DevBuf& d_off, unsigned long long* total) {
+    std::vector<unsigned int> h_cnt(blocks);
+    CK(cudaMemcpy(h_cnt.data(), d_cnt, blocks * sizeof(unsigned int), cudaMemcpyDeviceToHost));
+    std::vector<unsigned long long> h_off(blocks);
+    unsigned long long t = 0;
+    for (unsigned int b = 0; b < blocks; b++) { h_off[b] = t; t += h_cnt[b]; }
+    *total = t;
+    CK(d_off.alloc(blocks * sizeof(unsigned long long)));
+    CK(cudaMemcpy(d_off.p, h_off.data(), blocks * sizeof(unsigned long long), cudaMemcpyHostToDevice));
+    return KDB_OK;
+}
+}  // namespace
+
+extern "C" int kdb_edge_rows(int device, const uint8_t* letters, size_t n_letters, const uint64_t* rec_off, size_t n_recs, int k, int canonical,
+                             uint64_t* rec, uint64_t* pos1, uint64_t* id1, uint64_t* pos2, uint64_t* id2, size_t cap, size_t* n_edges,
+                             uint64_t* err_record) {
+    kdb_ctx* ctx = nullptr;
+    if (!rec_off || !n_edges || k < 1 || k > 31 || (n_letters && !letters)) return KDB_E_ARG;
+    *n_edges = 0;
+    if (n_recs == 0) return KDB_E_EMPTY;
+    CK(cudaSetDevice(device));
+    if (int rc = upload_lut(ctx)) return rc;
+    std::vector<unsigned long long> edge_off(n_recs + 1);
+    edge_off[0] = 0;
+    for (size_t r = 0; r < n_recs; r++) {
+        const unsigned long long len = rec_off[r + 1] - rec_off[r];
+        edge_off[r + 1] = edge_off[r] + (len > (unsigned long long)k ? len - k : 0);    // len-k+1 windows -> len-k edges
+    }
+    const unsigned long long total = edge_off[n_recs];
+    DevBuf d_let, d_off, d_eoff, d_key, d_out;
+    CK(d_let.alloc(n_letters)); CK(d_off.alloc((n_recs + 1) * 8)); CK(d_eoff.alloc((n_recs + 1) * 8)); CK(d_key.alloc(8));
+    CK(cudaMemcpy(d_let.p, letters, n_letters, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_off.p, rec_off, (n_recs + 1) * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_eoff.p, edge_off.data(), (n_recs + 1) * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemset(d_key.p, 0xFF, 8));
+    const unsigned long long work = std::max<unsigned long long>(n_letters, n_recs);
+    k8_check_letters<<<(unsigned int)((work + 255) / 256), 256>>>(d_let.as<uint8_t>(), n_letters, d_off.as<unsigned long long>(), n_recs, k, d_key.as<unsigned long long>());
+    CK(cudaGetLastError());
+    unsigned long long key = 0;
+    CK(cudaMemcpy(&key, d_key.p, 8, cudaMemcpyDeviceToHost));
+    if (key != ~0ull) {
+        if (err_record) *err_record = key >> 36;
+        const unsigned int cls = (unsigned int)((key >> 34) & 3);
+        if (cls == G_ALPHABET) return KDB_E_ALPHABET;
+        if (cls == G_SHORT) return KDB_E_SHORT;
+        return (key & 1) ? KDB_E_IUPAC : KDB_E_FORMAT;              // N in graph mode: ValueError
+    }
+    *n_edges = (size_t)total;
+    const size_t m = std::min<size_t>(cap, (size_t)total);
+    if (total == 0 || m == 0) return KDB_OK;
+    if (m < total) { g_last_error = "kdb_edge_rows: output capacity smaller than the edge count"; return KDB_E_ARG; }
+    CK(d_out.alloc(5 * total * 8));
+    unsigned long long* o = d_out.as<unsigned long long>();
+    k8_edge_rows<<<(unsigned int)((total + 255) / 256), 256>>>(d_let.as<uint8_t>(), d_off.as<unsigned long long>(), d_eoff.as<unsigned long long>(), n_recs, total,
+                                                              k, canonical, o, o + total, o + 2 * total, o + 3 * total, o + 4 * total);
+    CK(cudaGetLastError());
+    uint64_t* dst[5] = {rec, pos1, id1, pos2, id2};
+    for (int i = 0; i < 5; i++) if (dst[i]) CK(cudaMemcpy(dst[i], o + (size_t)i * total, total * 8, cudaMemcpyDeviceToHost));
+    return KDB_OK;
+}
+
+extern "C" int kdb_edge_weights(kdb_ctx* ctx, int canonical, uint64_t* n1, uint64_t* n2, uint64_t* weight, size_t cap, size_t* n) {
+    if (!ctx || !n) return KDB_E_ARG;
+    if (!ctx->finished) { ctx->err = "kdb_edge_weights before kdb_finish"; return KDB_E_STATE; }
+    if (ctx->canonical || ctx->k < 2) { ctx->err = "kdb_edge_weights needs a context of forward (k+1)-mers: create it with k+1, KDB_EDGE_KPLUS1 and without KDB_CANONICAL"; return KDB_E_ARG; }
+    if (int rc = set_device(ctx, ctx->device)) return rc;
+    CK(cudaStreamSynchronize(ctx->s_compute));
+    const int k = ctx->k - 1;
+    const unsigned int blocks = (unsigned int)((ctx->nbins + kEdgeBlock - 1) / kEdgeBlock);
+    DevBuf d_cnt, d_off, d_out;
+    CK(d_cnt.alloc(blocks * sizeof(unsigned int)));
+    k7_edge_weight_count<<<blocks, 256>>>(ctx->tab64, ctx->nbins, k, canonical, d_cnt.as<unsigned int>());
+    CK(cudaGetLastError());
+    unsigned long long total = 0;
+    if (int rc = scan_blocks(ctx, d_cnt.as<unsigned int>(), blocks, d_off, &total)) return rc;
+    *n = (size_t)total;
+    ctx->timing.total_launches++;
+    const size_t m = std::min<size_t>(cap, (size_t)total);
+    if (!m || !n1 || !n2 || !weight) return KDB_OK;
+    CK(d_out.alloc(3 * m * 8));
+    unsigned long long* o = d_out.as<unsigned long long>();
+    k7_edge_weight_write<<<blocks, 256>>>(ctx->tab64, ctx->nbins, k, canonical, d_off.as<unsigned long long>(), o, o + m, o + 2 * m, m);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(n1, o, m * 8, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(n2, o + m, m * 8, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(weight, o + 2 * m, m * 8, cudaMemcpyDeviceToHost));
+    ctx->timing.total_launches++;
+    return KDB_OK;
+}
+
+// minimizer.select_lexicographical_minimizers (kmerdb/minimizer.py:31-85) for one sequence.
+extern "C" int kdb_minimizers_compat(int device, const uint8_t* seq, size_t len, int k, uint64_t window, uint64_t* ids, uint8_t* is_min,
+                                     size_t cap, size_t* n_rows) {
+    kdb_ctx* ctx = nullptr;
+    if (!seq || !n_rows || k < 1 || k > 31 || window == 0) return KDB_E_ARG;
+    *n_rows = 0;
+    if (len < (size_t)k) return KDB_E_FORMAT;                                   // minimizer.py:59-60
+    const unsigned long long L = (1ull << (2 * k)) - (unsigned long long)k + 1; // minimizer.py:65 (4^k - k + 1, not len - k + 1)
+    if (len < L + (unsigned long long)k - 1) return KDB_E_FORMAT;               // minimizer.py:76-78 ValueError("WHOOPS")
+    *n_rows = (size_t)L;
+    if (!ids || !is_min || cap < L) return cap < L && (ids || is_min) ? KDB_E_ARG : KDB_OK;
+    CK(cudaSetDevice(device));
+    if (int rc = upload_lut(ctx)) return rc;
+    DevBuf d_seq, d_ids, d_min, d_bad;
+    CK(d_seq.alloc(L + k)); CK(d_ids.alloc(L * 8)); CK(d_min.alloc(L)); CK(d_bad.alloc(4));
+    CK(cudaMemcpy(d_seq.p, seq, L + k - 1, cudaMemcpyHostToDevice));
+    CK(cudaMemset(d_bad.p, 0, 4));
+    k8_min_compat<<<(unsigned int)((L + 255) / 256), 256>>>(d_seq.as<uint8_t>(), L, k, window, d_ids.as<unsigned long long>(), d_min.as<uint8_t>(), d_bad.as<unsigned int>());
+    CK(cudaGetLastError());
+    unsigned int bad = 0;
+    CK(cudaMemcpy(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost));
+    if (bad & 1u) return KDB_E_ALPHABET;
+    if (bad & 2u) return KDB_E_IUPAC;
+    CK(cudaMemcpy(ids, d_ids.p, L * 8, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(is_min, d_min.p, L, cudaMemcpyDeviceToHost));
+    return KDB_OK;
+}
+
+// True windowed minimizers (extension): for every run of w consecutive k-mers the position of
+// the smallest canonical id (leftmost on ties); consecutive windows choosing the same k-mer give one row.
+extern "C" int kdb_minimizers(int device, const uint8_t* seq, size_t len, int k, int w, uint64_t* pos, uint64_t* ids, size_t cap, size_t* n) {
+    kdb_ctx* ctx = nullptr;
+    if (!seq || !n || k < 1 || k > 31 || w < 1) return KDB_E_ARG;
+    *n = 0;
+    if (len < (size_t)k + (size_t)w - 1) return KDB_OK;
+    CK(cudaSetDevice(device));
+    if (int rc = upload_lut(ctx)) return rc;
+    const unsigned long long n_win = len - k + 1, n_out = n_win - w + 1;
+    DevBuf d_seq, d_ids, d_best, d_bad, d_cnt, d_off, d_out;
+    CK(d_seq.alloc(len)); CK(d_ids.alloc(n_win * 8)); CK(d_best.alloc(n_out * 8)); CK(d_bad.alloc(4));
+    CK(cudaMemcpy(d_seq.p, seq, len, cudaMemcpyHostToDevice));
+    CK(cudaMemset(d_bad.p, 0, 4));
+    k8_window_ids<<<(unsigned int)((n_win + 255) / 256), 256>>>(d_seq.as<uint8_t>(), n_win, k, d_ids.as<unsigned long long>(), d_bad.as<unsigned int>());
+    CK(cudaGetLastError());
+    unsigned int bad = 0;
+    CK(cudaMemcpy(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost));
+    if (bad & 1u) return KDB_E_ALPHABET;
+    if (bad & 2u) return KDB_E_IUPAC;
+    k8_min_window<<<(unsigned int)((n_out + 255) / 256), 256>>>(d_ids.as<unsigned long long>(), n_win, w, n_out, d_best.as<unsigned long long>());
+    CK(cudaGetLastError());
+    const unsigned int blocks = (unsigned int)((n_out + kEdgeBlock - 1) / kEdgeBlock);
+    CK(d_cnt.alloc(blocks * sizeof(unsigned int)));
+    k8_min_count<<<blocks, 256>>>(d_best.as<unsigned long long>(), n_out, d_cnt.as<unsigned int>());
+    CK(cudaGetLastError());
+    unsigned long long total = 0;
+    if (int rc = scan_blocks(ctx, d_cnt.as<unsigned int>(), blocks, d_off, &total)) return rc;
+    *n = (size_t)total;
+    const size_t m = std::min<size_t>(cap, (size_t)total);
+    if (!m || !pos || !ids) return KDB_OK;
+    CK(d_out.alloc(2 * m * 8));
+    unsigned long long* o = d_out.as<unsigned long long>();
+    k8_min_write<<<blocks, 256>>>(d_best.as<unsigned long long>(), d_ids.as<unsigned long long>(), n_out, d_off.as<unsigned long long>(), o, o + m, m);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(pos, o, m * 8, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(ids, o + m, m * 8, cudaMemcpyDeviceToHost));
     return KDB_OK;
 }

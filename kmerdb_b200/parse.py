@@ -230,6 +230,30 @@ def profile_bytes(data, k, fmt="fasta", replace_with_none=True, canonicalize=Tru
         return Profile(k, p.counts(), st, p.nullomers() if want_nullomers else None, p.timing())
 
 
+def profile_multik(data, min_k, max_k, fmt="fasta", replace_with_none=True, canonicalize=True, device=0, want_nullomers=False):
+    """`--minK/--maxK` sweep (kmerdb/__init__.py:1846-1855) over text held in host memory: the text crosses
+    PCIe once and stays in HBM; every k runs the device kernels on the same resident buffer.
+    Returns {k: Profile}."""
+    a = data if isinstance(data, np.ndarray) else np.frombuffer(data, dtype=np.uint8)
+    out = {}
+    buf = _native.DeviceBuffer(a.size + 16, device=device)
+    try:
+        buf.upload(a)
+        for k in range(min_k, max_k + 1):
+            with _native.Profiler(k, canonical=canonicalize, skip_n=replace_with_none, fastq=(fmt == "fastq"), device=device) as p:
+                p.feed_device(buf.ptr, a.size)
+                status = p.finish()
+                if status == _native.KDB_E_LAYOUT:       # host tokeniser decides (same for every k)
+                    out[k] = profile_bytes(data, k, fmt, replace_with_none, canonicalize, device, want_nullomers)
+                    continue
+                st = p.stats()
+                _raise_for_status(status, st)
+                out[k] = Profile(k, p.counts(), st, p.nullomers() if want_nullomers else None, p.timing())
+    finally:
+        buf.free()
+    return out
+
+
 def parsefile(filepath, k, replace_with_none=True, canonicalize=True, device=0, with_mononucleotides=False):
     """Drop-in for kmerdb.parse.parsefile (kmerdb/parse.py:90-163).
 
