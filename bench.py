@@ -129,17 +129,11 @@ def workload_config(args, n_gpus):
             "parallelism": "reads sharded over %d GPU(s); partial 4^k tables sum-reduced to rank 0 with NCCL" % n_gpus if n_gpus > 1 else "1 GPU"}
 
 
-class CudaArray:
-    """Zero-copy view of a device allocation for torch (CUDA array interface)."""
-
-    def __init__(self, ptr, n, typestr="<i8"):
-        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
-
-
 def run_b200(args):
     import torch
     import torch.distributed as dist
     from kmerdb_b200 import _native
+    from kmerdb_b200 import distributed as kd
 
     rank = int(os.environ.get("RANK", "0"))
     world = int(os.environ.get("WORLD_SIZE", "1"))
@@ -160,8 +154,6 @@ def run_b200(args):
     dev_text = _native.DeviceBuffer(nbytes + 16, device=local)
     _native.synth_device(dev_text, n_reads, READ_LEN, seed=SEED, first_read=rank * n_reads)
     prof = _native.Profiler(k, canonical=True, skip_n=True, fastq=False, device=local)
-    tab_ptr = None
-    red_tensor = None
 
     def barrier():
         if world > 1:
@@ -169,33 +161,12 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     def reduce_to_rank0():
-        """NCCL sum-reduce of the 4^k uint64 partials (as int64: two's complement sums are the same bits)
-        and of the additive scalars; min/max go through their own reductions."""
-        nonlocal tab_ptr, red_tensor
+        """NCCL sum-reduce of the 4^k uint64 partials and of the scalar pack to rank 0, then the non-additive
+        reductions (unique, nullomers) are recomputed there (kmerdb_b200/distributed.py)."""
         if world == 1:
             return
-        if tab_ptr is None:
-            tab_ptr, nb = prof.device_table()
-            red_tensor = torch.as_tensor(CudaArray(tab_ptr, nb), device=torch.device("cuda", local))
-        dist.reduce(red_tensor, dst=0, op=dist.ReduceOp.SUM)
-        part = prof.export_partials().astype(np.int64)
-        sums = torch.from_numpy(part[:8].copy()).cuda(local)
-        mins = torch.from_numpy(part[[8, 10]].copy().view(np.uint64).astype(np.float64)).cuda(local)  # min_len, err_key (exact below 2^53; ~0 stays largest)
-        maxs = torch.from_numpy(part[[9, 11]].copy()).cuda(local)
-        dist.reduce(sums, dst=0, op=dist.ReduceOp.SUM)
-        dist.reduce(mins, dst=0, op=dist.ReduceOp.MIN)
-        dist.reduce(maxs, dst=0, op=dist.ReduceOp.MAX)
+        kd.reduce_profiler(prof, dist, torch.device("cuda", local), dst=0)
         torch.cuda.synchronize()
-        if rank == 0:
-            out = np.zeros(16, dtype=np.uint64)
-            out[:8] = sums.cpu().numpy().view(np.uint64)
-            mn = mins.cpu().numpy()
-            out[8] = np.uint64(mn[0]) if mn[0] < 2.0 ** 63 else np.uint64(2 ** 64 - 1)
-            out[10] = np.uint64(mn[1]) if mn[1] < 2.0 ** 63 else np.uint64(2 ** 64 - 1)
-            mx = maxs.cpu().numpy().view(np.uint64)
-            out[9], out[11] = mx[0], mx[1]
-            prof.import_partials(out)
-            prof.refinalize()
 
     def step_device():
         prof.reset()

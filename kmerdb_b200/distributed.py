@@ -1,0 +1,96 @@
+"""Multi-GPU plumbing of the profile path: one process per GPU, reads sharded across ranks,
+one sum-reduction of the 4^k table plus a 16-word scalar pack; unique/nullomers are recomputed after the sum.
+
+torch.distributed is plumbing only (NCCL on the GPU box, gloo in the CPU tests): the kernels never see it.
+The reference's counterpart is the cross-file sum of kmerdb/__init__.py:1888-1891 and the header statistics
+re-derived from the summed vector at :1901-1903."""
+import numpy as np
+
+# layout of the scalar pack (kdb_export_partials): additive words, then min / max words
+SUM_WORDS = slice(0, 8)      # reads, kmers, sum_len, mono[4], windows with N
+MIN_WORDS = (8, 10)          # min_len, err_key   (~0 = none)
+MAX_WORDS = (9, 11)          # max_len, layout flag
+_SIGN = np.uint64(1 << 63)
+
+
+def _ordered_i64(u):
+    """uint64 -> int64 with the unsigned order kept (flip the top bit), so MIN/MAX of int64 tensors are exact."""
+    return (np.asarray(u, dtype=np.uint64) ^ _SIGN).view(np.int64)
+
+
+def _unordered_u64(i):
+    return np.asarray(i, dtype=np.int64).view(np.uint64) ^ _SIGN
+
+
+def combine_partials(part16, dist, device, dst=0):
+    """Reduce the 16-word scalar packs of all ranks to `dst`.  Returns the combined pack on dst, None elsewhere.
+    Sums are exact in two's complement; min/max use an order-preserving map of uint64 into int64."""
+    import torch
+    p = np.asarray(part16, dtype=np.uint64)
+    sums = torch.from_numpy(p[SUM_WORDS].view(np.int64).copy()).to(device)
+    mins = torch.from_numpy(_ordered_i64(p[list(MIN_WORDS)]).copy()).to(device)
+    maxs = torch.from_numpy(_ordered_i64(p[list(MAX_WORDS)]).copy()).to(device)
+    dist.reduce(sums, dst=dst, op=dist.ReduceOp.SUM)
+    dist.reduce(mins, dst=dst, op=dist.ReduceOp.MIN)
+    dist.reduce(maxs, dst=dst, op=dist.ReduceOp.MAX)
+    if dist.get_rank() != dst:
+        return None
+    out = np.zeros(16, dtype=np.uint64)
+    out[SUM_WORDS] = sums.cpu().numpy().view(np.uint64)
+    out[list(MIN_WORDS)] = _unordered_u64(mins.cpu().numpy())
+    out[list(MAX_WORDS)] = _unordered_u64(maxs.cpu().numpy())
+    return out
+
+
+def reduce_table(table_i64, dist, dst=0):
+    """Sum-reduce the uint64[4^k] partial tables (viewed as int64: the sums are the same bits) to `dst`."""
+    dist.reduce(table_i64, dst=dst, op=dist.ReduceOp.SUM)
+
+
+def shard_bounds(data, fmt, world):
+    """Cut uncompressed FASTA/FASTQ text into `world` contiguous ranges at record boundaries.
+    Returns world+1 offsets.  FASTA: a record starts at '>' after a line feed.  FASTQ (4-line records, the only
+    layout the device tokeniser takes natively): a record starts at a line whose index is a multiple of 4,
+    so the cut is found by counting line feeds from the start of the text."""
+    a = data if isinstance(data, np.ndarray) else np.frombuffer(data, dtype=np.uint8)
+    n = a.size
+    cuts = [0]
+    if fmt == "fastq":
+        lf = np.flatnonzero(a == 10)
+        n_rec = (lf.size + (1 if n and a[-1] != 10 else 0)) // 4
+        for r in range(1, world):
+            rec = (n_rec * r) // world
+            cuts.append(int(lf[4 * rec - 1]) + 1 if rec > 0 else 0)
+    else:
+        for r in range(1, world):
+            t = (n * r) // world
+            t = max(t, cuts[-1])
+            win = a[t:]
+            hit = np.flatnonzero((win[1:] == ord(">")) & (win[:-1] == 10))
+            cuts.append(t + int(hit[0]) + 1 if hit.size else n)
+    cuts.append(n)
+    return cuts
+
+
+class CudaArray:
+    """Zero-copy view of a raw device allocation for torch (CUDA array interface)."""
+
+    def __init__(self, ptr, n, typestr="<i8"):
+        self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
+
+
+def reduce_profiler(prof, dist, device, dst=0, _cache={}):
+    """After prof.finish() on every rank: NCCL sum-reduce of the partial tables and scalars to `dst`, then
+    the non-additive reductions (unique, nullomers) are recomputed there (kdb_refinalize)."""
+    import torch
+    key = id(prof)
+    if key not in _cache:
+        ptr, nb = prof.device_table()
+        _cache.clear()
+        _cache[key] = torch.as_tensor(CudaArray(ptr, nb), device=device)
+    reduce_table(_cache[key], dist, dst)
+    out = combine_partials(prof.export_partials(), dist, device, dst)
+    if out is not None:
+        prof.import_partials(out)
+        return prof.refinalize()
+    return 0
