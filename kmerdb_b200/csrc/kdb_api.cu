@@ -3,6 +3,7 @@
 #include "../../include/kmerdb_b200.h"
 
 #include <algorithm>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -52,6 +53,7 @@ struct kdb_ctx {
     bool partitioned = false;
     k3p_fn part_kernel = nullptr;
     int part_grid = 0, n_buckets = 0, parts = 1;
+    int subs = 1;
     uint16_t* stream = nullptr;
     size_t stream_cap = 0;
     unsigned int* cursor = nullptr;             // n_buckets cursors + n_buckets fail bases
@@ -185,14 +187,15 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
         (e = cudaFuncSetAttribute((const void*)ctx->hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->hist_dyn)) != cudaSuccess)
         return fail("smem attr", e);
     rc = occupancy_grid(ctx->hist_kernel, kHistThreads, ctx->hist_dyn, &ctx->hist_grid);
-    ctx->partitioned = k >= 8 && k <= 12 && !getenv("KDB_NO_PARTITION");
+    ctx->partitioned = k >= 8 && k <= 14 && !getenv("KDB_NO_PARTITION");
     if (ctx->partitioned) {
         ctx->part_kernel = k3p_kernel(k, ctx->canonical);
-        ctx->n_buckets = 1 << (2 * k - kPayloadBits);
+        ctx->n_buckets = 1 << (2 * k - payload_bits(k));
+        ctx->subs = 1 << (payload_bits(k) - kTableBits);
         ctx->parts = std::max(1, (1776 + ctx->n_buckets - 1) / ctx->n_buckets);
         const size_t dyn = k3p_smem_bytes(k);
         if ((e = cudaFuncSetAttribute((const void*)ctx->part_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)) != cudaSuccess) return fail("smem attr", e);
-        if ((e = cudaFuncSetAttribute((const void*)k3p_count, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << kPayloadBits)) != cudaSuccess) return fail("smem attr", e);
+        if ((e = cudaFuncSetAttribute((const void*)k3p_count, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << kTableBits)) != cudaSuccess) return fail("smem attr", e);
         if (!rc) rc = occupancy_grid(ctx->part_kernel, kPartThreads, dyn, &ctx->part_grid);
         if ((e = cudaMalloc(&ctx->cursor, 2 * ctx->n_buckets * sizeof(unsigned int))) != cudaSuccess) return fail("cudaMalloc cursor", e);
     }
@@ -299,7 +302,8 @@ static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, un
         // every window ends on a text byte, so (hi - lo) bounds the entries of the pass; canonical ids of
         // uniform sequence load the lowest bucket with 2x the average, hence the 3x head room
         const unsigned long long avg = (hi - lo) / ctx->n_buckets + 1;
-        const unsigned int cap = (unsigned int)((3 * avg + 4096 + 7) & ~7ull);
+        const unsigned int cap = (unsigned int)((3 * avg + kTile + 7) & ~7ull);   // >= kTile: keeps s_delta (kdb_part.cuh) from wrapping
+        if ((unsigned long long)cap * ctx->n_buckets >= 0xFFFFFFFFull) { ctx->err = "bucket stream index exceeds 32 bits"; return KDB_E_ARG; }
         if (int rc = ensure(ctx, (void**)&ctx->stream, &ctx->stream_cap, (size_t)cap * ctx->n_buckets, sizeof(uint16_t))) return rc;
         CK(cudaMemsetAsync(ctx->cursor, 0, ctx->n_buckets * sizeof(unsigned int), ctx->s_compute));
         CK(cudaMemsetAsync(ctx->cursor + ctx->n_buckets, 0xFF, ctx->n_buckets * sizeof(unsigned int), ctx->s_compute));
@@ -310,7 +314,8 @@ static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, un
         ctx->part_kernel<<<grid, kPartThreads, k3p_smem_bytes(ctx->k), ctx->s_compute>>>(Q);
         CK(cudaGetLastError());
         CK(cudaEventRecord(ctx->ev[7], ctx->s_compute));
-        k3p_count<<<ctx->n_buckets * ctx->parts, kBucketThreads, 4 << kPayloadBits, ctx->s_compute>>>(ctx->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->tab32);
+        k3p_count<<<ctx->n_buckets * ctx->parts * ctx->subs, kBucketThreads, 4 << kTableBits, ctx->s_compute>>>(ctx->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->subs,
+                                                                                                                 payload_bits(ctx->k), ctx->tab32);
         CK(cudaGetLastError());
         ctx->timing.total_launches++;
     } else {

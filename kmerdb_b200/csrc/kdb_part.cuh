@@ -1,4 +1,4 @@
-// K3p — bucket-partitioned histogram for 8 <= k <= 12, sm_100a.
+// K3p — bucket-partitioned histogram for 8 <= k <= 14, sm_100a.
 //
 // Same job as K3 (kmerdb/kmer.py:297-317 ids, kmerdb/parse.py:133-136 counts) but built to get past
 // the scattered-RED ceiling (1.9e11 updates/s): shared-memory atomics are ~11x faster
@@ -19,7 +19,10 @@
 
 namespace kdb {
 
-constexpr int kPayloadBits = 14;                       // 16384 bins x 4 B = 64 KiB shared table per bucket
+constexpr int kTableBits = 14;                         // 16384 bins x 4 B = 64 KiB shared count table
+// payload bits kept in the 16-bit stream entries: 14 for k <= 12 (one table per bucket); 16 for k = 13, 14
+// (the bucket is counted in 4 sub-passes of 14 bits each, so the bucket count stays at 1024 / 4096)
+__host__ __device__ constexpr int payload_bits(int k) { return k <= 12 ? 14 : 16; }
 constexpr int kPartThreads = 512;                      // 512 threads x 32 letters = one full tile
 constexpr int kBucketThreads = 256;
 
@@ -41,7 +44,8 @@ __device__ __forceinline__ uint32_t shr96_rt(uint32_t w2, uint32_t w1, uint32_t 
 
 template <int K, bool CANON>
 __global__ void __launch_bounds__(kPartThreads, 2) k3p_partition(const PartParams P) {
-    constexpr int NB = 1 << (2 * K - kPayloadBits);                 // buckets
+    constexpr int PB = payload_bits(K);
+    constexpr int NB = 1 << (2 * K - PB);                           // buckets
     constexpr int RBITS = 32 - 2 * K;                               // rank bits kept beside the id in one register
     constexpr uint32_t RCAP = (1u << RBITS) - 1u;                   // ranks >= RCAP take the direct RED path
     constexpr uint32_t mask = (1u << (2 * K)) - 1u;
@@ -50,7 +54,7 @@ __global__ void __launch_bounds__(kPartThreads, 2) k3p_partition(const PartParam
     uint32_t* const s_sorted = s_dyn_part;                          // ids of the tile, grouped by bucket
     uint32_t* const s_hist = s_dyn_part + kTile;
     uint32_t* const s_off = s_hist + NB;
-    uint32_t* const s_gbase = s_off + NB;
+    uint32_t* const s_delta = s_off + NB;                           // stream index of sorted entry j = s_delta[bucket] + j
     __shared__ uint32_t s_warp[kPartThreads / 32];
     __shared__ unsigned long long s_red[kPartThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -89,7 +93,7 @@ __global__ void __launch_bounds__(kPartThreads, 2) k3p_partition(const PartParam
                 if (wb & (0x80000000u >> e)) {
                     uint32_t id = (e < 16 ? __funnelshift_r(cur0, prev, 30 - 2 * (e & 15)) : __funnelshift_r(cur1, cur0, 30 - 2 * (e & 15))) & mask;
                     if (CANON) { const uint32_t rc = shr96_rt(r2, r1, r0, 34 + 2 * e - 2 * K) & mask; id = rc < id ? rc : id; }
-                    const uint32_t rank = atomicAdd(&s_hist[id >> kPayloadBits], 1u);
+                    const uint32_t rank = atomicAdd(&s_hist[id >> PB], 1u);
                     if (rank < RCAP) it = id | (rank << (2 * K));
                     else atomicAdd(P.tab32 + id, 1u);                // a bucket this crowded inside one tile: count directly
                 }
@@ -140,12 +144,13 @@ __global__ void __launch_bounds__(kPartThreads, 2) k3p_partition(const PartParam
             if (b < NB) {
                 s_off[b] = base;
                 base += cnt[j];
-                uint32_t gb = 0xFFFFFFFFu;
+                uint32_t dl = 0xFFFFFFFFu;
                 if (cnt[j]) {
-                    gb = atomicAdd(P.cursor + b, cnt[j]);
-                    if (gb + cnt[j] > P.cap) { atomicMin(P.fail_base + b, gb); gb = 0xFFFFFFFFu; }   // does not fit: RED path
+                    const uint32_t gb = atomicAdd(P.cursor + b, cnt[j]);
+                    if (gb + cnt[j] > P.cap) atomicMin(P.fail_base + b, gb);                          // does not fit: RED path
+                    else dl = (uint32_t)b * P.cap + gb - (base - cnt[j]);                             // (host keeps n_buckets * cap < 2^32)
                 }
-                s_gbase[b] = gb;
+                s_delta[b] = dl;
             }
         }
         __syncthreads();
@@ -156,7 +161,7 @@ __global__ void __launch_bounds__(kPartThreads, 2) k3p_partition(const PartParam
             const uint32_t it = item[e];
             if (it != 0xFFFFFFFFu) {
                 const uint32_t id = it & mask;
-                s_sorted[s_off[id >> kPayloadBits] + (it >> (2 * K))] = id;
+                s_sorted[s_off[id >> PB] + (it >> (2 * K))] = id;
             }
         }
         __syncthreads();
@@ -164,9 +169,8 @@ __global__ void __launch_bounds__(kPartThreads, 2) k3p_partition(const PartParam
         // ---- phase 4: the sorted array leaves as payload runs, one entry per thread ----------------------
         for (uint32_t j = tid; j < total; j += kPartThreads) {
             const uint32_t id = s_sorted[j];
-            const uint32_t b = id >> kPayloadBits;
-            const uint32_t gb = s_gbase[b];
-            if (gb != 0xFFFFFFFFu) P.stream[(size_t)b * P.cap + gb + (j - s_off[b])] = (uint16_t)(id & ((1u << kPayloadBits) - 1u));
+            const uint32_t dl = s_delta[id >> PB];
+            if (dl != 0xFFFFFFFFu) P.stream[dl + j] = (uint16_t)(id & ((1u << PB) - 1u));
             else atomicAdd(P.tab32 + id, 1u);
         }
     }
@@ -181,13 +185,16 @@ __global__ void __launch_bounds__(kPartThreads, 2) k3p_partition(const PartParam
     }
 }
 
-// One work item = (bucket, part).  grid = n_buckets * parts.
+// One work item = (bucket, part, sub).  grid = n_buckets * parts * subs; sub selects the payloads whose bits
+// above kTableBits equal it (subs = 1 for k <= 12; 4 for k = 13, 14: the four CTAs of a bucket part run next to
+// each other, so the re-reads of the stream hit L2).
 __global__ void __launch_bounds__(kBucketThreads) k3p_count(const uint16_t* __restrict__ stream, const unsigned int* __restrict__ cursor,
-                                                            const unsigned int* __restrict__ fail_base, unsigned int cap, int parts,
-                                                            unsigned int* __restrict__ tab32) {
+                                                            const unsigned int* __restrict__ fail_base, unsigned int cap, int parts, int subs,
+                                                            int pb, unsigned int* __restrict__ tab32) {
     extern __shared__ unsigned int s_tab[];
     const int tid = threadIdx.x;
-    const uint32_t b = blockIdx.x / parts, part = blockIdx.x % parts;
+    const uint32_t sub = blockIdx.x % subs, bp = blockIdx.x / subs;
+    const uint32_t b = bp / parts, part = bp % parts;
     uint32_t end = cursor[b];
     { const uint32_t fb = fail_base[b]; end = end < fb ? end : fb; end = end < cap ? end : cap; }
     if (end == 0) return;
@@ -195,23 +202,36 @@ __global__ void __launch_bounds__(kBucketThreads) k3p_count(const uint16_t* __re
     const uint32_t units = (end + 7) >> 3, per = (units + parts - 1) / parts;
     const uint32_t u0 = part * per, u1 = min(units, u0 + per);
     if (u0 >= u1) return;
-    for (int i = tid; i < (1 << kPayloadBits); i += kBucketThreads) s_tab[i] = 0;
+    for (int i = tid; i < (1 << kTableBits); i += kBucketThreads) s_tab[i] = 0;
     __syncthreads();
     const uint4* src = reinterpret_cast<const uint4*>(stream + (size_t)b * cap);
-    for (uint32_t u = u0 + tid; u < u1; u += kBucketThreads) {
-        const uint4 v = __ldcs(src + u);
-        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-        const uint32_t valid = min(8u, end - 8 * u);
+    if (subs == 1) {
+        for (uint32_t u = u0 + tid; u < u1; u += kBucketThreads) {
+            const uint4 v = __ldcs(src + u);
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+            const uint32_t valid = min(8u, end - 8 * u);
 #pragma unroll
-        for (int q = 0; q < 8; q++)
-            if ((uint32_t)q < valid) atomicAdd(&s_tab[(w[q >> 1] >> (16 * (q & 1))) & 0x3FFFu], 1u);
+            for (int q = 0; q < 8; q++)
+                if ((uint32_t)q < valid) atomicAdd(&s_tab[(w[q >> 1] >> (16 * (q & 1))) & 0x3FFFu], 1u);
+        }
+    } else {
+        for (uint32_t u = u0 + tid; u < u1; u += kBucketThreads) {
+            const uint4 v = __ldg(src + u);
+            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+            const uint32_t valid = min(8u, end - 8 * u);
+#pragma unroll
+            for (int q = 0; q < 8; q++) {
+                const uint32_t pl = (w[q >> 1] >> (16 * (q & 1))) & 0xFFFFu;
+                if ((uint32_t)q < valid && (pl >> kTableBits) == sub) atomicAdd(&s_tab[pl & 0x3FFFu], 1u);
+            }
+        }
     }
     __syncthreads();
-    unsigned int* dst = tab32 + ((size_t)b << kPayloadBits);
-    for (int i = tid; i < (1 << kPayloadBits); i += kBucketThreads) { const unsigned int x = s_tab[i]; if (x) atomicAdd(dst + i, x); }
+    unsigned int* dst = tab32 + ((size_t)b << pb) + ((size_t)sub << kTableBits);
+    for (int i = tid; i < (1 << kTableBits); i += kBucketThreads) { const unsigned int x = s_tab[i]; if (x) atomicAdd(dst + i, x); }
 }
 
-__host__ inline size_t k3p_smem_bytes(int k) { return (size_t)(kTile + 3 * (1 << (2 * k - kPayloadBits))) * sizeof(uint32_t); }
+__host__ inline size_t k3p_smem_bytes(int k) { return (size_t)(kTile + 3 * (1 << (2 * k - payload_bits(k)))) * sizeof(uint32_t); }
 
 typedef void (*k3p_fn)(const PartParams);
 template <int K>
@@ -220,7 +240,8 @@ __host__ inline k3p_fn k3p_kernel(int k, bool canon) {
     switch (k) {
         case 8: return k3p_select<8>(canon);   case 9: return k3p_select<9>(canon);
         case 10: return k3p_select<10>(canon); case 11: return k3p_select<11>(canon);
-        case 12: return k3p_select<12>(canon);
+        case 12: return k3p_select<12>(canon); case 13: return k3p_select<13>(canon);
+        case 14: return k3p_select<14>(canon);
     }
     return nullptr;
 }
