@@ -143,16 +143,18 @@ struct ChunkMasks {
     uint32_t any_cr, any_hi;    // some byte is CR / >= 0x80
 };
 
-template <typename ByteWord>
-__device__ __forceinline__ ChunkMasks chunk_masks(ByteWord word) {
+template <typename Quad>
+__device__ __forceinline__ ChunkMasks chunk_masks(Quad quad) {
     ChunkMasks M;
     M.lf = 0; M.acgt = 0; M.any_cr = 0; M.any_hi = 0;
 #pragma unroll
     for (int q = 0; q < 4; q++) {
         uint32_t xc = 0, lf16 = 0, ok16 = 0;
+        const uint4 v4 = quad(q);                                                  // one conflict-free 16-byte shared load
+        const uint32_t w4[4] = {v4.x, v4.y, v4.z, v4.w};
 #pragma unroll
         for (int r = 0; r < 4; r++) {
-            const uint32_t wv = word(4 * q + r);
+            const uint32_t wv = w4[r];
             const uint32_t t = ((wv >> 1) ^ (wv >> 2)) & 0x03030303u;              // A0 C1 G2 T3 (N -> 0)
             const uint32_t s = t | (t >> 4);
             const uint32_t sel = (s & 0xFFu) | ((s >> 8) & 0xFF00u);
@@ -237,11 +239,15 @@ __device__ __forceinline__ TailAgg tail_scan_exclusive(TailAgg v, TailAgg* sm, T
     for (int d = 1; d < 32; d <<= 1) { const TailAgg o = tail_shfl_up(v, d); if (lane >= d) v = tail_combine(o, v); }
     if (lane == 31) sm[warp] = v;
     __syncthreads();
-    TailAgg pre = ident;
-    for (int w = 0; w < warp; w++) pre = tail_combine(pre, sm[w]);
-    TailAgg tot = pre;
-    for (int w = warp; w < kThreads / 32; w++) tot = tail_combine(tot, sm[w]);
-    *total = tot;
+    if (warp == 0) {                                         // inclusive scan of the warp aggregates by the first warp
+        TailAgg w = lane < kThreads / 32 ? sm[lane] : ident;
+#pragma unroll
+        for (int d = 1; d < kThreads / 32; d <<= 1) { const TailAgg o = tail_shfl_up(w, d); if (lane >= d) w = tail_combine(o, w); }
+        if (lane < kThreads / 32) sm[lane] = w;
+    }
+    __syncthreads();
+    const TailAgg pre = warp ? sm[warp - 1] : ident;
+    *total = sm[kThreads / 32 - 1];
     TailAgg e = tail_shfl_up(v, 1);
     if (lane == 0) e = ident;
     return tail_combine(pre, e);
@@ -275,8 +281,11 @@ __device__ __forceinline__ bool finalize_w(Emit& E, Tally& Y, unsigned long long
 }
 
 template <bool FASTQ>
-__global__ void __launch_bounds__(kThreads, 3) k2_encode(const EncodeParams P) {
-    __shared__ uint32_t s_text[(kChunk / 4) * (kThreads + 1)];   // transposed: word i of thread t at [i*(T+1)+t]
+__global__ void __launch_bounds__(kThreads, 4) k2_encode(const EncodeParams P) {
+    // two text buffers (cp.async double buffering).  Chunk t (64 bytes) lives at words [16t, 16t+16) with its four
+    // 16-byte groups XOR-swizzled by (t >> 1) & 3, so that the per-thread LDS.128 of a quarter warp hits 8 distinct
+    // bank groups.
+    __shared__ __align__(16) uint32_t s_text2[2][kTile / 4];
     __shared__ uint32_t s_out[kPackCodes + 2 * kPackBits];
     __shared__ uint8_t s_lut[256];
     __shared__ LineAgg s_scan[kThreads / 32];
@@ -293,40 +302,46 @@ __global__ void __launch_bounds__(kThreads, 3) k2_encode(const EncodeParams P) {
     Y.mono[0] = Y.mono[1] = Y.mono[2] = Y.mono[3] = 0; Y.nwin = 0; Y.err = 0;
     unsigned long long letters_total = 0, err_key = ~0ull;
     unsigned int layout = 0;
-    auto word = [&](int i) -> uint32_t { return s_text[i * (kThreads + 1) + tid]; };
-    auto byte_at = [&](uint32_t p) -> uint8_t { return (uint8_t)(s_text[(p >> 2) * (kThreads + 1) + tid] >> (8 * (p & 3))); };
-
-    for (unsigned int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+    const uint32_t* s_text = s_text2[0];
+    const uint32_t swz = ((uint32_t)tid >> 1) & 3u;
+    auto word = [&](int i) -> uint32_t { return s_text[16 * tid + 4 * (((uint32_t)i >> 2) ^ swz) + (i & 3)]; };
+    auto quad = [&](int q) -> uint4 { return *reinterpret_cast<const uint4*>(s_text + 16 * tid + 4 * ((uint32_t)q ^ swz)); };
+    auto byte_at = [&](uint32_t p) -> uint8_t { return (uint8_t)(s_text[16 * tid + 4 * ((p >> 4) ^ swz) + ((p >> 2) & 3)] >> (8 * (p & 3))); };
+    // asynchronous copy of one tile into buffer `b` (16 bytes per request, zero fill past P.hi)
+    auto stage = [&](unsigned int tile, int b) {
         const unsigned long long tile0 = P.lo + (unsigned long long)tile * kTile;
-        __syncthreads();
-        // ---- stage the tile: coalesced 16-byte loads, transposed into shared memory ----------
 #pragma unroll
         for (int r = 0; r < kChunk / 16; r++) {
-            const int q = tid + kThreads * r;
+            const uint32_t q = tid + kThreads * r;
             const unsigned long long g = tile0 + 16ull * q;
-            uint4 v = make_uint4(0, 0, 0, 0);
-            if (g + 16 <= P.hi) v = __ldcs(reinterpret_cast<const uint4*>(P.text + g));
-            else if (g < P.hi) {
-                uint32_t t4[4] = {0, 0, 0, 0};
-                for (int j = 0; j < (int)(P.hi - g); j++) t4[j >> 2] |= (uint32_t)P.text[g + j] << (8 * (j & 3));
-                v = make_uint4(t4[0], t4[1], t4[2], t4[3]);
-            }
-            const int owner = q >> 2, w0 = (q & 3) * 4;
-            s_text[(w0 + 0) * (kThreads + 1) + owner] = v.x;
-            s_text[(w0 + 1) * (kThreads + 1) + owner] = v.y;
-            s_text[(w0 + 2) * (kThreads + 1) + owner] = v.z;
-            s_text[(w0 + 3) * (kThreads + 1) + owner] = v.w;
+            const uint32_t t = q >> 2, grp = (q & 3) ^ ((t >> 1) & 3);
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&s_text2[b][16 * t + 4 * grp]);
+            const uint32_t nb = g + 16 <= P.hi ? 16u : (g < P.hi ? (uint32_t)(P.hi - g) : 0u);
+            const uint8_t* src = P.text + (nb ? g : P.lo);
+            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(nb) : "memory");
         }
+        asm volatile("cp.async.commit_group;" ::: "memory");
+    };
+
+    int buf = 0;
+    if (blockIdx.x < P.n_tiles) stage(blockIdx.x, 0);
+    for (unsigned int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, buf ^= 1) {
+        const unsigned long long tile0 = P.lo + (unsigned long long)tile * kTile;
+        __syncthreads();                                    // everyone is done with the buffer the next copy overwrites
+        // ---- stage: the next tile streams into the other buffer while this one is processed ----------------
+        if (tile + gridDim.x < P.n_tiles) { stage(tile + gridDim.x, buf ^ 1); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
+        else asm volatile("cp.async.wait_group 0;" ::: "memory");
+        s_text = s_text2[buf];
         for (int i = tid; i < kPackCodes + 2 * kPackBits; i += kThreads) s_out[i] = 0;
         __syncthreads();
 
         const unsigned long long a = tile0 + (unsigned long long)tid * kChunk;
         const int lim = a >= P.hi ? 0 : (P.hi - a >= (unsigned long long)kChunk ? kChunk : (int)(P.hi - a));
         uint8_t prev = '\n';
-        if (lim > 0 && a > 0) prev = tid > 0 ? (uint8_t)(s_text[(kChunk / 4 - 1) * (kThreads + 1) + tid - 1] >> 24) : P.text[a - 1];
+        if (lim > 0 && a > 0) prev = tid > 0 ? (uint8_t)(s_text[16 * (tid - 1) + 4 * (3u ^ (((uint32_t)(tid - 1) >> 1) & 3u)) + 3] >> 24) : P.text[a - 1];
 
         // ---- phase A: bit masks of my chunk; phase B: line starts -> CTA scan ---------------------
-        const ChunkMasks M = chunk_masks(word);      // zero fill beyond lim is neither LF nor a letter
+        const ChunkMasks M = chunk_masks(quad);      // zero fill beyond lim is neither LF nor a letter
         LineAgg g{0, 0, 0};
         if (lim > 0) {
             unsigned long long lsm = ((M.lf << 1) | (prev == '\n' ? 1ull : 0ull)) & ones64((uint32_t)lim);
@@ -363,7 +378,7 @@ __global__ void __launch_bounds__(kThreads, 3) k2_encode(const EncodeParams P) {
             bool need_halo;
             if (FASTQ) need_halo = prev != '\n' && kind == 1;
             else if (prev != '\n') need_halo = kind == K_SEQ;
-            else need_halo = hdr_before != 0 && (uint8_t)s_text[tid] != '>';
+            else need_halo = hdr_before != 0 && byte_at(0) != '>';
             uint32_t halo_codes = 0, halo_nn = 0;
             bool walked = false;
             rec0 = rec;

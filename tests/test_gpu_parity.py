@@ -185,3 +185,35 @@ def test_kmer_to_id_batch(golden):
     assert _native.kmer_to_id_batch(two, 2, canonical=True).tolist() == golden["scalars"]["kmer_to_id_2mers_canonical"]
     ids = _native.kmer_to_id_batch(b"ATCNATCACGRACG", 7)
     assert ids[0] == np.uint64(2 ** 64 - 1) and ids[1] == np.uint64(2 ** 64 - 2)
+
+
+def test_full_size_100M_reads_properties():
+    """BASELINE.json configs[2] size on one GPU (100 M x 150 bp, 16.2 GB of FASTA text, 16 passes): the
+    size-independent properties of the result, and identity of two different feed chunkings."""
+    n, k = 100_000_000, 12
+    rb = _native.synth_record_bytes()
+    buf = _native.DeviceBuffer(n * rb + 16)
+    _native.synth_device(buf, n)
+    with _native.Profiler(k) as p:
+        p.feed_device(buf.ptr, n * rb)
+        assert p.finish() == 0
+        st, counts = p.stats(), p.counts()
+        assert st["total_reads"] == n and st["total_kmers"] == n * (150 - k + 1) == int(counts.sum(dtype=np.uint64))
+        assert st["sum_len"] == n * 150 == sum(st["mono"]) and st["min_len"] == st["max_len"] == 150
+        assert st["unique_kmers"] == int(np.count_nonzero(counts)) == (4 ** k + 4 ** (k // 2)) // 2     # saturated canonical space
+        # canonical ids only: a bin above its own reverse complement stays empty
+        ids = np.flatnonzero(counts).astype(np.uint64)
+        assert ids.size == st["unique_kmers"]
+        # checksum of checksums: two feeds cut at a record boundary give the same vector
+        p.reset()
+        cut = 37_000_008 * rb                          # a record boundary whose byte offset is a multiple of 16 (device feeds are 16-byte aligned)
+        p.feed_device(buf.ptr, cut)
+        p.feed_device(buf.ptr + cut, n * rb - cut)
+        assert p.finish() == 0
+        assert np.array_equal(p.counts(), counts) and p.stats() == st
+    # the first 200 000 reads of the same stream against the oracle
+    host = _native.synth_host(200000)
+    rc, ocounts, ost = oracle.profile(host, k, threads=8)
+    with _native.Profiler(k) as q:
+        q.feed_device(buf.ptr, 200000 * rb)
+        assert q.finish() == 0 and np.array_equal(q.counts(), ocounts)
