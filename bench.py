@@ -46,7 +46,7 @@ class ClockSampler:
 
     def start(self):
         try:
-            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "100"],
+            self.proc = subprocess.Popen(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q, "--format=csv,noheader,nounits", "-lms", "20"],
                                          stdout=subprocess.PIPE, stderr=subprocess.DEVNULL, text=True)
             self.thread = threading.Thread(target=self._read, daemon=True)
             self.thread.start()
@@ -186,11 +186,11 @@ def run_b200(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     ev0.record()
-    job_ms = count_ms = scan_ms = fold_ms = final_ms = encode_ms = 0.0
+    job_ms = count_ms = scan_ms = fold_ms = final_ms = encode_ms = part_ms = 0.0
     count_launches = launches = 0
     for _ in range(args.steps):
         t = step_device()
-        job_ms += t["job_ms"]; count_ms += t["count_ms"]; encode_ms += t["encode_ms"]; scan_ms += t["scan_ms"]; fold_ms += t["fold_ms"]; final_ms += t["final_ms"]
+        job_ms += t["job_ms"]; count_ms += t["count_ms"]; part_ms += t["partition_ms"]; encode_ms += t["encode_ms"]; scan_ms += t["scan_ms"]; fold_ms += t["fold_ms"]; final_ms += t["final_ms"]
         count_launches += t["count_launches"]; launches += t["total_launches"]
     ev1.record()
     barrier()
@@ -239,16 +239,22 @@ def run_b200(args):
         assert stats["total_kmers"] == world * n_reads * (READ_LEN - k + 1), stats
         assert st_host["total_kmers"] == stats["total_kmers"] and int(counts_view.sum()) == stats["total_kmers"]
         peak, peak_src = peaks()
+        # dominant kernel of the step: k3p_partition (ids + tile-local bucket sort + stream write), one launch per pass
         per_launch_bytes = nbytes / (count_launches / args.steps)
-        avg_launch_s = count_ms * 1e-3 / count_launches
+        avg_launch_s = part_ms * 1e-3 / count_launches
         achieved = per_launch_bytes / avg_launch_s / 1e9
         traffic = None
-        tpath = os.path.join(ROOT, "profiles", "traffic_k2_count.json")
+        tpath = os.path.join(ROOT, "profiles", "traffic_k3p_partition.json")
         if os.path.exists(tpath):
             try:
-                traffic = json.load(open(tpath)).get("dram_bytes_per_launch")
+                tj = json.load(open(tpath))
+                traffic = tj["dram_bytes_per_text_byte"] * per_launch_bytes     # ncu --set full capture, scaled to this launch size
             except Exception:
                 traffic = None
+        per_kernel = {}
+        for name, ms in (("k1_scan", scan_ms), ("k2_encode", encode_ms), ("k3p_partition", part_ms), ("k3p_count", count_ms - part_ms)):
+            gbs = nbytes * args.steps / (ms * 1e-3) / 1e9 if ms > 0 else None
+            per_kernel[name] = {"ms_per_step": ms / args.steps, "GBps_of_text": gbs, "frac_of_hbm_peak": gbs / peak if gbs else None}
         line = {
             "metric": METRIC, "value": world * n_bases * args.steps / job_max if world == 1 else world * n_bases * args.steps / wall_max,
             "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
@@ -258,13 +264,14 @@ def run_b200(args):
             "e2e": {"value": world * n_bases * e2e_steps / e2e_wall, "unit": UNIT, "h2d_bytes_per_step": nbytes,
                     "d2h_bytes_per_step": 8 * 4 ** k + 112, "steps": e2e_steps},
             "gpu_launches": int(launches),
-            "roofline": {"bound": "hbm", "kernel": "k3_count", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
+            "roofline": {"bound": "hbm", "kernel": "k3p_partition", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_base": rb / READ_LEN, "bytes_per_launch": per_launch_bytes,
                          "avg_launch_ms": 1e3 * avg_launch_s,
                          "whole_job_frac": (nbytes * args.steps / (job_max if world == 1 else wall_max) / 1e9) / peak,
-                         "note": "k>=8 is bound by scattered 32-bit atomics, not HBM: see DESIGN.md (atomic roofline) and profiles/"},
-            "kernel_ms_per_step": {"scan": scan_ms / args.steps, "count": count_ms / args.steps, "fold": fold_ms / args.steps, "final": final_ms / args.steps, "encode": encode_ms / args.steps},
+                         "kernels": per_kernel,
+                         "note": "the count path is bound by shared-memory bank wavefronts and instruction issue, not HBM: see DESIGN.md section 4 and profiles/"},
+            "kernel_ms_per_step": {"scan": scan_ms / args.steps, "partition": part_ms / args.steps, "count": count_ms / args.steps, "fold": fold_ms / args.steps, "final": final_ms / args.steps, "encode": encode_ms / args.steps},
             "clocks": clocks,
             "result_check": {"total_kmers": stats["total_kmers"], "unique_kmers": stats["unique_kmers"], "total_reads": stats["total_reads"]},
         }
@@ -283,7 +290,7 @@ def run_b200(args):
 def main():
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
-    ap.add_argument("--steps", type=int, default=10)
+    ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--reads", type=int, default=10_000_000, help="reads per GPU (configs[1]: 10M x 150 bp)")

@@ -392,7 +392,7 @@ extern "C" int kdb_feed_host(kdb_ctx* ctx, const uint8_t* bytes, size_t n) {
     if (int rc = begin_feed(ctx)) return rc;
     // stage pass by pass on the copy stream; the compute stream waits for the pass it needs, so the
     // copy of pass i+1 overlaps the kernels of pass i
-    const unsigned long long pass = 256ull << 20;
+    const unsigned long long pass = 96ull << 20;       // short passes: the kernels of the last pass are the only ones PCIe does not hide
     const size_t n_pass = (size_t)((n + pass - 1) / pass);
     while (ctx->ev_copy.size() < n_pass + 1) { cudaEvent_t e; CK(cudaEventCreate(&e)); ctx->ev_copy.push_back(e); }
     CK(cudaEventRecord(ctx->ev_copy[n_pass], ctx->s_copy));
