@@ -144,6 +144,7 @@ def run_b200(args):
     if not torch.cuda.is_available():
         raise SystemExit("bench.py needs a CUDA device: the profile path has no CPU fallback")
     torch.cuda.set_device(local)
+    numa_cpus = kd.bind_to_gpu_numa(local) if world > 1 else None      # pinned buffers on the GPU's NUMA node
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 

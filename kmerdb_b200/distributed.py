@@ -94,3 +94,30 @@ def reduce_profiler(prof, dist, device, dst=0, _cache={}):
         prof.import_partials(out)
         return prof.refinalize()
     return 0
+
+
+def bind_to_gpu_numa(local_device):
+    """Pin this process to the CPUs next to its GPU (sysfs local_cpulist of the PCI device) so that pinned host
+    buffers are allocated on the GPU's NUMA node: with 8 ranks feeding 8 GPUs the host->device copies otherwise
+    cross the socket interconnect.  Silently does nothing when sysfs does not say."""
+    import os
+    try:
+        import torch
+        pr = torch.cuda.get_device_properties(local_device)
+        bus = "%04x:%02x:%02x.0" % (pr.pci_domain_id, pr.pci_bus_id, pr.pci_device_id)
+        with open("/sys/bus/pci/devices/%s/local_cpulist" % bus) as fh:
+            spec = fh.read().strip()
+        cpus = set()
+        for part in spec.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                cpus.update(range(int(a), int(b) + 1))
+            elif part:
+                cpus.add(int(part))
+        cpus &= os.sched_getaffinity(0)
+        if cpus:
+            os.sched_setaffinity(0, cpus)
+            return sorted(cpus)
+    except Exception:
+        pass
+    return None
