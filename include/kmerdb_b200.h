@@ -107,6 +107,13 @@ int kdb_export_partials(kdb_ctx* ctx, uint64_t* out16); /* [reads,kmers,sum_len,
 int kdb_import_partials(kdb_ctx* ctx, const uint64_t* in16);
 int kdb_refinalize(kdb_ctx* ctx);
 
+/* Multi-k sweep (`--minK/--maxK`, kmerdb/__init__.py:1846-1855: the reference runs _profile once per k and
+ * re-parses the input every time).  After kdb_attach(leader, follower) — same device and flags, 2 <= k(leader) <
+ * k(follower), before any feed — every feed of the leader also counts the follower's k from the leader's packed
+ * letter stream: the text is scanned and encoded once for the whole sweep.  Finish the leader first, then each
+ * follower; kdb_counts/kdb_stats/kdb_nullomers work on followers as usual; kdb_reset(leader) resets the sweep. */
+int kdb_attach(kdb_ctx* leader, kdb_ctx* follower);
+
 /* Start a new file on the same context (tables zeroed, allocations kept). */
 int kdb_reset(kdb_ctx* ctx);
 int kdb_timing(kdb_ctx* ctx, kdb_timing_t* out);

@@ -19,7 +19,7 @@ EXPORTS = [
     "kdb_reset", "kdb_timing", "kdb_kmer_to_id_batch", "kdb_synth_record_bytes", "kdb_synth_device",
     "kdb_synth_host", "kdb_microbench_atomics", "kdb_dev_alloc", "kdb_dev_free", "kdb_host_alloc_pinned",
     "kdb_host_free_pinned", "kdb_memcpy_h2d", "kdb_memcpy_d2h",
-    "kdb_edge_rows", "kdb_edge_weights", "kdb_minimizers_compat", "kdb_minimizers",
+    "kdb_edge_rows", "kdb_edge_weights", "kdb_minimizers_compat", "kdb_minimizers", "kdb_attach",
 ]
 
 
@@ -65,7 +65,7 @@ def lib():
         ("kdb_nullomers", [vp, vp, sz, ctypes.POINTER(sz)]),
         ("kdb_device_table", [vp, ctypes.POINTER(vp), ctypes.POINTER(sz)]),
         ("kdb_export_partials", [vp, vp]), ("kdb_import_partials", [vp, vp]), ("kdb_refinalize", [vp]),
-        ("kdb_reset", [vp]), ("kdb_timing", [vp, ctypes.POINTER(Timing)]),
+        ("kdb_attach", [vp, vp]), ("kdb_reset", [vp]), ("kdb_timing", [vp, ctypes.POINTER(Timing)]),
         ("kdb_kmer_to_id_batch", [ci, ctypes.c_char_p, sz, ci, ci, vp]),
         ("kdb_synth_device", [ci, vp, u64, u64, ci, ci, u64]), ("kdb_synth_host", [vp, u64, u64, ci, ci, u64]),
         ("kdb_microbench_atomics", [ci, sz, u64, ci, ctypes.POINTER(ctypes.c_double)]),
@@ -177,6 +177,10 @@ class Profiler:
     def finish(self):
         """Returns the status code (0, or the reference exception class code of the first failing record)."""
         return self._check(lib().kdb_finish(self._ctx), "kdb_finish")
+
+    def attach(self, follower):
+        """Multi-k sweep: `follower` (a Profiler with a larger k) counts from this context's packed stream."""
+        self._check(lib().kdb_attach(self._ctx, follower._ctx), "kdb_attach")
 
     def refinalize(self):
         return self._check(lib().kdb_refinalize(self._ctx), "kdb_refinalize")

@@ -33,14 +33,17 @@ def _inputs(args):
     raise ValueError("Could not determine file type of input")
 
 
-def _profile(args, k, files):
-    """kmerdb/__init__.py:1862-2013 for one k."""
+def _profile(args, k, files, precomputed=None):
+    """kmerdb/__init__.py:1862-2013 for one k.  `precomputed`: [(counts, file_metadata)] per file from the shared sweep."""
     N = 4 ** k
     counts = np.zeros(N, dtype="uint64")
     file_metadata = []
-    for f in files:
-        c, meta, _nullomers = parse.parsefile(f, k, replace_with_none=args.no_ambiguous, canonicalize=not args.do_not_canonicalize,
-                                              device=args.device)
+    for i, f in enumerate(files):
+        if precomputed is not None:
+            c, meta = precomputed[i]
+        else:
+            c, meta, _nullomers = parse.parsefile(f, k, replace_with_none=args.no_ambiguous, canonicalize=not args.do_not_canonicalize,
+                                                  device=args.device)
         counts = counts + c                                        # __init__.py:1890
         file_metadata.append(meta)
     total = int(np.sum(counts))
@@ -67,7 +70,21 @@ def profile(args):
             raise ValueError("In multi-k mode, arguments --minK and --maxK are required.")
         elif args.minK < 4 or args.maxK < 5 or args.minK > 25 or args.maxK > 30:
             raise ValueError("Valid --min|max between 3 and 30")
-        return [_profile(args, k, files) for k in range(args.minK, args.maxK + 1)]
+        # one scan + encode per file for the whole sweep (kdb_attach); outputs appear in increasing k like the reference loop
+        sweeps, outs = [], []
+        for f in files:
+            md5, sha256 = parse.checksum(f)
+            it = parse.iter_profile_multik(parse._read_text_bytes(f), args.minK, args.maxK, fmt=parse._file_format(f),
+                                           replace_with_none=args.no_ambiguous, canonicalize=not args.do_not_canonicalize, device=args.device)
+            sweeps.append((f, md5, sha256, it))
+        for k in range(args.minK, args.maxK + 1):
+            pre = []
+            for f, md5, sha256, it in sweeps:
+                kk, prof = next(it)
+                assert kk == k
+                pre.append((prof.counts, prof.file_metadata(f, md5, sha256)))
+            outs.append(_profile(args, k, files, precomputed=pre))
+        return outs
     return [_profile(args, args.k, files)]
 
 

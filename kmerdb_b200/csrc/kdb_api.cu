@@ -67,6 +67,10 @@ struct kdb_ctx {
     kdb_stats_t stats{};
     kdb_timing_t timing{};
     std::string err;
+    // multi-k sweep (kdb_attach): followers count larger k from this context's packed stream
+    std::vector<kdb_ctx*> followers;
+    kdb_ctx* leader = nullptr;
+    int k_halo = 0;
 };
 
 #define CK(call)                                                                                   \
@@ -116,6 +120,8 @@ extern "C" const char* kdb_last_error(const kdb_ctx* ctx) { return ctx ? ctx->er
 
 extern "C" void kdb_destroy(kdb_ctx* ctx) {
     if (!ctx) return;
+    for (kdb_ctx* f : ctx->followers) f->leader = nullptr;
+    if (ctx->leader) { auto& v = ctx->leader->followers; v.erase(std::remove(v.begin(), v.end(), ctx), v.end()); }
     cudaSetDevice(ctx->device);
     cudaFree(ctx->tab32); cudaFree(ctx->tab64); cudaFree(ctx->acc); cudaFree(ctx->carry); cudaFree(ctx->carry_len);
     cudaFree(ctx->tile_sum); /* tile_state lives inside the tile_sum allocation */ cudaFree(ctx->rec_len); cudaFree(ctx->feed_buf); cudaFree(ctx->packed); cudaFree(ctx->stream); cudaFree(ctx->cursor);
@@ -147,8 +153,25 @@ static int reset_state(kdb_ctx* ctx) {
 
 extern "C" int kdb_reset(kdb_ctx* ctx) {
     if (!ctx) return KDB_E_ARG;
+    if (ctx->leader) { ctx->err = "kdb_reset on a follower: reset its leader"; return KDB_E_STATE; }
     if (int rc = set_device(ctx, ctx->device)) return rc;
+    for (kdb_ctx* f : ctx->followers) if (int rc = reset_state(f)) return rc;
     return reset_state(ctx);
+}
+
+// Multi-k sweep (kmerdb/__init__.py:1853-1855 runs _profile once per k and re-parses the file each time): a
+// follower counts its larger k from the leader's packed letter stream, so the text is scanned and encoded once.
+extern "C" int kdb_attach(kdb_ctx* leader, kdb_ctx* follower) {
+    kdb_ctx* ctx = leader;
+    if (!leader || !follower || leader == follower) return KDB_E_ARG;
+    if (leader->leader || follower->leader || !follower->followers.empty()) { ctx->err = "kdb_attach: contexts are already part of a sweep"; return KDB_E_STATE; }
+    if (leader->device != follower->device || (leader->flags & 7) != (follower->flags & 7)) { ctx->err = "kdb_attach: device and CANONICAL/SKIP_N/FASTQ flags must match"; return KDB_E_ARG; }
+    if (leader->k < 2 || follower->k <= leader->k) { ctx->err = "kdb_attach: needs 2 <= k(leader) < k(follower)"; return KDB_E_ARG; }
+    if (leader->timing.bytes_fed || follower->timing.bytes_fed || leader->finished || follower->finished) { ctx->err = "kdb_attach after data was fed"; return KDB_E_STATE; }
+    leader->followers.push_back(follower);
+    follower->leader = leader;
+    leader->k_halo = std::max(leader->k_halo, follower->k);
+    return KDB_OK;
 }
 
 extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
@@ -246,6 +269,53 @@ static int close_carry_record(kdb_ctx* ctx) {
     return KDB_OK;
 }
 
+// K3 / K3p of one pass: ids from `src`'s packed stream into `ctx`'s tables (ctx == src, or a follower of src that
+// counts a larger k from the same stream).  Launched on src's stream; ctx->ev[7] marks the end of the first kernel.
+static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigned long long lo, unsigned long long hi) {
+    const int smear = ctx->k - src->k;
+    cudaStream_t st = src->s_compute;
+    if (ctx != src && ctx->bytes_since_fold + (hi - lo) > 0x7fffffffull) {
+        const unsigned long long quads = (ctx->nbins + 3) / 4;
+        k3_fold<<<(int)std::min<unsigned long long>((quads + 255) / 256, 148ull * 16), 256, 0, st>>>(ctx->tab32, ctx->tab64, ctx->nbins);
+        CK(cudaGetLastError());
+        ctx->bytes_since_fold = 0;
+    }
+    if (ctx->partitioned) {
+        // every window ends on a text byte, so (hi - lo) bounds the entries of the pass; canonical ids of
+        // uniform sequence load the lowest bucket with 2x the average, hence the 3x head room
+        const unsigned long long avg = (hi - lo) / ctx->n_buckets + 1;
+        const unsigned int cap = (unsigned int)((3 * avg + kTile + 7) & ~7ull);   // >= kTile: keeps s_delta (kdb_part.cuh) from wrapping
+        if ((unsigned long long)cap * ctx->n_buckets >= 0xFFFFFFFFull) { ctx->err = "bucket stream index exceeds 32 bits"; return KDB_E_ARG; }
+        if (int rc = ensure(ctx, (void**)&ctx->stream, &ctx->stream_cap, (size_t)cap * ctx->n_buckets, sizeof(uint16_t))) return rc;
+        CK(cudaMemsetAsync(ctx->cursor, 0, ctx->n_buckets * sizeof(unsigned int), st));
+        CK(cudaMemsetAsync(ctx->cursor + ctx->n_buckets, 0xFF, ctx->n_buckets * sizeof(unsigned int), st));
+        PartParams Q{};
+        Q.packed = src->packed; Q.n_tiles = n_tiles; Q.skip_n = ctx->skip_n; Q.smear = smear; Q.tab32 = ctx->tab32; Q.stream = ctx->stream;
+        Q.cursor = ctx->cursor; Q.fail_base = ctx->cursor + ctx->n_buckets; Q.cap = cap; Q.acc = ctx->acc;
+        const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->part_grid);
+        ctx->part_kernel<<<grid, kPartThreads, k3p_smem_bytes(ctx->k), st>>>(Q);
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(ctx->ev[7], st));
+        k3p_count<<<ctx->n_buckets * ctx->parts * ctx->subs, kBucketThreads, 4 << kTableBits, st>>>(ctx->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->subs,
+                                                                                                  payload_bits(ctx->k), ctx->tab32);
+        CK(cudaGetLastError());
+        ctx->timing.total_launches++;
+    } else {
+        HistParams H{};
+        H.packed = src->packed; H.n_tiles = n_tiles; H.skip_n = ctx->skip_n; H.smear = smear; H.tab32 = ctx->tab32; H.acc = ctx->acc;
+        const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->hist_grid);
+        ctx->hist_kernel<<<grid, kHistThreads, ctx->hist_dyn, st>>>(H);
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(ctx->ev[7], st));
+    }
+    if (ctx != src) {
+        ctx->timing.count_launches++;
+        ctx->timing.total_launches++;
+        ctx->bytes_since_fold += hi - lo;
+    }
+    return KDB_OK;
+}
+
 static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, unsigned long long hi, unsigned long long n) {
     const unsigned int n_tiles = (unsigned int)((hi - lo + kTile - 1) / kTile);
     if (int rc = ensure(ctx, (void**)&ctx->tile_sum, &ctx->tile_cap, n_tiles, sizeof(TileSummary) + sizeof(TileState))) return rc;
@@ -288,7 +358,7 @@ static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, un
     if (int rc = ensure(ctx, (void**)&ctx->packed, &ctx->packed_cap, (size_t)n_tiles * kPackStride, sizeof(uint32_t))) return rc;
     EncodeParams P{};
     P.text = text; P.lo = lo; P.hi = hi; P.n = n; P.tiles = ctx->tile_state; P.n_tiles = n_tiles; P.k = ctx->k;
-    P.skip_n = ctx->skip_n; P.packed = ctx->packed; P.rec_len = ctx->rec_len;
+    P.skip_n = ctx->skip_n; P.k_halo = std::max(ctx->k, ctx->k_halo); P.packed = ctx->packed; P.rec_len = ctx->rec_len;
     P.rec_first = rec_first; P.fq_rec_base = ctx->fq_rec_base; P.acc = ctx->acc;
     CK(cudaEventRecord(ctx->ev[2], ctx->s_compute));
     {
@@ -298,35 +368,14 @@ static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, un
         CK(cudaGetLastError());
     }
     CK(cudaEventRecord(ctx->ev[6], ctx->s_compute));
-    if (ctx->partitioned) {
-        // every window ends on a text byte, so (hi - lo) bounds the entries of the pass; canonical ids of
-        // uniform sequence load the lowest bucket with 2x the average, hence the 3x head room
-        const unsigned long long avg = (hi - lo) / ctx->n_buckets + 1;
-        const unsigned int cap = (unsigned int)((3 * avg + kTile + 7) & ~7ull);   // >= kTile: keeps s_delta (kdb_part.cuh) from wrapping
-        if ((unsigned long long)cap * ctx->n_buckets >= 0xFFFFFFFFull) { ctx->err = "bucket stream index exceeds 32 bits"; return KDB_E_ARG; }
-        if (int rc = ensure(ctx, (void**)&ctx->stream, &ctx->stream_cap, (size_t)cap * ctx->n_buckets, sizeof(uint16_t))) return rc;
-        CK(cudaMemsetAsync(ctx->cursor, 0, ctx->n_buckets * sizeof(unsigned int), ctx->s_compute));
-        CK(cudaMemsetAsync(ctx->cursor + ctx->n_buckets, 0xFF, ctx->n_buckets * sizeof(unsigned int), ctx->s_compute));
-        PartParams Q{};
-        Q.packed = ctx->packed; Q.n_tiles = n_tiles; Q.skip_n = ctx->skip_n; Q.tab32 = ctx->tab32; Q.stream = ctx->stream;
-        Q.cursor = ctx->cursor; Q.fail_base = ctx->cursor + ctx->n_buckets; Q.cap = cap; Q.acc = ctx->acc;
-        const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->part_grid);
-        ctx->part_kernel<<<grid, kPartThreads, k3p_smem_bytes(ctx->k), ctx->s_compute>>>(Q);
-        CK(cudaGetLastError());
-        CK(cudaEventRecord(ctx->ev[7], ctx->s_compute));
-        k3p_count<<<ctx->n_buckets * ctx->parts * ctx->subs, kBucketThreads, 4 << kTableBits, ctx->s_compute>>>(ctx->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->subs,
-                                                                                                                 payload_bits(ctx->k), ctx->tab32);
-        CK(cudaGetLastError());
-        ctx->timing.total_launches++;
-    } else {
-        HistParams H{};
-        H.packed = ctx->packed; H.n_tiles = n_tiles; H.skip_n = ctx->skip_n; H.tab32 = ctx->tab32; H.acc = ctx->acc;
-        const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->hist_grid);
-        ctx->hist_kernel<<<grid, kHistThreads, ctx->hist_dyn, ctx->s_compute>>>(H);
-        CK(cudaGetLastError());
-        CK(cudaEventRecord(ctx->ev[7], ctx->s_compute));
-    }
+    if (int rc = count_stage(ctx, ctx, n_tiles, lo, hi)) return rc;
     CK(cudaEventRecord(ctx->ev[3], ctx->s_compute));
+    for (kdb_ctx* f : ctx->followers) {                                  // larger k of a sweep, from the same packed stream
+        CK(cudaEventRecord(f->ev[6], ctx->s_compute));
+        if (int rc = count_stage(f, ctx, n_tiles, lo, hi)) { ctx->err = f->err; return rc; }
+        CK(cudaEventRecord(f->ev[3], ctx->s_compute));
+    }
+    CK(cudaEventRecord(ctx->ev[5], ctx->s_compute));
     const unsigned long long n_complete = n_entries - 1;
     if (n_complete) {
         const int g4 = (int)std::min<unsigned long long>((n_complete + 255) / 256, 148ull * 8);
@@ -346,7 +395,11 @@ static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, un
     CK(cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[6])); ctx->timing.encode_ms += ms;
     CK(cudaEventElapsedTime(&ms, ctx->ev[6], ctx->ev[3])); ctx->timing.count_ms += ms;
     CK(cudaEventElapsedTime(&ms, ctx->ev[6], ctx->ev[7])); ctx->timing.partition_ms += ms;
-    CK(cudaEventElapsedTime(&ms, ctx->ev[3], ctx->ev[4])); ctx->timing.final_ms += ms;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[5], ctx->ev[4])); ctx->timing.final_ms += ms;
+    for (kdb_ctx* f : ctx->followers) {
+        CK(cudaEventElapsedTime(&ms, f->ev[6], f->ev[3])); f->timing.count_ms += ms;
+        CK(cudaEventElapsedTime(&ms, f->ev[6], f->ev[7])); f->timing.partition_ms += ms;
+    }
     ctx->timing.count_launches++;
     ctx->timing.total_launches += 4;
     ctx->bytes_since_fold += hi - lo;
@@ -354,6 +407,7 @@ static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, un
 }
 
 static int begin_feed(kdb_ctx* ctx) {
+    if (ctx->leader) { ctx->err = "kdb_feed on a follower: feed its leader"; return KDB_E_STATE; }
     if (ctx->finished) { ctx->err = "kdb_feed after kdb_finish (call kdb_reset first)"; return KDB_E_STATE; }
     if (!ctx->job_started) { CK(cudaEventRecord(ctx->ev_job0, ctx->s_compute)); ctx->job_started = true; }
     // line indices restart with every fragment (fragments begin at a record boundary)
@@ -442,10 +496,38 @@ static int fill_stats(kdb_ctx* ctx) {
     return KDB_OK;
 }
 
+// A follower finishes after its leader: its own table is folded and counted for non-zeros; the per-record
+// reductions are the leader's.  Raises: whatever the leader raises (the sweep dies at its first k); else a record
+// shorter than this k (kmerdb/kmer.py:461-463) — alphabet raises do not depend on k, and a window of this k that
+// holds RYSWKMBDHV contains a window of the leader's k that does, so no new KeyError can appear.
+static int finish_follower(kdb_ctx* ctx) {
+    kdb_ctx* L = ctx->leader;
+    if (!L->finished) { ctx->err = "kdb_finish on a follower before its leader"; return KDB_E_STATE; }
+    CK(cudaStreamSynchronize(L->s_compute));
+    CK(cudaEventRecord(ctx->ev[0], ctx->s_compute));
+    if (int rc = fold_now(ctx)) return rc;
+    if (int rc = compute_unique(ctx)) return rc;
+    CK(cudaEventRecord(ctx->ev[1], ctx->s_compute));
+    if (int rc = fill_stats(ctx)) return rc;
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1])); ctx->timing.final_ms += ms;
+    ctx->timing.job_ms = ctx->timing.count_ms + ctx->timing.final_ms;
+    kdb_stats_t& s = ctx->stats;
+    const kdb_stats_t& l = L->stats;
+    s.total_reads = l.total_reads; s.sum_len = l.sum_len; s.min_len = l.min_len; s.max_len = l.max_len;
+    for (int i = 0; i < 4; i++) s.mono[i] = l.mono[i];
+    s.n_windows_with_n = l.n_windows_with_n;
+    s.err_record = l.err_record;
+    s.status = l.status ? l.status : (l.min_len < (uint64_t)ctx->k ? KDB_E_SHORT : KDB_OK);
+    ctx->finished = true;
+    return s.status;
+}
+
 extern "C" int kdb_finish(kdb_ctx* ctx) {
     if (!ctx) return KDB_E_ARG;
     if (int rc = set_device(ctx, ctx->device)) return rc;
     if (ctx->finished) return ctx->stats.status;
+    if (ctx->leader) return finish_follower(ctx);
     if (!ctx->job_started) { CK(cudaEventRecord(ctx->ev_job0, ctx->s_compute)); ctx->job_started = true; }
     CK(cudaEventRecord(ctx->ev[0], ctx->s_compute));
     if (int rc = close_carry_record(ctx)) return rc;

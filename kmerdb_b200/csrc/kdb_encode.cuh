@@ -3,7 +3,8 @@
 // Replaces the tokenising half of kmer.shred (kmerdb/kmer.py:517-534: alphabet check, N / IUPAC
 // detection, window completeness) and the record bookkeeping of parse.parsefile
 // (kmerdb/parse.py:128-137: seq_lengths).  For every 16 KiB text tile it writes a packed region
-//   [0] n_letters  [1] halo codes  [2] halo N bits  [3] -
+//   [0] n_letters  [1] halo codes  [2] halo N bits  [3] halo W bits (W of the <=15 letters before the tile,
+//       most recent at bit 0: lets K3 derive the W bits of a larger k from this stream, see smear_w)
 //   codes : 2 bits / letter, 16 letters per u32, first letter in the top bits (kmer.py:44-49 codes)
 //   W     : 1 bit / letter — the window ENDING at this letter is complete (k letters of one record)
 //           and free of RYSWKMBDHV; in skip mode (replace_with_none) also free of N
@@ -26,6 +27,7 @@ struct EncodeParams {
     const TileState* tiles;
     unsigned int n_tiles;
     int k, skip_n;
+    int k_halo;                       // >= k: letters of history the tile header carries (largest k counted from this stream)
     uint32_t* packed;                 // n_tiles * kPackStride words
     unsigned long long* rec_len;
     unsigned long long rec_first;
@@ -379,7 +381,7 @@ __global__ void __launch_bounds__(kThreads, 4) k2_encode(const EncodeParams P) {
             if (FASTQ) need_halo = prev != '\n' && kind == 1;
             else if (prev != '\n') need_halo = kind == K_SEQ;
             else need_halo = hdr_before != 0 && byte_at(0) != '>';
-            uint32_t halo_codes = 0, halo_nn = 0;
+            uint32_t halo_codes = 0, halo_nn = 0, halo_w = 0;
             bool walked = false;
             rec0 = rec;
             // k-1 letters before my chunk, read back from the text: only the first thread of a tile, ragged
@@ -389,10 +391,11 @@ __global__ void __launch_bounds__(kThreads, 4) k2_encode(const EncodeParams P) {
                 walked = true;
                 if (!need_halo) return;
                 uint8_t hc[16];
-                const int cnt = halo_classes<FASTQ>(P.text, a, k, hc);
+                const int cnt = halo_classes<FASTQ>(P.text, a, P.k_halo, hc);
                 Emit dummyE; Tally dummyY;
                 for (int i = 0; i < cnt; i++) {
                     track_letter<false>(T, dummyE, dummyY, hc[i], k, kmask, skip_n);
+                    halo_w = (halo_w << 1) | ((T.have >= (uint32_t)k && !(T.nmask && skip_n) && !T.imask) ? 1u : 0u);
                     halo_codes = (halo_codes << 2) | (hc[i] <= C_T ? hc[i] : 0u);
                     halo_nn = (halo_nn << 1) | (hc[i] == C_N ? 1u : 0u);
                 }
@@ -400,7 +403,7 @@ __global__ void __launch_bounds__(kThreads, 4) k2_encode(const EncodeParams P) {
             if (tid == 0 || lim != kChunk) walk();
             if (tid == 0) {
                 uint32_t* hdr = P.packed + (size_t)tile * kPackStride;
-                hdr[1] = halo_codes; hdr[2] = halo_nn; hdr[3] = 0;
+                hdr[1] = halo_codes; hdr[2] = halo_nn; hdr[3] = halo_w;
                 seed.codes = halo_codes; seed.ni = T.nmask | (T.imask << 16); seed.meta = T.have | 0x100; seed.letters = 0;
             }
             unsigned long long len = 0, qlen = 0;

@@ -19,9 +19,23 @@ struct HistParams {
     const uint32_t* packed;
     unsigned int n_tiles;
     int skip_n;
+    int smear;                  // k - (k the packed stream was encoded for): see smear_w
     unsigned int* tab32;
     Accum* acc;
 };
+
+// W bits of a larger k from the W bits of the k the stream was encoded for: a window of k+d letters is complete
+// and clean exactly when the d+1 windows of k letters ending at its last d+1 letters are (k >= 2: consecutive
+// windows overlap, so they lie in one record).  wb holds 32 letters MSB first, prevw the 32 letters before them.
+__device__ __forceinline__ uint32_t smear_w(uint32_t prevw, uint32_t wb, int d) {
+    if (d == 0) return wb;
+    unsigned long long x = ((unsigned long long)prevw << 32) | wb;
+    const uint32_t n = (uint32_t)d + 1;
+    uint32_t w = 1;
+    while (2 * w <= n) { x &= x >> w; w *= 2; }
+    if (n > w) x &= x >> (n - w);
+    return (uint32_t)x;
+}
 
 // reverse complement of 16 packed letters (first letter in the top bits)
 __device__ __forceinline__ uint32_t rc_word(uint32_t x) {
@@ -106,6 +120,7 @@ __global__ void __launch_bounds__(kHistThreads) k3_count(const HistParams P) {
         const uint32_t cur1 = (uint32_t)tid * 32 + 16 < n ? codes[2 * tid + 1] : 0u;
         const uint32_t prev = tid ? codes[2 * tid - 1] : reg[1];
         uint32_t wb = reg[kPackHdr + kPackCodes + tid];
+        if (P.smear) wb = smear_w(tid ? reg[kPackHdr + kPackCodes + tid - 1] : reg[3], wb, P.smear);
         bool generic = false;
         uint32_t nn_cur = 0, nn_prev = 0;
         if (!P.skip_n) {                                   // expansion mode: windows may hold N

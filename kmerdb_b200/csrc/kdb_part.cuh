@@ -30,6 +30,7 @@ struct PartParams {
     const uint32_t* packed;
     unsigned int n_tiles;
     int skip_n;
+    int smear;                   // k - (k the packed stream was encoded for), kdb_hist.cuh smear_w
     unsigned int* tab32;
     uint16_t* stream;            // n_buckets * cap entries
     unsigned int* cursor;        // n_buckets: entries claimed so far
@@ -78,6 +79,7 @@ __global__ void __launch_bounds__(kPartThreads, 2) k3p_partition(const PartParam
             cur1 = (uint32_t)tid * 32 + 16 < n ? codes[2 * tid + 1] : 0u;
             prev = tid ? codes[2 * tid - 1] : reg[1];
             wb = reg[kPackHdr + kPackCodes + tid];
+            if (P.smear) wb = smear_w(tid ? reg[kPackHdr + kPackCodes + tid - 1] : reg[3], wb, P.smear);
             if (!P.skip_n) {
                 const uint32_t* nnw = reg + kPackHdr + kPackCodes + kPackBits;
                 nn_cur = nnw[tid];

@@ -230,28 +230,45 @@ def profile_bytes(data, k, fmt="fasta", replace_with_none=True, canonicalize=Tru
         return Profile(k, p.counts(), st, p.nullomers() if want_nullomers else None, p.timing())
 
 
-def profile_multik(data, min_k, max_k, fmt="fasta", replace_with_none=True, canonicalize=True, device=0, want_nullomers=False):
-    """`--minK/--maxK` sweep (kmerdb/__init__.py:1846-1855) over text held in host memory: the text crosses
-    PCIe once and stays in HBM; every k runs the device kernels on the same resident buffer.
-    Returns {k: Profile}."""
+def iter_profile_multik(data, min_k, max_k, fmt="fasta", replace_with_none=True, canonicalize=True, device=0, want_nullomers=False):
+    """`--minK/--maxK` sweep (kmerdb/__init__.py:1846-1855) over text held in host memory, yielding (k, Profile)
+    for k = min_k .. max_k.  The reference re-parses the file for every k; here the text crosses PCIe once, is
+    scanned and 2-bit encoded once (for min_k), and every larger k is counted from the same packed letter stream
+    (kdb_attach).  Like the reference loop, the sweep raises at the first k that fails, after the smaller k."""
     a = data if isinstance(data, np.ndarray) else np.frombuffer(data, dtype=np.uint8)
-    out = {}
-    buf = _native.DeviceBuffer(a.size + 16, device=device)
+    ks = list(range(min_k, max_k + 1))
+    if not ks:
+        return
+    kw = dict(canonical=canonicalize, skip_n=replace_with_none, fastq=(fmt == "fastq"), device=device)
+    if min_k < 2:                                          # the shared stream needs overlapping windows (k >= 2)
+        yield min_k, profile_bytes(data, min_k, fmt, replace_with_none, canonicalize, device, want_nullomers)
+        yield from iter_profile_multik(data, min_k + 1, max_k, fmt, replace_with_none, canonicalize, device, want_nullomers)
+        return
+    profs = [_native.Profiler(k, **kw) for k in ks]
     try:
-        buf.upload(a)
-        for k in range(min_k, max_k + 1):
-            with _native.Profiler(k, canonical=canonicalize, skip_n=replace_with_none, fastq=(fmt == "fastq"), device=device) as p:
-                p.feed_device(buf.ptr, a.size)
-                status = p.finish()
-                if status == _native.KDB_E_LAYOUT:       # host tokeniser decides (same for every k)
-                    out[k] = profile_bytes(data, k, fmt, replace_with_none, canonicalize, device, want_nullomers)
-                    continue
-                st = p.stats()
-                _raise_for_status(status, st)
-                out[k] = Profile(k, p.counts(), st, p.nullomers() if want_nullomers else None, p.timing())
+        for f in profs[1:]:
+            profs[0].attach(f)
+        profs[0].feed(a)
+        status = profs[0].finish()
+        if status == _native.KDB_E_LAYOUT:                 # host tokeniser decides (same for every k)
+            for p in profs:
+                p.close()
+            for k in ks:
+                yield k, profile_bytes(data, k, fmt, replace_with_none, canonicalize, device, want_nullomers)
+            return
+        for k, p in zip(ks, profs):
+            status = p.finish()
+            st = p.stats()
+            _raise_for_status(status, st)
+            yield k, Profile(k, p.counts(), st, p.nullomers() if want_nullomers else None, p.timing())
     finally:
-        buf.free()
-    return out
+        for p in profs:
+            p.close()
+
+
+def profile_multik(data, min_k, max_k, **kw):
+    """{k: Profile} of iter_profile_multik."""
+    return dict(iter_profile_multik(data, min_k, max_k, **kw))
 
 
 def parsefile(filepath, k, replace_with_none=True, canonicalize=True, device=0, with_mononucleotides=False):

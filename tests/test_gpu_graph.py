@@ -119,6 +119,38 @@ def test_shred_matches_reference_golden(golden):
         assert sids == ["x"] * len(ids)
 
 
+@pytest.mark.parametrize("skip_n", [True, False])
+def test_multik_shared_stream_hard_layouts(skip_n):
+    """The shared-encode sweep (kdb_attach) on inputs where windows cross lines, chunks, tiles and N runs."""
+    rng = np.random.default_rng(77)
+    cases = [(_random_fasta(rng, 120, 40, 30000, 61, alphabet="ACGTN", p=[0.2475, 0.2475, 0.2475, 0.2475, 0.01]), False),
+             (_random_fasta(rng, 300, 16, 600, 0), False),
+             (_random_fastq(rng, 2000, 16, 300), True)]
+    for text, fq in cases:
+        profs = parse.profile_multik(text, 2, 12 if not skip_n else 14, fmt="fastq" if fq else "fasta", replace_with_none=skip_n)
+        for k, pr in profs.items():
+            rc, ocounts, ost = oracle.profile(text, k, fastq=fq, skip_n=skip_n, threads=8)
+            assert rc == 0 and np.array_equal(pr.counts, ocounts), (k, fq)
+            assert (pr.total_kmers, pr.unique_kmers, pr.total_reads, pr.min_read_length, pr.max_read_length) == \
+                   (ost["total_kmers"], ost["unique_kmers"], ost["total_reads"], ost["min_len"], ost["max_len"])
+
+
+def test_multik_sweep_raises_at_the_first_failing_k():
+    text = b">a\nACGTACGTACGTACGT\n>b\nACGTACG\n>c\nACGTTTGACCAGTACA\n"          # record b has 7 letters
+    it = parse.iter_profile_multik(text, 5, 9)
+    got = []
+    with pytest.raises(AttributeError):                     # kmer.py:461-463 at k = 8
+        for k, pr in it:
+            got.append(k)
+            rc, oc, _ = oracle.profile(text, k)
+            assert rc == 0 and np.array_equal(pr.counts, oc)
+    assert got == [5, 6, 7]
+    with pytest.raises(KeyError):
+        parse.profile_multik(b">a\nACGTRCGTACGTACGT\n", 4, 6)
+    with pytest.raises(NameError):
+        parse.profile_multik(b">a\nACGTACGTACGTACGT\n>b\nACGTaCGTACGTACGT\n", 4, 6)
+
+
 def test_multik_sweep_vs_oracle():
     host = _native.synth_host(20000)
     profs = parse.profile_multik(host, 4, 14)
