@@ -309,38 +309,40 @@ __global__ void __launch_bounds__(kThreads, 4) k2_encode(const EncodeParams P) {
     auto word = [&](int i) -> uint32_t { return s_text[16 * tid + 4 * (((uint32_t)i >> 2) ^ swz) + (i & 3)]; };
     auto quad = [&](int q) -> uint4 { return *reinterpret_cast<const uint4*>(s_text + 16 * tid + 4 * ((uint32_t)q ^ swz)); };
     auto byte_at = [&](uint32_t p) -> uint8_t { return (uint8_t)(s_text[16 * tid + 4 * ((p >> 4) ^ swz) + ((p >> 2) & 3)] >> (8 * (p & 3))); };
-    // asynchronous copy of one tile into buffer `b` (16 bytes per request, zero fill past P.hi)
+    // asynchronous copy of my own 64-byte chunk of one tile into buffer `b` (four 16-byte requests, zero fill past
+    // P.hi).  A thread only ever reads the chunk it copied, so cp.async.wait_group is all the synchronisation the text
+    // needs; .ca keeps the 32-byte sectors in L1 between the two requests that share them.
     auto stage = [&](unsigned int tile, int b) {
-        const unsigned long long tile0 = P.lo + (unsigned long long)tile * kTile;
+        const unsigned long long c0 = P.lo + (unsigned long long)tile * kTile + (unsigned long long)tid * kChunk;
 #pragma unroll
         for (int r = 0; r < kChunk / 16; r++) {
-            const uint32_t q = tid + kThreads * r;
-            const unsigned long long g = tile0 + 16ull * q;
-            const uint32_t t = q >> 2, grp = (q & 3) ^ ((t >> 1) & 3);
-            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&s_text2[b][16 * t + 4 * grp]);
+            const unsigned long long g = c0 + 16ull * r;
+            const uint32_t dst = (uint32_t)__cvta_generic_to_shared(&s_text2[b][16 * tid + 4 * ((uint32_t)r ^ swz)]);
             const uint32_t nb = g + 16 <= P.hi ? 16u : (g < P.hi ? (uint32_t)(P.hi - g) : 0u);
             const uint8_t* src = P.text + (nb ? g : P.lo);
-            asm volatile("cp.async.cg.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(nb) : "memory");
+            asm volatile("cp.async.ca.shared.global [%0], [%1], 16, %2;" ::"r"(dst), "l"(src), "r"(nb) : "memory");
         }
         asm volatile("cp.async.commit_group;" ::: "memory");
     };
 
     int buf = 0;
     if (blockIdx.x < P.n_tiles) stage(blockIdx.x, 0);
+    for (int i = tid; i < kPackCodes + 2 * kPackBits; i += kThreads) s_out[i] = 0;
+    __syncthreads();
     for (unsigned int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x, buf ^= 1) {
         const unsigned long long tile0 = P.lo + (unsigned long long)tile * kTile;
-        __syncthreads();                                    // everyone is done with the buffer the next copy overwrites
         // ---- stage: the next tile streams into the other buffer while this one is processed ----------------
         if (tile + gridDim.x < P.n_tiles) { stage(tile + gridDim.x, buf ^ 1); asm volatile("cp.async.wait_group 1;" ::: "memory"); }
         else asm volatile("cp.async.wait_group 0;" ::: "memory");
         s_text = s_text2[buf];
-        for (int i = tid; i < kPackCodes + 2 * kPackBits; i += kThreads) s_out[i] = 0;
-        __syncthreads();
 
         const unsigned long long a = tile0 + (unsigned long long)tid * kChunk;
         const int lim = a >= P.hi ? 0 : (P.hi - a >= (unsigned long long)kChunk ? kChunk : (int)(P.hi - a));
         uint8_t prev = '\n';
-        if (lim > 0 && a > 0) prev = tid > 0 ? (uint8_t)(s_text[16 * (tid - 1) + 4 * (3u ^ (((uint32_t)(tid - 1) >> 1) & 3u)) + 3] >> 24) : P.text[a - 1];
+        {   // last byte of the chunk before mine: from the lane below, or from the text for the first lane of a warp
+            const uint32_t up = __shfl_up_sync(0xffffffffu, word(15) >> 24, 1);
+            if (lim > 0 && a > 0) prev = lane > 0 ? (uint8_t)up : P.text[a - 1];
+        }
 
         // ---- phase A: bit masks of my chunk; phase B: line starts -> CTA scan ---------------------
         const ChunkMasks M = chunk_masks(quad);      // zero fill beyond lim is neither LF nor a letter
@@ -354,15 +356,22 @@ __global__ void __launch_bounds__(kThreads, 4) k2_encode(const EncodeParams P) {
                 while (lsm) { const uint32_t p = __ffsll(lsm) - 1; lsm &= lsm - 1; g.hdr += byte_at(p) == '>' ? 1u : 0u; }
             } else if (lsm) g.last = 1u;
         }
-        LineAgg total;
-        const LineAgg inc = block_scan_inclusive(g, s_scan, &total);
+        // CTA scan with one barrier: warp scans by shuffles, then every warp folds the (<= 8) warp totals below it itself
+        LineAgg inc = g, warp_pre{0, 0, 0};
+#pragma unroll
+        for (int d = 1; d < 32; d <<= 1) { const LineAgg o = shfl_up_agg(inc, d); if (lane >= d) inc = combine(o, inc); }
+        if (lane == 31) s_scan[warp] = inc;
+        __syncthreads();
+#pragma unroll
+        for (int w = 0; w < kThreads / 32; w++) { const LineAgg t = s_scan[w]; if (w < warp) warp_pre = combine(warp_pre, t); }
+        inc = combine(warp_pre, inc);
         const TileState ts = P.tiles[tile];
         const unsigned long long ls_before = ts.ls_base + (inc.ls - g.ls);
         unsigned long long hdr_before = ts.hdr_base + (inc.hdr - g.hdr);
         unsigned int last_before;
         {
             LineAgg e = shfl_up_agg(inc, 1);
-            if (lane == 0) e = warp ? s_scan[warp - 1] : LineAgg{0, 0, 0};
+            if (lane == 0) e = warp_pre;
             last_before = e.last ? e.last : ts.last;
         }
 
@@ -582,10 +591,11 @@ __global__ void __launch_bounds__(kThreads, 4) k2_encode(const EncodeParams P) {
             uint32_t* dst = P.packed + (size_t)tile * kPackStride;
             if (tid == 0) dst[0] = tile_letters;
             const uint32_t cw = (tile_letters + 15) >> 4, bw = (tile_letters + 31) >> 5;
-            for (uint32_t i = tid; i < cw; i += kThreads) dst[kPackHdr + i] = s_out[i];
+            // (the words are cleared as they leave: the next tile ORs into them after its own scans' barriers)
+            for (uint32_t i = tid; i < cw; i += kThreads) { dst[kPackHdr + i] = s_out[i]; s_out[i] = 0; }
             for (uint32_t i = tid; i < bw; i += kThreads) {
-                dst[kPackHdr + kPackCodes + i] = s_out[kPackCodes + i];
-                dst[kPackHdr + kPackCodes + kPackBits + i] = s_out[kPackCodes + kPackBits + i];
+                dst[kPackHdr + kPackCodes + i] = s_out[kPackCodes + i]; s_out[kPackCodes + i] = 0;
+                dst[kPackHdr + kPackCodes + kPackBits + i] = s_out[kPackCodes + kPackBits + i]; s_out[kPackCodes + kPackBits + i] = 0;
             }
         }
     }

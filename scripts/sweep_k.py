@@ -32,3 +32,25 @@ for k in range(kmin, kmax + 1):
         print(json.dumps(rows[-1]), flush=True)
 os.makedirs("gpurun_out", exist_ok=True)
 json.dump({"n_reads": n, "rows": rows}, open("gpurun_out/sweep_k.json", "w"), indent=1)
+
+# ---- the same sweep with one scan + encode for all k (kdb_attach) ------------------------------------------
+import time
+profs = [_native.Profiler(k) for k in range(kmin, kmax + 1)]
+for f in profs[1:]:
+    profs[0].attach(f)
+best = None
+for it in range(4):
+    profs[0].reset()
+    t0 = time.perf_counter()
+    profs[0].feed_device(buf.ptr, n * rb)
+    for p in profs:
+        assert p.finish() == 0
+    dt = time.perf_counter() - t0
+    if it and (best is None or dt < best):
+        best = dt
+for k, p in zip(range(kmin, kmax + 1), profs):
+    assert p.stats()["total_kmers"] == n * (150 - k + 1) and p.stats()["unique_kmers"] == rows[k - kmin]["unique"]
+shared = {"wall_ms": 1e3 * best, "sum_of_separate_jobs_ms": sum(r["job_ms"] for r in rows),
+          "leader": profs[0].timing(), "followers_count_ms": {k: p.timing()["count_ms"] for k, p in zip(range(kmin + 1, kmax + 1), profs[1:])}}
+print(json.dumps(shared), flush=True)
+json.dump({"n_reads": n, "rows": rows, "shared_sweep": shared}, open("gpurun_out/sweep_k.json", "w"), indent=1)
