@@ -150,6 +150,15 @@ int kdb_edge_weights(kdb_ctx* ctx, int canonical, uint64_t* n1, uint64_t* n2, ui
 int kdb_minimizers_compat(int device, const uint8_t* seq, size_t len, int k, uint64_t window, uint64_t* ids, uint8_t* is_min, size_t cap, size_t* n_rows);
 int kdb_minimizers(int device, const uint8_t* seq, size_t len, int k, int w, uint64_t* pos, uint64_t* ids, size_t cap, size_t* n);
 
+/* ---- .kdb body rows (kmerdb/__init__.py:1980-1990) ------------------------------------------
+ * Rows "i\ti\tcount\tfrequency\n" for i = first_row .. first_row + n_rows - 1 (counts[j] belongs to row first_row + j),
+ * assembled on the GPU.  The text "count\tfrequency" of every DISTINCT count value comes from the caller
+ * (uniq_vals ascending; string u = str_bytes[str_off[u] .. str_off[u+1])), formatted exactly as the reference
+ * formats np.uint64 and np.float64, so the rows are byte-identical to the reference's.  *n_bytes receives the size
+ * of the text; call with out = NULL to size the buffer.  All pointers are host pointers. */
+int kdb_format_rows(int device, const uint64_t* counts, uint64_t first_row, uint64_t n_rows, const uint64_t* uniq_vals,
+                    const uint32_t* str_off, const char* str_bytes, size_t n_uniq, char* out, size_t cap, size_t* n_bytes);
+
 /* Synthetic benchmark input: n_reads records of read_len i.i.d. uniform ACGT letters,
  * FASTA framing ">%09d\n" + letters + "\n" (or FASTQ framing), written straight into HBM.
  * read index = first_read + i; counter-based generator, reproducible on the host

@@ -19,7 +19,7 @@ EXPORTS = [
     "kdb_reset", "kdb_timing", "kdb_kmer_to_id_batch", "kdb_synth_record_bytes", "kdb_synth_device",
     "kdb_synth_host", "kdb_microbench_atomics", "kdb_dev_alloc", "kdb_dev_free", "kdb_host_alloc_pinned",
     "kdb_host_free_pinned", "kdb_memcpy_h2d", "kdb_memcpy_d2h",
-    "kdb_edge_rows", "kdb_edge_weights", "kdb_minimizers_compat", "kdb_minimizers", "kdb_attach",
+    "kdb_edge_rows", "kdb_edge_weights", "kdb_minimizers_compat", "kdb_minimizers", "kdb_attach", "kdb_format_rows",
 ]
 
 
@@ -65,7 +65,8 @@ def lib():
         ("kdb_nullomers", [vp, vp, sz, ctypes.POINTER(sz)]),
         ("kdb_device_table", [vp, ctypes.POINTER(vp), ctypes.POINTER(sz)]),
         ("kdb_export_partials", [vp, vp]), ("kdb_import_partials", [vp, vp]), ("kdb_refinalize", [vp]),
-        ("kdb_attach", [vp, vp]), ("kdb_reset", [vp]), ("kdb_timing", [vp, ctypes.POINTER(Timing)]),
+        ("kdb_attach", [vp, vp]),
+        ("kdb_format_rows", [ci, vp, u64, u64, vp, vp, vp, sz, vp, sz, ctypes.POINTER(sz)]), ("kdb_reset", [vp]), ("kdb_timing", [vp, ctypes.POINTER(Timing)]),
         ("kdb_kmer_to_id_batch", [ci, ctypes.c_char_p, sz, ci, ci, vp]),
         ("kdb_synth_device", [ci, vp, u64, u64, ci, ci, u64]), ("kdb_synth_host", [vp, u64, u64, ci, ci, u64]),
         ("kdb_microbench_atomics", [ci, sz, u64, ci, ctypes.POINTER(ctypes.c_double)]),
@@ -337,3 +338,19 @@ def minimizers(seq, k, w, device=0):
     if rc in (KDB_E_CUDA, KDB_E_ARG):
         raise NativeError("kdb_minimizers failed (%d): %s" % (rc, _err()))
     return rc, pos[:n.value], ids[:n.value]
+
+
+def format_rows(counts, first_row, uniq_vals, str_off, str_bytes, device=0):
+    """kdb_format_rows: the .kdb body text (uint8 array) of rows first_row .. first_row + len(counts) - 1."""
+    c = np.ascontiguousarray(counts, dtype=np.uint64)
+    u = np.ascontiguousarray(uniq_vals, dtype=np.uint64)
+    so = np.ascontiguousarray(str_off, dtype=np.uint32)
+    sb = np.frombuffer(str_bytes, dtype=np.uint8)
+    n = ctypes.c_size_t()
+    args = (device, c.ctypes.data, int(first_row), c.size, u.ctypes.data, so.ctypes.data, sb.ctypes.data, u.size)
+    if lib().kdb_format_rows(*args, None, 0, ctypes.byref(n)):
+        raise NativeError("kdb_format_rows: " + _err())
+    out = np.empty(n.value, dtype=np.uint8)
+    if n.value and lib().kdb_format_rows(*args, out.ctypes.data, out.size, ctypes.byref(n)):
+        raise NativeError("kdb_format_rows: " + _err())
+    return out

@@ -54,7 +54,7 @@ def _profile(args, k, files, precomputed=None):
     if args.sorted:
         sys.stderr.write("--sorted is broken in kmerdb v0.9.6 (undefined names at kmerdb/__init__.py:1974-1975); rows are written in id order\n")
     out = "{0}.{1}.kdb".format(args.output_name, k)                 # __init__.py:1954
-    kdbfile.write_kdb(out, metadata, counts, quiet=args.quiet)
+    kdbfile.write_kdb_gpu(out, metadata, counts, device=args.device, quiet=args.quiet)
     sys.stderr.write("\n\n\nFinal stats:\n\n\n")
     sys.stderr.write("Total k-mers processed: {0}\n".format(total))
     sys.stderr.write("Unique nullomer count:   {0}\n".format(unique_nullomers))

@@ -18,6 +18,7 @@
 #include "kdb_final.cuh"
 #include "kdb_synth.cuh"
 #include "kdb_graph.cuh"
+#include "kdb_rows.cuh"
 
 using namespace kdb;
 
@@ -955,5 +956,42 @@ extern "C" int kdb_minimizers(int device, const uint8_t* seq, size_t len, int k,
     CK(cudaGetLastError());
     CK(cudaMemcpy(pos, o, m * 8, cudaMemcpyDeviceToHost));
     CK(cudaMemcpy(ids, o + m, m * 8, cudaMemcpyDeviceToHost));
+    return KDB_OK;
+}
+
+// ---- K9: .kdb body rows (kdb_rows.cuh) ---------------------------------------------------------------------
+extern "C" int kdb_format_rows(int device, const uint64_t* counts, uint64_t first_row, uint64_t n_rows, const uint64_t* uniq_vals,
+                               const uint32_t* str_off, const char* str_bytes, size_t n_uniq, char* out, size_t cap, size_t* n_bytes) {
+    kdb_ctx* ctx = nullptr;
+    if (!counts || !uniq_vals || !str_off || !str_bytes || !n_bytes || n_uniq == 0 || n_uniq > 0x7fffffffull) return KDB_E_ARG;
+    *n_bytes = 0;
+    if (n_rows == 0) return KDB_OK;
+    CK(cudaSetDevice(device));
+    const unsigned int blocks = (unsigned int)((n_rows + kRowBlock - 1) / kRowBlock);
+    const size_t str_total = str_off[n_uniq];
+    DevBuf d_counts, d_uniq, d_soff, d_str, d_idx, d_blen, d_boff, d_bad, d_out;
+    CK(d_counts.alloc(n_rows * 8)); CK(d_uniq.alloc(n_uniq * 8)); CK(d_soff.alloc((n_uniq + 1) * 4)); CK(d_str.alloc(str_total));
+    CK(d_idx.alloc(n_rows * 4)); CK(d_blen.alloc(blocks * 4)); CK(d_bad.alloc(4));
+    CK(cudaMemcpy(d_counts.p, counts, n_rows * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_uniq.p, uniq_vals, n_uniq * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_soff.p, str_off, (n_uniq + 1) * 4, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_str.p, str_bytes, str_total, cudaMemcpyHostToDevice));
+    CK(cudaMemset(d_bad.p, 0, 4));
+    k9_row_len<<<blocks, kRowBlock>>>(d_counts.as<unsigned long long>(), first_row, n_rows, d_uniq.as<unsigned long long>(), d_soff.as<unsigned int>(),
+                                      (unsigned int)n_uniq, d_idx.as<unsigned int>(), d_blen.as<unsigned int>(), d_bad.as<unsigned int>());
+    CK(cudaGetLastError());
+    unsigned int bad = 0;
+    CK(cudaMemcpy(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost));
+    if (bad) { g_last_error = (bad & 1) ? "kdb_format_rows: a count is missing from the string table" : "kdb_format_rows: a row exceeds 96 bytes"; return KDB_E_ARG; }
+    unsigned long long total = 0;
+    if (int rc = scan_blocks(ctx, d_blen.as<unsigned int>(), blocks, d_boff, &total)) return rc;
+    *n_bytes = (size_t)total;
+    if (!out) return KDB_OK;
+    if (cap < total) { g_last_error = "kdb_format_rows: output buffer too small"; return KDB_E_ARG; }
+    CK(d_out.alloc(total));
+    k9_row_write<<<blocks, kRowBlock>>>(first_row, n_rows, d_idx.as<unsigned int>(), d_soff.as<unsigned int>(), d_str.as<char>(),
+                                        d_boff.as<unsigned long long>(), d_out.as<char>());
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(out, d_out.p, total, cudaMemcpyDeviceToHost));
     return KDB_OK;
 }

@@ -47,8 +47,48 @@ def format_rows(start, counts, total_kmers):
     return "".join(["%d\t%d\t%d\t%r\n" % (i, i, c, f) for i, c, f in zip(ids, counts.tolist(), freq.tolist())]).encode("ascii")
 
 
+def count_strings(counts, total_kmers):
+    """The text "count\tfrequency" of every distinct count value (ascending), as the reference's str.format prints
+    np.uint64 and np.float64 (kmerdb/__init__.py:1945, :1990).  Returns (uniq uint64, str_off uint32, bytes)."""
+    mx = int(counts.max()) if len(counts) else 0
+    if mx < (1 << 24):
+        uniq = np.flatnonzero(np.bincount(counts.astype(np.int64), minlength=1)).astype(np.uint64)
+    else:
+        uniq = np.unique(counts)
+    tot = float(total_kmers)
+    strs = [("%d\t%r" % (c, (c / tot) if tot else float("nan"))).encode("ascii") for c in uniq.tolist()]
+    off = np.zeros(len(strs) + 1, dtype=np.uint32)
+    off[1:] = np.cumsum([len(x) for x in strs])
+    return uniq, off, b"".join(strs)
+
+
+def write_kdb_gpu(path, metadata, counts, device=0, threads=8, quiet=True, rows_per_call=1 << 22):
+    """write_kdb with the rows assembled on the GPU (kdb_format_rows); BGZF deflate on host threads."""
+    from . import _native
+    head, md = header_bytes(metadata)
+    uniq, off, blob = count_strings(counts, md["total_kmers"])
+
+    def deflate(buf):
+        return b"".join(bgzf_block(bytes(buf[o:o + _BLOCK])) for o in range(0, len(buf), _BLOCK))
+
+    with open(path, "wb") as fh:
+        for o in range(0, len(head), 65536):
+            fh.write(bgzf_block(head[o:o + 65536]))
+        with ThreadPoolExecutor(max_workers=threads) as ex:
+            for lo in range(0, len(counts), rows_per_call):
+                text = _native.format_rows(counts[lo:lo + rows_per_call], lo, uniq, off, blob, device=device)
+                if not quiet:
+                    sys.stdout.write(text.tobytes().decode("ascii"))
+                step = _BLOCK * 32
+                mv = memoryview(text)
+                for blobz in ex.map(deflate, [mv[o:o + step] for o in range(0, len(text), step)]):
+                    fh.write(blobz)
+        fh.write(_BGZF_EOF)
+    return md
+
+
 def write_kdb(path, metadata, counts, threads=8, quiet=True, rows_per_task=1 << 15):
-    """Write `<path>`: header block(s), 4^k rows, BGZF EOF marker."""
+    """Write `<path>`: header block(s), 4^k rows, BGZF EOF marker (rows formatted on the host)."""
     head, md = header_bytes(metadata)
     total = md["total_kmers"]
     n = len(counts)

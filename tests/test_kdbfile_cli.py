@@ -76,3 +76,32 @@ def test_cli_profile_graph_end_to_end(tmp_path):
     cli.cli(["graph", "-k", "5", "--quiet", fa, str(tmp_path / "g.kdbg")])
     body = gzip.open(str(tmp_path / "g.kdbg"), "rt").read().split(kdbfile.HEADER_DELIMITER)[1].splitlines()
     assert len(body) == 50 * (90 - 5) and body[0].split("\t")[:3] == ["0", "r0", "0"] and len(body[0].split("\t")) == 8
+
+
+@pytest.mark.gpu
+def test_gpu_rows_are_byte_identical_to_host_rows(tmp_path):
+    """kdb_format_rows (GPU) against the host formatter, which itself is checked against str.format of numpy scalars."""
+    import time
+    rng = np.random.default_rng(3)
+    for k, hi in ((6, 5), (9, 3000), (12, 200)):
+        counts = rng.integers(0, hi, size=4 ** k).astype(np.uint64)
+        counts[rng.integers(0, 4 ** k, size=7)] = np.array([0, 1, 2 ** 31, 2 ** 40 + 7, 10 ** 15, 999999, 1000000], dtype=np.uint64)
+        total = int(counts.sum())
+        md = {"version": "0.9.6", "metadata_blocks": 1, "k": k, "total_kmers": total, "unique_kmers": int(np.count_nonzero(counts)),
+              "unique_nullomers": 0, "sorted": False, "tags": [], "files": []}
+        t0 = time.perf_counter()
+        kdbfile.write_kdb_gpu(str(tmp_path / "g.kdb"), md, counts)
+        t1 = time.perf_counter()
+        g = gzip.open(str(tmp_path / "g.kdb"), "rb").read()
+        if k <= 9:
+            kdbfile.write_kdb(str(tmp_path / "h.kdb"), md, counts)
+            assert g == gzip.open(str(tmp_path / "h.kdb"), "rb").read()
+        else:
+            body = g.split(kdbfile.HEADER_DELIMITER.encode())[1]
+            lo, n = 4 ** k - 5000, 5000
+            assert body.endswith(kdbfile.format_rows(lo, counts[lo:], total)) and body.startswith(kdbfile.format_rows(0, counts[:n], total))
+            assert body.count(b"\n") == 4 ** k
+            print("k=%d: %d rows, %.1f MB of text, written in %.2f s" % (k, 4 ** k, len(body) / 1e6, t1 - t0))
+    z = np.zeros(256, dtype=np.uint64)                                  # all-zero profile: 0/0 prints as nan, like np.divide
+    uniq, off, blob = kdbfile.count_strings(z, 0)
+    assert blob == b"0\tnan"
