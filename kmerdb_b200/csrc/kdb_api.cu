@@ -64,6 +64,7 @@ struct kdb_ctx {
     unsigned long long carry_rec_id = 0, fq_rec_base = 0;
     unsigned long long bytes_since_fold = 0;
     bool job_started = false, finished = false, host_layout = false;
+    bool tab64_valid = false;                   // tab64 holds folded counts (it is not zeroed at reset: the first fold writes it)
     int count_grid = 0;
     kdb_stats_t stats{};
     kdb_timing_t timing{};
@@ -138,7 +139,6 @@ extern "C" void kdb_destroy(kdb_ctx* ctx) {
 static int reset_state(kdb_ctx* ctx) {
     CK(cudaEventRecord(ctx->ev_job0, ctx->s_compute));   // a job starts with zeroing its tables
     CK(cudaMemsetAsync(ctx->tab32, 0, ctx->nbins * sizeof(unsigned int), ctx->s_compute));
-    CK(cudaMemsetAsync(ctx->tab64, 0, ctx->nbins * sizeof(unsigned long long), ctx->s_compute));
     Accum a{};
     a.min_len = ~0ull; a.err_key = ~0ull;
     CK(cudaMemcpyAsync(ctx->acc, &a, sizeof a, cudaMemcpyHostToDevice, ctx->s_compute));
@@ -147,7 +147,7 @@ static int reset_state(kdb_ctx* ctx) {
     CK(cudaStreamSynchronize(ctx->s_compute));
     ctx->h_carry = ScanCarry{};
     ctx->have_carry = false; ctx->carry_rec_id = 0; ctx->fq_rec_base = 0; ctx->bytes_since_fold = 0;
-    ctx->job_started = true; ctx->finished = false; ctx->host_layout = false;
+    ctx->job_started = true; ctx->finished = false; ctx->host_layout = false; ctx->tab64_valid = false;
     ctx->stats = kdb_stats_t{}; ctx->timing = kdb_timing_t{};
     return KDB_OK;
 }
@@ -241,20 +241,33 @@ static int ensure(kdb_ctx* ctx, void** p, size_t* cap, size_t need, size_t elem)
     return KDB_OK;
 }
 
-static int fold_now(kdb_ctx* ctx) {
-    if (ctx->bytes_since_fold == 0) return KDB_OK;
-    CK(cudaEventRecord(ctx->ev[4], ctx->s_compute));
+// tab64 += tab32 (or tab64 = tab32 for the first fold of a job), tab32 = 0.  count_unique: the fold that ends the
+// job also counts the non-zero bins (acc->unique must be zero before).
+static int fold_now(kdb_ctx* ctx, bool count_unique = false, cudaStream_t st = nullptr) {
+    if (!st) st = ctx->s_compute;
+    if (ctx->bytes_since_fold == 0 && !(count_unique || !ctx->tab64_valid)) return KDB_OK;
+    if (ctx->bytes_since_fold == 0 && !ctx->tab64_valid) {      // nothing was counted: the result is all zeros
+        CK(cudaMemsetAsync(ctx->tab64, 0, ctx->nbins * sizeof(unsigned long long), st));
+        ctx->tab64_valid = true;
+        if (!count_unique) return KDB_OK;
+    }
+    CK(cudaEventRecord(ctx->ev[4], st));
     const unsigned long long quads = (ctx->nbins + 3) / 4;
     const int grid = (int)std::min<unsigned long long>((quads + 255) / 256, 148ull * 16);
-    k3_fold<<<grid, 256, 0, ctx->s_compute>>>(ctx->tab32, ctx->tab64, ctx->nbins);
+    const bool first = !ctx->tab64_valid;
+    if (first && count_unique) k3_fold_final<true, true><<<grid, 256, 0, st>>>(ctx->tab32, ctx->tab64, ctx->nbins, ctx->acc);
+    else if (first) k3_fold_final<true, false><<<grid, 256, 0, st>>>(ctx->tab32, ctx->tab64, ctx->nbins, ctx->acc);
+    else if (count_unique) k3_fold_final<false, true><<<grid, 256, 0, st>>>(ctx->tab32, ctx->tab64, ctx->nbins, ctx->acc);
+    else k3_fold<<<grid, 256, 0, st>>>(ctx->tab32, ctx->tab64, ctx->nbins);
     CK(cudaGetLastError());
-    CK(cudaEventRecord(ctx->ev[5], ctx->s_compute));
+    CK(cudaEventRecord(ctx->ev[5], st));
     CK(cudaEventSynchronize(ctx->ev[5]));
     float ms = 0;
     CK(cudaEventElapsedTime(&ms, ctx->ev[4], ctx->ev[5]));
     ctx->timing.fold_ms += ms;
     ctx->timing.total_launches++;
     ctx->bytes_since_fold = 0;
+    ctx->tab64_valid = true;
     return KDB_OK;
 }
 
@@ -275,12 +288,7 @@ static int close_carry_record(kdb_ctx* ctx) {
 static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigned long long lo, unsigned long long hi) {
     const int smear = ctx->k - src->k;
     cudaStream_t st = src->s_compute;
-    if (ctx != src && ctx->bytes_since_fold + (hi - lo) > 0x7fffffffull) {
-        const unsigned long long quads = (ctx->nbins + 3) / 4;
-        k3_fold<<<(int)std::min<unsigned long long>((quads + 255) / 256, 148ull * 16), 256, 0, st>>>(ctx->tab32, ctx->tab64, ctx->nbins);
-        CK(cudaGetLastError());
-        ctx->bytes_since_fold = 0;
-    }
+    if (ctx != src && ctx->bytes_since_fold + (hi - lo) > 0x7fffffffull) if (int rc = fold_now(ctx, false, st)) return rc;
     if (ctx->partitioned) {
         // every window ends on a text byte, so (hi - lo) bounds the entries of the pass; canonical ids of
         // uniform sequence load the lowest bucket with 2x the average, hence the 3x head room
@@ -506,8 +514,8 @@ static int finish_follower(kdb_ctx* ctx) {
     if (!L->finished) { ctx->err = "kdb_finish on a follower before its leader"; return KDB_E_STATE; }
     CK(cudaStreamSynchronize(L->s_compute));
     CK(cudaEventRecord(ctx->ev[0], ctx->s_compute));
-    if (int rc = fold_now(ctx)) return rc;
-    if (int rc = compute_unique(ctx)) return rc;
+    CK(cudaMemsetAsync(&ctx->acc->unique, 0, sizeof(unsigned long long), ctx->s_compute));
+    if (int rc = fold_now(ctx, true)) return rc;
     CK(cudaEventRecord(ctx->ev[1], ctx->s_compute));
     if (int rc = fill_stats(ctx)) return rc;
     float ms = 0;
@@ -532,8 +540,8 @@ extern "C" int kdb_finish(kdb_ctx* ctx) {
     if (!ctx->job_started) { CK(cudaEventRecord(ctx->ev_job0, ctx->s_compute)); ctx->job_started = true; }
     CK(cudaEventRecord(ctx->ev[0], ctx->s_compute));
     if (int rc = close_carry_record(ctx)) return rc;
-    if (int rc = fold_now(ctx)) return rc;
-    if (int rc = compute_unique(ctx)) return rc;
+    CK(cudaMemsetAsync(&ctx->acc->unique, 0, sizeof(unsigned long long), ctx->s_compute));
+    if (int rc = fold_now(ctx, true)) return rc;
     CK(cudaEventRecord(ctx->ev[1], ctx->s_compute));
     CK(cudaEventRecord(ctx->ev_job1, ctx->s_compute));
     if (int rc = fill_stats(ctx)) return rc;

@@ -27,6 +27,39 @@ __global__ void __launch_bounds__(256) k3_fold(unsigned int* __restrict__ tab32,
     }
 }
 
+// The fold that ends a job: FIRST = tab64 holds nothing yet (it is written, not read: no zeroing pass, no read);
+// COUNT = also count the non-zero bins of the result (unique_kmers, parse.py:141) so the table is not read again.
+template <bool FIRST, bool COUNT>
+__global__ void __launch_bounds__(256) k3_fold_final(unsigned int* __restrict__ tab32, unsigned long long* __restrict__ tab64,
+                                                     unsigned long long nbins, Accum* acc) {
+    unsigned long long nz = 0;
+    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x * 4;
+    for (unsigned long long i = ((unsigned long long)blockIdx.x * blockDim.x + threadIdx.x) * 4; i < nbins; i += stride) {
+        if (i + 4 <= nbins) {
+            const uint4 v = *reinterpret_cast<uint4*>(tab32 + i);
+            ulonglong2 a = make_ulonglong2(0, 0), b = make_ulonglong2(0, 0);
+            if (!FIRST) { a = *reinterpret_cast<ulonglong2*>(tab64 + i); b = *reinterpret_cast<ulonglong2*>(tab64 + i + 2); }
+            a.x += v.x; a.y += v.y; b.x += v.z; b.y += v.w;
+            if (FIRST || (v.x | v.y | v.z | v.w)) {
+                *reinterpret_cast<ulonglong2*>(tab64 + i) = a;
+                *reinterpret_cast<ulonglong2*>(tab64 + i + 2) = b;
+            }
+            if (v.x | v.y | v.z | v.w) *reinterpret_cast<uint4*>(tab32 + i) = make_uint4(0, 0, 0, 0);
+            if (COUNT) nz += (a.x != 0) + (a.y != 0) + (b.x != 0) + (b.y != 0);
+        } else {
+            for (unsigned long long j = i; j < nbins; j++) {
+                const unsigned long long x = (FIRST ? 0ull : tab64[j]) + tab32[j];
+                tab64[j] = x; tab32[j] = 0;
+                if (COUNT) nz += x != 0;
+            }
+        }
+    }
+    if (COUNT) {
+        for (int d = 16; d; d >>= 1) nz += __shfl_xor_sync(0xffffffffu, nz, d);
+        if ((threadIdx.x & 31) == 0 && nz) atomicAdd(&acc->unique, nz);
+    }
+}
+
 // Records [0, n_complete) of rec_len are closed: min / max length, short-record raise, and for
 // FASTQ the sequence/quality length agreement (Bio.SeqIO raises ValueError otherwise -> host).
 template <bool FASTQ>
