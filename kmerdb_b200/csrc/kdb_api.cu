@@ -301,7 +301,7 @@ static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigne
         PartParams Q{};
         Q.packed = src->packed; Q.n_tiles = n_tiles; Q.skip_n = ctx->skip_n; Q.smear = smear; Q.tab32 = ctx->tab32; Q.stream = ctx->stream;
         Q.cursor = ctx->cursor; Q.fail_base = ctx->cursor + ctx->n_buckets; Q.cap = cap; Q.acc = ctx->acc;
-        const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->part_grid);
+        const int grid = (int)std::min<unsigned int>((n_tiles + 1) / 2, (unsigned int)ctx->part_grid);   // work unit = two tiles
         ctx->part_kernel<<<grid, kPartThreads, k3p_smem_bytes(ctx->k), st>>>(Q);
         CK(cudaGetLastError());
         CK(cudaEventRecord(ctx->ev[7], st));

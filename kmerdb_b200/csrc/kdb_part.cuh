@@ -61,29 +61,40 @@ __global__ void __launch_bounds__(kPartThreads, 2) k3p_partition(const PartParam
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long kmers = 0;
 
-    for (unsigned int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
-        const uint32_t* reg = P.packed + (size_t)tile * kPackStride;
-        const uint32_t n = reg[0];
+    // Work unit = two consecutive packed tiles.  Tiles that are at most half full (FASTQ: half of the text is quality
+    // lines) share one sort pass — tile A on threads 0..255, tile B on threads 256..511 — so the per-pass costs (bucket
+    // histogram, scan, cursor bumps) and the stream runs do not degrade with sparse tiles.
+    const unsigned int n_units = (P.n_tiles + 1) / 2;
+    for (unsigned int unit = blockIdx.x; unit < n_units; unit += gridDim.x)
+    for (int half = 0; half < 2; half++) {
+        const unsigned int tA = 2 * unit, tB = tA + 1;
+        const uint32_t nA = P.packed[(size_t)tA * kPackStride], nB = tB < P.n_tiles ? P.packed[(size_t)tB * kPackStride] : 0u;
+        const bool both = nA <= kTile / 2 && nB <= kTile / 2;
+        if (half == 1 && (both || tB >= P.n_tiles)) break;
+        const bool onB = both ? tid >= kPartThreads / 2 : half == 1;
+        const int ltid = both ? (tid & (kPartThreads / 2 - 1)) : tid;
+        const uint32_t* reg = P.packed + (size_t)(onB ? tB : tA) * kPackStride;
+        const uint32_t n = onB ? nB : nA;
         __syncthreads();
         for (int i = tid; i < NB; i += kPartThreads) s_hist[i] = 0;
         __syncthreads();
 
         // ---- phase 1: ids of my 32 letters, rank inside their bucket ------------------------------
         uint32_t item[32];                                           // id | rank << 2K, or ~0 = nothing to store
-        const bool active = (uint32_t)tid * 32 < n;
+        const bool active = (uint32_t)ltid * 32 < n;
         bool generic = false;
         uint32_t cur0 = 0, cur1 = 0, prev = 0, wb = 0, nn_cur = 0, nn_prev = 0;
         if (active) {
             const uint32_t* codes = reg + kPackHdr;
-            cur0 = codes[2 * tid];
-            cur1 = (uint32_t)tid * 32 + 16 < n ? codes[2 * tid + 1] : 0u;
-            prev = tid ? codes[2 * tid - 1] : reg[1];
-            wb = reg[kPackHdr + kPackCodes + tid];
-            if (P.smear) wb = smear_w(tid ? reg[kPackHdr + kPackCodes + tid - 1] : reg[3], wb, P.smear);
+            cur0 = codes[2 * ltid];
+            cur1 = (uint32_t)ltid * 32 + 16 < n ? codes[2 * ltid + 1] : 0u;
+            prev = ltid ? codes[2 * ltid - 1] : reg[1];
+            wb = reg[kPackHdr + kPackCodes + ltid];
+            if (P.smear) wb = smear_w(ltid ? reg[kPackHdr + kPackCodes + ltid - 1] : reg[3], wb, P.smear);
             if (!P.skip_n) {
                 const uint32_t* nnw = reg + kPackHdr + kPackCodes + kPackBits;
-                nn_cur = nnw[tid];
-                nn_prev = tid ? nnw[tid - 1] : reg[2];
+                nn_cur = nnw[ltid];
+                nn_prev = ltid ? nnw[ltid - 1] : reg[2];
                 generic = (nn_cur | (nn_prev & ((1u << (K - 1)) - 1u))) != 0;
             }
         }
