@@ -57,13 +57,57 @@ def checksum(filepath):
     return md5.hexdigest(), sha.hexdigest()
 
 
-def _read_text_bytes(filepath):
+def _bgzf_blocks(raw):
+    """Offsets of the members of a BGZF file (gzip members whose extra field carries their size, e.g. written by
+    bgzip), or None when `raw` is ordinary gzip."""
+    out, off, n = [], 0, len(raw)
+    while off < n:
+        if n - off < 18 or raw[off:off + 4] != b"\x1f\x8b\x08\x04" or raw[off + 12:off + 16] != b"BC\x02\x00":
+            return None
+        size = int.from_bytes(raw[off + 16:off + 18], "little") + 1
+        out.append((off, size))
+        off += size
+    return out if off == n else None
+
+
+def _gunzip(raw, threads=8):
+    """Host gzip decode (kmerdb/parse.py:63-68 uses gzip.open).  Block-compressed input (BGZF) is inflated on a
+    thread pool, one member per task; plain gzip goes through zlib in one piece.  Same bytes either way."""
+    import zlib
+    blocks = _bgzf_blocks(raw) if len(raw) > (1 << 20) else None
+    if not blocks:
+        return gzip.decompress(raw)
+    from concurrent.futures import ThreadPoolExecutor
+    mv = memoryview(raw)
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        parts = list(ex.map(lambda b: zlib.decompress(mv[b[0] + 18:b[0] + b[1] - 8], -15), blocks))
+    return b"".join(parts)
+
+
+def _read_text_bytes(filepath, raw=None):
     """Uncompressed file text (host gzip decode, as in kmerdb/parse.py:63-68)."""
-    if is_gz_file(filepath):
-        with gzip.open(filepath, "rb") as fh:
-            return fh.read()
-    with open(filepath, "rb") as fh:
-        return fh.read()
+    if raw is None:
+        with open(filepath, "rb") as fh:
+            raw = fh.read()
+    if raw[:2] == b"\x1f\x8b" and is_gz_file(filepath):
+        return _gunzip(raw)
+    return raw
+
+
+def _checksums_async(raw):
+    """md5 and sha256 of the raw file bytes (kmerdb/util.py:35-50) on two host threads (hashlib releases the GIL), so
+    they run beside the H2D copy and the kernels instead of in front of them.  Returns a callable giving (md5, sha256)."""
+    from concurrent.futures import ThreadPoolExecutor
+    ex = ThreadPoolExecutor(max_workers=2)
+    f1 = ex.submit(lambda: hashlib.md5(raw).hexdigest())
+    f2 = ex.submit(lambda: hashlib.sha256(raw).hexdigest())
+
+    def result():
+        try:
+            return f1.result(), f2.result()
+        finally:
+            ex.shutdown(wait=True)
+    return result
 
 
 def _file_format(filepath):
@@ -283,10 +327,15 @@ def parsefile(filepath, k, replace_with_none=True, canonicalize=True, device=0, 
         raise TypeError("kmerdb.parse.parsefile expects an int as its second positional argument")
     elif type(replace_with_none) is not bool:
         raise TypeError("kmerdb.parse.parsefile expects the keyword argument 'replace_with_none' to be a bool")
-    md5, sha256 = checksum(filepath)
-    data = _read_text_bytes(filepath)
-    fmt = _file_format(filepath)
-    prof = profile_bytes(data, k, fmt, replace_with_none, bool(canonicalize), device)
+    with open(filepath, "rb") as fh:
+        raw = fh.read()
+    sums = _checksums_async(raw)                               # hashes of the raw bytes, computed beside the GPU work
+    try:
+        data = _read_text_bytes(filepath, raw)
+        fmt = _file_format(filepath)
+        prof = profile_bytes(data, k, fmt, replace_with_none, bool(canonicalize), device)
+    finally:
+        md5, sha256 = sums()
     assert prof.nullomers == len(prof.nullomer_array), "Internal Error: kmerdb.parse.parsefile() found inconsistencies between two ways of counting nullomers. Internal error."
     meta = prof.file_metadata(filepath, md5, sha256)
     if with_mononucleotides:
