@@ -64,6 +64,7 @@ struct kdb_ctx {
     unsigned long long carry_rec_id = 0, fq_rec_base = 0;
     unsigned long long bytes_since_fold = 0;
     bool job_started = false, finished = false, host_layout = false;
+    bool tab32_clean = false;                   // tab32 is all zero (every fold leaves it so): reset skips the 4^k x 4 B memset
     bool tab64_valid = false;                   // tab64 holds folded counts (it is not zeroed at reset: the first fold writes it)
     int count_grid = 0;
     kdb_stats_t stats{};
@@ -138,7 +139,8 @@ extern "C" void kdb_destroy(kdb_ctx* ctx) {
 
 static int reset_state(kdb_ctx* ctx) {
     CK(cudaEventRecord(ctx->ev_job0, ctx->s_compute));   // a job starts with zeroing its tables
-    CK(cudaMemsetAsync(ctx->tab32, 0, ctx->nbins * sizeof(unsigned int), ctx->s_compute));
+    if (!ctx->tab32_clean) CK(cudaMemsetAsync(ctx->tab32, 0, ctx->nbins * sizeof(unsigned int), ctx->s_compute));
+    ctx->tab32_clean = true;
     Accum a{};
     a.min_len = ~0ull; a.err_key = ~0ull;
     CK(cudaMemcpyAsync(ctx->acc, &a, sizeof a, cudaMemcpyHostToDevice, ctx->s_compute));
@@ -268,6 +270,7 @@ static int fold_now(kdb_ctx* ctx, bool count_unique = false, cudaStream_t st = n
     ctx->timing.total_launches++;
     ctx->bytes_since_fold = 0;
     ctx->tab64_valid = true;
+    ctx->tab32_clean = true;
     return KDB_OK;
 }
 
@@ -288,6 +291,7 @@ static int close_carry_record(kdb_ctx* ctx) {
 static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigned long long lo, unsigned long long hi) {
     const int smear = ctx->k - src->k;
     cudaStream_t st = src->s_compute;
+    ctx->tab32_clean = false;
     if (ctx != src && ctx->bytes_since_fold + (hi - lo) > 0x7fffffffull) if (int rc = fold_now(ctx, false, st)) return rc;
     if (ctx->partitioned) {
         // every window ends on a text byte, so (hi - lo) bounds the entries of the pass; canonical ids of
