@@ -626,6 +626,15 @@ extern "C" int kdb_export_partials(kdb_ctx* ctx, uint64_t* out16) {
     Accum a;
     CK(cudaMemcpy(&a, ctx->acc, sizeof a, cudaMemcpyDeviceToHost));
     memset(out16, 0, 16 * sizeof(uint64_t));
+    if (ctx->leader) {                       // a follower of a sweep: the per-record scalars are its leader's
+        const kdb_stats_t& st = ctx->stats;
+        a.sum_len = st.sum_len; a.n_windows_with_n = st.n_windows_with_n;
+        for (int i = 0; i < 4; i++) a.mono[i] = st.mono[i];
+        a.min_len = st.total_reads ? st.min_len : ~0ull; a.max_len = st.max_len;
+        const unsigned int pr = st.status == KDB_E_ALPHABET ? P_ALPHABET : st.status == KDB_E_SHORT ? P_SHORT : P_IUPAC;
+        a.err_key = (st.status >= KDB_E_ALPHABET && st.status <= KDB_E_SHORT) ? st.err_record * 4 + pr : ~0ull;
+        a.layout_flag = st.status == KDB_E_LAYOUT;
+    }
     out16[0] = ctx->stats.total_reads; out16[1] = a.total_kmers; out16[2] = a.sum_len;
     for (int i = 0; i < 4; i++) out16[3 + i] = a.mono[i];
     out16[7] = a.n_windows_with_n; out16[8] = a.min_len; out16[9] = a.max_len; out16[10] = a.err_key;
