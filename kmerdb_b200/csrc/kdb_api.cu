@@ -299,17 +299,18 @@ static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigne
         const unsigned long long avg = (hi - lo) / ctx->n_buckets + 1;
         const unsigned int cap = (unsigned int)((3 * avg + kTile + 7) & ~7ull);   // >= kTile: keeps s_delta (kdb_part.cuh) from wrapping
         if ((unsigned long long)cap * ctx->n_buckets >= 0xFFFFFFFFull) { ctx->err = "bucket stream index exceeds 32 bits"; return KDB_E_ARG; }
-        if (int rc = ensure(ctx, (void**)&ctx->stream, &ctx->stream_cap, (size_t)cap * ctx->n_buckets, sizeof(uint16_t))) return rc;
+        // the bucket streams live in the leader: the k of a sweep are counted one after the other on one stream
+        if (int rc = ensure(src, (void**)&src->stream, &src->stream_cap, (size_t)cap * ctx->n_buckets, sizeof(uint16_t))) { ctx->err = src->err; return rc; }
         CK(cudaMemsetAsync(ctx->cursor, 0, ctx->n_buckets * sizeof(unsigned int), st));
         CK(cudaMemsetAsync(ctx->cursor + ctx->n_buckets, 0xFF, ctx->n_buckets * sizeof(unsigned int), st));
         PartParams Q{};
-        Q.packed = src->packed; Q.n_tiles = n_tiles; Q.skip_n = ctx->skip_n; Q.smear = smear; Q.tab32 = ctx->tab32; Q.stream = ctx->stream;
+        Q.packed = src->packed; Q.n_tiles = n_tiles; Q.skip_n = ctx->skip_n; Q.smear = smear; Q.tab32 = ctx->tab32; Q.stream = src->stream;
         Q.cursor = ctx->cursor; Q.fail_base = ctx->cursor + ctx->n_buckets; Q.cap = cap; Q.acc = ctx->acc;
         const int grid = (int)std::min<unsigned int>((n_tiles + 1) / 2, (unsigned int)ctx->part_grid);   // work unit = two tiles
         ctx->part_kernel<<<grid, kPartThreads, k3p_smem_bytes(ctx->k), st>>>(Q);
         CK(cudaGetLastError());
         CK(cudaEventRecord(ctx->ev[7], st));
-        k3p_count<<<ctx->n_buckets * ctx->parts * ctx->subs, kBucketThreads, 4 << kTableBits, st>>>(ctx->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->subs,
+        k3p_count<<<ctx->n_buckets * ctx->parts * ctx->subs, kBucketThreads, 4 << kTableBits, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->subs,
                                                                                                   payload_bits(ctx->k), ctx->tab32);
         CK(cudaGetLastError());
         ctx->timing.total_launches++;
