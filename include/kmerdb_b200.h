@@ -149,6 +149,10 @@ int kdb_edge_weights(kdb_ctx* ctx, int canonical, uint64_t* n1, uint64_t* n2, ui
  * canonical id of the smallest id, leftmost on ties, consecutive repeats collapsed. */
 int kdb_minimizers_compat(int device, const uint8_t* seq, size_t len, int k, uint64_t window, uint64_t* ids, uint8_t* is_min, size_t cap, size_t* n_rows);
 int kdb_minimizers(int device, const uint8_t* seq, size_t len, int k, int w, uint64_t* pos, uint64_t* ids, size_t cap, size_t* n);
+/* kdb_minimizers for many records (reads) in one call: `letters` / `rec_off` as for kdb_edge_rows; rows (record index,
+ * position inside the record, canonical id), record-major; records shorter than k + w - 1 give no row; cap = 0 counts only. */
+int kdb_minimizers_batch(int device, const uint8_t* letters, size_t n_letters, const uint64_t* rec_off, size_t n_recs, int k, int w,
+                         uint64_t* rec, uint64_t* pos, uint64_t* ids, size_t cap, size_t* n_rows);
 
 /* ---- .kdb body rows (kmerdb/__init__.py:1980-1990) ------------------------------------------
  * Rows "i\ti\tcount\tfrequency\n" for i = first_row .. first_row + n_rows - 1 (counts[j] belongs to row first_row + j),

@@ -19,7 +19,7 @@ EXPORTS = [
     "kdb_reset", "kdb_timing", "kdb_kmer_to_id_batch", "kdb_synth_record_bytes", "kdb_synth_device",
     "kdb_synth_host", "kdb_microbench_atomics", "kdb_dev_alloc", "kdb_dev_free", "kdb_host_alloc_pinned",
     "kdb_host_free_pinned", "kdb_memcpy_h2d", "kdb_memcpy_d2h",
-    "kdb_edge_rows", "kdb_edge_weights", "kdb_minimizers_compat", "kdb_minimizers", "kdb_attach", "kdb_format_rows",
+    "kdb_edge_rows", "kdb_edge_weights", "kdb_minimizers_compat", "kdb_minimizers", "kdb_attach", "kdb_format_rows", "kdb_minimizers_batch",
 ]
 
 
@@ -77,6 +77,7 @@ def lib():
         ("kdb_edge_weights", [vp, ci, vp, vp, vp, sz, ctypes.POINTER(sz)]),
         ("kdb_minimizers_compat", [ci, vp, sz, ci, u64, vp, vp, sz, ctypes.POINTER(sz)]),
         ("kdb_minimizers", [ci, vp, sz, ci, ci, vp, vp, sz, ctypes.POINTER(sz)]),
+        ("kdb_minimizers_batch", [ci, vp, sz, vp, sz, ci, ci, vp, vp, vp, sz, ctypes.POINTER(sz)]),
     ]:
         fn = getattr(L, name)
         fn.restype = ci
@@ -354,3 +355,22 @@ def format_rows(counts, first_row, uniq_vals, str_off, str_bytes, device=0):
     if n.value and lib().kdb_format_rows(*args, out.ctypes.data, out.size, ctypes.byref(n)):
         raise NativeError("kdb_format_rows: " + _err())
     return out
+
+
+def minimizers_batch(letters, rec_off, k, w, device=0, count_only=False):
+    """kdb_minimizers_batch: (status, rows uint64[n, 3] = (record, position, id)) or (status, n_rows) when count_only."""
+    a = np.ascontiguousarray(np.frombuffer(letters, dtype=np.uint8) if not isinstance(letters, np.ndarray) else letters, dtype=np.uint8)
+    off = np.ascontiguousarray(rec_off, dtype=np.uint64)
+    n = ctypes.c_size_t()
+    args = (device, a.ctypes.data if a.size else None, a.size, off.ctypes.data, off.size - 1, int(k), int(w))
+    rc = lib().kdb_minimizers_batch(*args, None, None, None, 0, ctypes.byref(n))
+    if rc in (KDB_E_CUDA, KDB_E_ARG):
+        raise NativeError("kdb_minimizers_batch failed (%d): %s" % (rc, _err()))
+    if rc or count_only:
+        return rc, (n.value if count_only else None)
+    cols = [np.empty(n.value, dtype=np.uint64) for _ in range(3)]
+    if n.value:
+        rc = lib().kdb_minimizers_batch(*args, *[c.ctypes.data for c in cols], n.value, ctypes.byref(n))
+        if rc:
+            raise NativeError("kdb_minimizers_batch failed (%d): %s" % (rc, _err()))
+    return 0, (np.stack(cols, axis=1) if n.value else np.zeros((0, 3), dtype=np.uint64))

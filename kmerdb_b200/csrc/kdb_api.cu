@@ -1017,3 +1017,48 @@ extern "C" int kdb_format_rows(int device, const uint64_t* counts, uint64_t firs
     CK(cudaMemcpy(out, d_out.p, total, cudaMemcpyDeviceToHost));
     return KDB_OK;
 }
+
+// True windowed minimizers of many records in one call (reads): rows (record, position inside the record, canonical id),
+// record-major.  Records shorter than k + w - 1 give no row.  cap = 0 (or NULL outputs) only counts.
+extern "C" int kdb_minimizers_batch(int device, const uint8_t* letters, size_t n_letters, const uint64_t* rec_off, size_t n_recs, int k, int w,
+                                    uint64_t* rec, uint64_t* pos, uint64_t* ids, size_t cap, size_t* n_rows) {
+    kdb_ctx* ctx = nullptr;
+    if (!rec_off || !n_rows || k < 1 || k > 31 || w < 1 || (n_letters && !letters)) return KDB_E_ARG;
+    *n_rows = 0;
+    if (n_recs == 0 || n_letters < (size_t)k + (size_t)w - 1) return KDB_OK;
+    CK(cudaSetDevice(device));
+    if (int rc = upload_lut(ctx)) return rc;
+    const unsigned long long n_win = n_letters - k + 1, n_out = n_win - w + 1;
+    DevBuf d_let, d_off, d_ids, d_best, d_bad, d_cnt, d_boff, d_out;
+    CK(d_let.alloc(n_letters)); CK(d_off.alloc((n_recs + 1) * 8)); CK(d_ids.alloc(n_win * 8)); CK(d_best.alloc(n_out * 8)); CK(d_bad.alloc(4));
+    CK(cudaMemcpy(d_let.p, letters, n_letters, cudaMemcpyHostToDevice));
+    CK(cudaMemcpy(d_off.p, rec_off, (n_recs + 1) * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemset(d_bad.p, 0, 4));
+    k8_window_ids<<<(unsigned int)((n_win + 255) / 256), 256>>>(d_let.as<uint8_t>(), n_win, k, d_ids.as<unsigned long long>(), d_bad.as<unsigned int>());
+    CK(cudaGetLastError());
+    unsigned int bad = 0;
+    CK(cudaMemcpy(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost));
+    if (bad & 1u) return KDB_E_ALPHABET;
+    if (bad & 2u) return KDB_E_IUPAC;
+    k8_min_window<<<(unsigned int)((n_out + 255) / 256), 256>>>(d_ids.as<unsigned long long>(), n_win, w, n_out, d_best.as<unsigned long long>());
+    CK(cudaGetLastError());
+    const unsigned int blocks = (unsigned int)((n_out + kEdgeBlock - 1) / kEdgeBlock);
+    CK(d_cnt.alloc(blocks * sizeof(unsigned int)));
+    k8_minb_rows<false><<<blocks, 256>>>(d_best.as<unsigned long long>(), d_ids.as<unsigned long long>(), n_out, d_off.as<unsigned long long>(), n_recs, k, w,
+                                         d_cnt.as<unsigned int>(), nullptr, nullptr, nullptr, nullptr, 0);
+    CK(cudaGetLastError());
+    unsigned long long total = 0;
+    if (int rc = scan_blocks(ctx, d_cnt.as<unsigned int>(), blocks, d_boff, &total)) return rc;
+    *n_rows = (size_t)total;
+    const size_t m = std::min<size_t>(cap, (size_t)total);
+    if (!m || !rec || !pos || !ids) return KDB_OK;
+    CK(d_out.alloc(3 * m * 8));
+    unsigned long long* o = d_out.as<unsigned long long>();
+    k8_minb_rows<true><<<blocks, 256>>>(d_best.as<unsigned long long>(), d_ids.as<unsigned long long>(), n_out, d_off.as<unsigned long long>(), n_recs, k, w,
+                                        nullptr, d_boff.as<unsigned long long>(), o, o + m, o + 2 * m, m);
+    CK(cudaGetLastError());
+    CK(cudaMemcpy(rec, o, m * 8, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(pos, o + m, m * 8, cudaMemcpyDeviceToHost));
+    CK(cudaMemcpy(ids, o + 2 * m, m * 8, cudaMemcpyDeviceToHost));
+    return KDB_OK;
+}

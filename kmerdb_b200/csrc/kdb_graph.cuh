@@ -282,4 +282,89 @@ __global__ void __launch_bounds__(256) k8_min_write(const unsigned long long* __
     }
 }
 
+// ---- batched minimizers: many records (reads) in one call ------------------------------------------------
+// ids and window minima are computed over the concatenated letters with the kernels above (a window that crosses a
+// record boundary yields garbage that is never emitted); these two kernels decide, per letter position p, whether the
+// window group starting at p lies inside its record and whether it names a new k-mer, and write the rows
+// (record, position inside the record, id).  The record of a position comes from a binary search in a shared-memory
+// copy of the slice of rec_off that covers the block.
+constexpr int kMinbSlice = kEdgeBlock + 2;
+struct RecSlice {
+    unsigned long long first;                      // index of the first record of the block
+    unsigned int n;                                // entries of rec_off held in shared memory (0 = search global memory)
+};
+__device__ __forceinline__ RecSlice load_rec_slice(const unsigned long long* __restrict__ rec_off, unsigned long long n_recs,
+                                                   unsigned long long p0, unsigned long long p1, unsigned long long* s_off, RecSlice* s_hdr) {
+    if (threadIdx.x == 0) {
+        const unsigned long long r0 = upper_rec(rec_off, n_recs, p0), r1 = upper_rec(rec_off, n_recs, p1);
+        s_hdr->first = r0;
+        s_hdr->n = (r1 - r0 + 2 <= (unsigned long long)kMinbSlice) ? (unsigned int)(r1 - r0 + 2) : 0u;
+    }
+    __syncthreads();
+    const RecSlice h = *s_hdr;
+    for (unsigned int i = threadIdx.x; i < h.n; i += blockDim.x) s_off[i] = rec_off[h.first + i];
+    __syncthreads();
+    return h;
+}
+// record of position p and its bounds
+__device__ __forceinline__ unsigned long long rec_of(const unsigned long long* __restrict__ rec_off, unsigned long long n_recs, const RecSlice h,
+                                                     const unsigned long long* s_off, unsigned long long p, unsigned long long* start, unsigned long long* end) {
+    if (h.n) {
+        unsigned int lo = 0, hi = h.n - 1;          // s_off[lo] <= p < s_off[hi]
+        while (hi - lo > 1) { const unsigned int mid = (lo + hi) >> 1; if (s_off[mid] <= p) lo = mid; else hi = mid; }
+        *start = s_off[lo]; *end = s_off[lo + 1];
+        return h.first + lo;
+    }
+    const unsigned long long r = upper_rec(rec_off, n_recs, p);
+    *start = rec_off[r]; *end = rec_off[r + 1];
+    return r;
+}
+
+template <bool WRITE>
+__global__ void __launch_bounds__(256) k8_minb_rows(const unsigned long long* __restrict__ best, const unsigned long long* __restrict__ ids,
+                                                    unsigned long long n_out, const unsigned long long* __restrict__ rec_off, unsigned long long n_recs,
+                                                    int k, int w, unsigned int* __restrict__ block_n, const unsigned long long* __restrict__ block_off,
+                                                    unsigned long long* __restrict__ out_rec, unsigned long long* __restrict__ out_pos,
+                                                    unsigned long long* __restrict__ out_id, unsigned long long cap) {
+    __shared__ unsigned long long s_off[kMinbSlice];
+    __shared__ RecSlice s_hdr;
+    __shared__ unsigned int s_warp[8];
+    __shared__ unsigned int s_total;
+    const unsigned long long base = (unsigned long long)blockIdx.x * kEdgeBlock;
+    const unsigned long long last = base + kEdgeBlock - 1 < n_out ? base + kEdgeBlock - 1 : n_out - 1;
+    const RecSlice h = load_rec_slice(rec_off, n_recs, base, last, s_off, &s_hdr);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    unsigned long long off = WRITE ? block_off[blockIdx.x] : 0ull;
+    unsigned int mine = 0;
+    for (int j0 = 0; j0 < kEdgeBlock; j0 += 256) {
+        const unsigned long long p = base + j0 + threadIdx.x;
+        bool keep = false;
+        unsigned long long r = 0, start = 0, end = 0;
+        if (p < n_out) {
+            r = rec_of(rec_off, n_recs, h, s_off, p, &start, &end);
+            keep = p + (unsigned long long)(k + w - 1) <= end && (p == start || best[p] != best[p - 1]);
+        }
+        if (!WRITE) { mine += keep; continue; }
+        const unsigned int bal = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) s_warp[warp] = __popc(bal);
+        __syncthreads();
+        unsigned int before = 0, total = 0;
+        for (int q = 0; q < 8; q++) { const unsigned int v = s_warp[q]; if (q < warp) before += v; total += v; }
+        if (keep) {
+            const unsigned long long o = off + before + __popc(bal & ((1u << lane) - 1u));
+            if (o < cap) { out_rec[o] = r; out_pos[o] = best[p] - start; out_id[o] = ids[best[p]]; }
+        }
+        off += total;
+        __syncthreads();
+    }
+    if (!WRITE) {
+        if (threadIdx.x == 0) s_total = 0;
+        __syncthreads();
+        for (int d = 16; d; d >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, d);
+        if (lane == 0 && mine) atomicAdd(&s_total, mine);
+        __syncthreads();
+        if (threadIdx.x == 0) block_n[blockIdx.x] = s_total;
+    }
+}
+
 }  // namespace kdb

@@ -39,3 +39,19 @@ def windowed_minimizers(seq, k, w, device=0):
     if status == _native.KDB_E_IUPAC:
         raise KeyError("ambiguous letter inside a window")
     return [(int(p), int(i)) for p, i in zip(pos, ids)]
+
+
+def windowed_minimizers_file(fasta_file, k, w, device=0):
+    """True (w, k) minimizers of every record of a FASTA/FASTQ file in one device call:
+    list of (seq_id, position, canonical kmer_id), record-major."""
+    import numpy as np
+    from . import parse
+    recs = list(parse.parse_sequence_file(fasta_file))
+    lens = np.array([len(s) for _, s in recs], dtype=np.uint64)
+    off = np.concatenate([np.zeros(1, dtype=np.uint64), np.cumsum(lens, dtype=np.uint64)])
+    status, rows = _native.minimizers_batch("".join(s for _, s in recs).encode("ascii", "replace"), off, k, w, device=device)
+    if status == _native.KDB_E_ALPHABET:
+        raise NameError("name 'permitted_AA_characters_extended' is not defined")
+    if status == _native.KDB_E_IUPAC:
+        raise KeyError("ambiguous letter inside a window")
+    return [(recs[int(r)][0], int(p), int(i)) for r, p, i in rows]

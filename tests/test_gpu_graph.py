@@ -158,3 +158,44 @@ def test_multik_sweep_vs_oracle():
         rc, ocounts, ost = oracle.profile(host, k, threads=8)
         assert rc == 0 and np.array_equal(pr.counts, ocounts), k
         assert pr.total_kmers == ost["total_kmers"] and pr.unique_kmers == ost["unique_kmers"]
+
+
+@pytest.mark.parametrize("k,w", [(5, 4), (12, 10), (15, 32), (9, 40)])
+def test_batched_minimizers_equal_per_record_oracle(k, w, tmp_path):
+    rng = np.random.default_rng(k + w)
+    recs = []
+    for i in range(700):
+        L = int(rng.choice([0, 1, k, k + w - 2, k + w - 1, k + w, 150, 151, 400, 5000], p=[.02, .02, .04, .05, .05, .05, .5, .17, .08, .02]))
+        recs.append("".join(np.array(list("ACGT"))[rng.choice(4, size=L, p=[0.4, 0.1, 0.1, 0.4])]))
+    want = []
+    for r, s in enumerate(recs):
+        rc, pos, ids = oracle.minimizers_true(s, k, w)
+        assert rc == 0
+        want += [(r, int(p), int(i)) for p, i in zip(pos, ids)]
+    lens = np.array([len(s) for s in recs], dtype=np.uint64)
+    off = np.concatenate([[0], np.cumsum(lens)]).astype(np.uint64)
+    st, rows = _native.minimizers_batch("".join(recs).encode(), off, k, w)
+    assert st == 0 and [tuple(int(x) for x in row) for row in rows] == want
+    st, n = _native.minimizers_batch("".join(recs).encode(), off, k, w, count_only=True)
+    assert st == 0 and n == len(want)
+    path = str(tmp_path / "m.fa")
+    open(path, "w").write("".join(">s%d\n%s\n" % (i, s) for i, s in enumerate(recs) if s))
+    got = minimizer.windowed_minimizers_file(path, k, w)
+    names = ["s%d" % i for i, s in enumerate(recs) if s]
+    nonempty = [i for i, s in enumerate(recs) if s]
+    remap = {r: j for j, r in enumerate(nonempty)}
+    assert got == [(names[remap[r]], p, i) for r, p, i in want]
+
+
+def test_batched_minimizers_at_read_scale():
+    """2 M synthetic 150 bp reads in one call (count only): every read yields at least one minimizer."""
+    n = 2_000_000
+    text = _native.synth_host(n).reshape(n, 162)
+    letters = np.ascontiguousarray(text[:, 11:161]).reshape(-1)
+    off = (np.arange(n + 1, dtype=np.uint64) * np.uint64(150))
+    st, rows = _native.minimizers_batch(letters, off, 12, 10, count_only=True)
+    assert st == 0 and n <= rows <= n * 130
+    s = letters[:150 * 50].tobytes().decode()
+    want = sum(len(oracle.minimizers_true(s[150 * r:150 * r + 150], 12, 10)[1]) for r in range(50))
+    st, rows50 = _native.minimizers_batch(letters[:150 * 50], off[:51], 12, 10)
+    assert len(rows50) == want

@@ -217,3 +217,19 @@ def test_full_size_100M_reads_properties():
     with _native.Profiler(k) as q:
         q.feed_device(buf.ptr, 200000 * rb)
         assert q.finish() == 0 and np.array_equal(q.counts(), ocounts)
+
+
+def test_configs1_full_vector_vs_oracle():
+    """Parity gate T2 at BASELINE.json configs[1] size: 10 M x 150 bp, k=12 canonical — the whole 4^12 vector and the
+    scalars against the CPU oracle (16 host threads, ~10 s)."""
+    n, k = 10_000_000, 12
+    host = _native.synth_host(n)
+    rc, ocounts, ost = oracle.profile(host, k, threads=max(4, len(os.sched_getaffinity(0))))
+    assert rc == 0
+    with _native.Profiler(k) as p:
+        p.feed(host)
+        assert p.finish() == 0
+        st, counts = p.stats(), p.counts()
+    assert hashlib.sha256(counts.tobytes()).hexdigest() == hashlib.sha256(ocounts.tobytes()).hexdigest()
+    for a in ("total_reads", "total_kmers", "unique_kmers", "sum_len", "min_len", "max_len", "mono"):
+        assert st[a] == ost[a], a
