@@ -163,6 +163,29 @@ int kdb_minimizers_batch(int device, const uint8_t* letters, size_t n_letters, c
 int kdb_format_rows(int device, const uint64_t* counts, uint64_t first_row, uint64_t n_rows, const uint64_t* uniq_vals,
                     const uint32_t* str_off, const char* str_bytes, size_t n_uniq, char* out, size_t cap, size_t* n_bytes);
 
+/* ---- .kdb body back into a count vector (KDBReader._slurp, kmerdb/fileutil.py:308-466, sort=False) ----
+ * For row j of the body: l = line.rstrip().split("\t"); 4 columns; x, id, count = int(l[0..2]); x == j;
+ * kmer_ids[j] = id; counts[id] = count (fileutil.py:350-365; frequencies = count / 4^k is left to the caller).
+ * The reader keeps counts[4^k], kmer_ids[4^k] in HBM; feed the inflated body in pieces cut at row ends (host pointers),
+ * in file order; rows beyond 4^k are ignored like the reference's `for j in range(N)`.
+ * kdb_reader_finish returns KDB_OK and copies the vectors out (NULL = skip), or the class of the first failing row
+ * (*err_row = its index): */
+typedef struct kdb_reader kdb_reader;
+enum {
+    KDB_R_BASE = 32,
+    KDB_R_COLUMNS = 33, /* AssertionError fileutil.py:351 (not 4 columns)                                 */
+    KDB_R_INT = 34,     /* ValueError     fileutil.py:357-361 (int() of column 1, 2 or 3)                 */
+    KDB_R_INDEX = 35,   /* AssertionError fileutil.py:359 (column 1 is not the row number; also a body
+                           with fewer than 4^k rows, which the reference meets as a stale line)          */
+    KDB_R_RANGE = 36,   /* IndexError     fileutil.py:365 (k-mer id >= 4^k)                               */
+    KDB_R_DUP = 37      /* a k-mer id on two rows: the later row wins in the reference; kmerdb never
+                           writes such a file and this reader refuses it                                 */
+};
+kdb_reader* kdb_reader_create(int device, int k);
+int kdb_reader_feed(kdb_reader* r, const uint8_t* text, size_t n_bytes);
+int kdb_reader_finish(kdb_reader* r, uint64_t* counts, uint64_t* kmer_ids, uint64_t* n_rows, uint64_t* err_row);
+void kdb_reader_destroy(kdb_reader* r);
+
 /* Synthetic benchmark input: n_reads records of read_len i.i.d. uniform ACGT letters,
  * FASTA framing ">%09d\n" + letters + "\n" (or FASTQ framing), written straight into HBM.
  * read index = first_read + i; counter-based generator, reproducible on the host

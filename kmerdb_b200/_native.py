@@ -20,6 +20,7 @@ EXPORTS = [
     "kdb_synth_host", "kdb_microbench_atomics", "kdb_dev_alloc", "kdb_dev_free", "kdb_host_alloc_pinned",
     "kdb_host_free_pinned", "kdb_memcpy_h2d", "kdb_memcpy_d2h",
     "kdb_edge_rows", "kdb_edge_weights", "kdb_minimizers_compat", "kdb_minimizers", "kdb_attach", "kdb_format_rows", "kdb_minimizers_batch",
+    "kdb_reader_create", "kdb_reader_feed", "kdb_reader_finish", "kdb_reader_destroy",
 ]
 
 
@@ -78,10 +79,15 @@ def lib():
         ("kdb_minimizers_compat", [ci, vp, sz, ci, u64, vp, vp, sz, ctypes.POINTER(sz)]),
         ("kdb_minimizers", [ci, vp, sz, ci, ci, vp, vp, sz, ctypes.POINTER(sz)]),
         ("kdb_minimizers_batch", [ci, vp, sz, vp, sz, ci, ci, vp, vp, vp, sz, ctypes.POINTER(sz)]),
+        ("kdb_reader_feed", [vp, vp, sz]), ("kdb_reader_finish", [vp, vp, vp, ctypes.POINTER(u64), ctypes.POINTER(u64)]),
     ]:
         fn = getattr(L, name)
         fn.restype = ci
         fn.argtypes = args
+    L.kdb_reader_create.restype = vp
+    L.kdb_reader_create.argtypes = [ci, ci]
+    L.kdb_reader_destroy.restype = None
+    L.kdb_reader_destroy.argtypes = [vp]
     L.kdb_synth_record_bytes.restype = sz
     L.kdb_synth_record_bytes.argtypes = [ci, ci]
     _lib = L
@@ -374,3 +380,52 @@ def minimizers_batch(letters, rec_off, k, w, device=0, count_only=False):
         if rc:
             raise NativeError("kdb_minimizers_batch failed (%d): %s" % (rc, _err()))
     return 0, (np.stack(cols, axis=1) if n.value else np.zeros((0, 3), dtype=np.uint64))
+
+
+KDB_R_COLUMNS, KDB_R_INT, KDB_R_INDEX, KDB_R_RANGE, KDB_R_DUP = 33, 34, 35, 36, 37
+
+
+class RowReader:
+    """kdb_reader: the rows of a .kdb body -> (counts, kmer_ids), parsed on the GPU."""
+
+    def __init__(self, k, device=0):
+        self.k = int(k)
+        self._r = lib().kdb_reader_create(int(device), self.k)
+        if not self._r:
+            raise NativeError("kdb_reader_create: " + _err())
+
+    def feed(self, text):
+        """`text`: bytes-like holding whole rows, in file order."""
+        a = np.frombuffer(text, dtype=np.uint8)
+        if a.size and lib().kdb_reader_feed(self._r, a.ctypes.data, a.size):
+            raise NativeError("kdb_reader_feed: " + _err())
+
+    def finish(self, want_ids=True):
+        """(status, counts, kmer_ids, n_rows, err_row); the arrays are None unless status == 0."""
+        n = 4 ** self.k
+        counts = np.empty(n, dtype=np.uint64)
+        ids = np.empty(n, dtype=np.uint64) if want_ids else None
+        n_rows, err_row = ctypes.c_uint64(), ctypes.c_uint64()
+        rc = lib().kdb_reader_finish(self._r, counts.ctypes.data, ids.ctypes.data if want_ids else None, ctypes.byref(n_rows), ctypes.byref(err_row))
+        if rc in (KDB_E_CUDA, KDB_E_ARG):
+            raise NativeError("kdb_reader_finish failed (%d): %s" % (rc, _err()))
+        if rc:
+            return rc, None, None, n_rows.value, err_row.value
+        return 0, counts, ids, n_rows.value, None
+
+    def close(self):
+        if self._r:
+            lib().kdb_reader_destroy(self._r)
+            self._r = None
+
+    def __enter__(self):
+        return self
+
+    def __exit__(self, *a):
+        self.close()
+
+    def __del__(self):
+        try:
+            self.close()
+        except Exception:
+            pass

@@ -115,7 +115,7 @@ def make_graph(args):
 
 def get_minimizers(args):
     """kmerdb/__init__.py:425-450.  k comes from the .kdb header; output `<kdb stripped>.kdbi.1`."""
-    md, _ = kdbfile.read_kdb(args.kdb)
+    md = kdbfile.KDBReader(args.kdb, slurp=False).metadata
     out = str(args.kdb).strip(".kdb") + ".kdbi.1"                   # __init__.py:437 (character strip, as in the reference)
     with open(out, "w") as fh:
         for rid, seq in parse.parse_sequence_file(args.fasta):

@@ -19,6 +19,7 @@
 #include "kdb_synth.cuh"
 #include "kdb_graph.cuh"
 #include "kdb_rows.cuh"
+#include "kdb_read.cuh"
 
 using namespace kdb;
 
@@ -1060,5 +1061,83 @@ extern "C" int kdb_minimizers_batch(int device, const uint8_t* letters, size_t n
     CK(cudaMemcpy(rec, o, m * 8, cudaMemcpyDeviceToHost));
     CK(cudaMemcpy(pos, o + m, m * 8, cudaMemcpyDeviceToHost));
     CK(cudaMemcpy(ids, o + 2 * m, m * 8, cudaMemcpyDeviceToHost));
+    return KDB_OK;
+}
+
+// ---- .kdb body -> count vector (KDBReader._slurp, kmerdb/fileutil.py:308-466) ------------------------------
+struct kdb_reader {
+    int device = 0, k = 0;
+    unsigned long long n_bins = 0, rows = 0;
+    DevBuf d_ids, d_counts, d_seen, d_err, d_text;
+    size_t text_cap = 0;
+};
+
+extern "C" kdb_reader* kdb_reader_create(int device, int k) {
+    kdb_ctx* ctx = nullptr;
+    if (k < 1 || k > 16) { g_last_error = "kdb_reader_create: k outside 1..16"; return nullptr; }
+    kdb_reader* r = new kdb_reader();
+    r->device = device; r->k = k; r->n_bins = 1ull << (2 * k);
+    auto fail = [&](cudaError_t e) { g_last_error = std::string("kdb_reader_create: ") + cudaGetErrorString(e); delete r; return (kdb_reader*)nullptr; };
+    cudaError_t e;
+    if ((e = cudaSetDevice(device)) != cudaSuccess) return fail(e);
+    const size_t seen_bytes = (size_t)((r->n_bins + 31) / 32) * 4;
+    if ((e = r->d_ids.alloc(r->n_bins * 8)) != cudaSuccess || (e = r->d_counts.alloc(r->n_bins * 8)) != cudaSuccess ||
+        (e = r->d_seen.alloc(seen_bytes)) != cudaSuccess || (e = r->d_err.alloc(8)) != cudaSuccess) return fail(e);
+    if ((e = cudaMemset(r->d_ids.p, 0, r->n_bins * 8)) != cudaSuccess || (e = cudaMemset(r->d_counts.p, 0, r->n_bins * 8)) != cudaSuccess ||
+        (e = cudaMemset(r->d_seen.p, 0, seen_bytes)) != cudaSuccess || (e = cudaMemset(r->d_err.p, 0xFF, 8)) != cudaSuccess) return fail(e);
+    (void)ctx;
+    return r;
+}
+
+extern "C" void kdb_reader_destroy(kdb_reader* r) {
+    if (!r) return;
+    cudaSetDevice(r->device);
+    delete r;
+}
+
+// `text` holds whole rows (it starts at a row start; a last row without '\n' is taken as complete).
+extern "C" int kdb_reader_feed(kdb_reader* r, const uint8_t* text, size_t n) {
+    kdb_ctx* ctx = nullptr;
+    if (!r || (n && !text)) return KDB_E_ARG;
+    if (n == 0) return KDB_OK;
+    CK(cudaSetDevice(r->device));
+    if (n > r->text_cap) {
+        if (r->d_text.p) { cudaFree(r->d_text.p); r->d_text.p = nullptr; }
+        CK(r->d_text.alloc(n));
+        r->text_cap = n;
+    }
+    CK(cudaMemcpy(r->d_text.p, text, n, cudaMemcpyHostToDevice));
+    const unsigned int blocks = (unsigned int)((n + kReadBlock - 1) / kReadBlock);
+    DevBuf d_cnt, d_off;
+    CK(d_cnt.alloc(blocks * sizeof(unsigned int)));
+    k10_count_rows<<<blocks, kReadThreads>>>(r->d_text.as<uint8_t>(), n, d_cnt.as<unsigned int>());
+    CK(cudaGetLastError());
+    unsigned long long feeds = 0;
+    if (int rc = scan_blocks(ctx, d_cnt.as<unsigned int>(), blocks, d_off, &feeds)) return rc;
+    ReadParams P;
+    P.text = r->d_text.as<uint8_t>(); P.n = n; P.blk_off = d_off.as<unsigned long long>(); P.first_row = r->rows; P.n_bins = r->n_bins;
+    P.kmer_ids = r->d_ids.as<unsigned long long>(); P.counts = r->d_counts.as<unsigned long long>(); P.seen = r->d_seen.as<unsigned int>();
+    P.err = r->d_err.as<unsigned long long>();
+    k10_parse_rows<<<blocks, kReadThreads>>>(P);
+    CK(cudaGetLastError());
+    CK(cudaDeviceSynchronize());
+    r->rows += feeds + (text[n - 1] != '\n' ? 1 : 0);
+    return KDB_OK;
+}
+
+// Copies the vectors out (either may be NULL).  Return value: 0, or the KDB_R_* class of the first failing row (*err_row).
+// Fewer than 4^k rows fail as KDB_R_INDEX at row n_rows: the reference re-reads its last line there (fileutil.py:339-344, :359).
+extern "C" int kdb_reader_finish(kdb_reader* r, uint64_t* counts, uint64_t* kmer_ids, uint64_t* n_rows, uint64_t* err_row) {
+    kdb_ctx* ctx = nullptr;
+    if (!r) return KDB_E_ARG;
+    CK(cudaSetDevice(r->device));
+    unsigned long long err = 0;
+    CK(cudaMemcpy(&err, r->d_err.p, 8, cudaMemcpyDeviceToHost));
+    if (n_rows) *n_rows = r->rows;
+    if (err == ~0ull && r->rows < r->n_bins) err = ((unsigned long long)r->rows << 3) | (r->rows ? R_INDEX : R_COLUMNS);
+    if (err != ~0ull && (err >> 3) > r->rows && r->rows < r->n_bins) err = ((unsigned long long)r->rows << 3) | R_INDEX;
+    if (err != ~0ull) { if (err_row) *err_row = err >> 3; return KDB_R_BASE + (int)(err & 7); }
+    if (counts) CK(cudaMemcpy(counts, r->d_counts.p, r->n_bins * 8, cudaMemcpyDeviceToHost));
+    if (kmer_ids) CK(cudaMemcpy(kmer_ids, r->d_ids.p, r->n_bins * 8, cudaMemcpyDeviceToHost));
     return KDB_OK;
 }

@@ -109,8 +109,101 @@ def write_kdb(path, metadata, counts, threads=8, quiet=True, rows_per_task=1 << 
     return md
 
 
-def read_kdb(path):
-    """(metadata dict, counts uint64[4^k]) of a .kdb file written by kmerdb or by write_kdb (4-column rows)."""
+_ROW_ERRORS = {33: (AssertionError, "kmerdb.fileutil.KDBReader requires .kdb files to have 4 columns."),
+               34: (ValueError, "invalid literal for int() with base 10"),
+               35: (AssertionError, "Line number doesn't match file row index"),
+               36: (IndexError, "index is out of bounds for axis 0"),
+               37: (ValueError, "a k-mer id appears on two rows")}
+
+
+def _inflate_groups(raw, threads=8, group=2048):
+    """The inflated text of a BGZF file, yielded in pieces of `group` blocks (inflate on a thread pool)."""
+    from .parse import _bgzf_blocks
+    blocks = _bgzf_blocks(raw)
+    if blocks is None:                                       # ordinary gzip: one piece
+        yield gzip.decompress(raw)
+        return
+    mv = memoryview(raw)
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        for g in range(0, len(blocks), group):
+            yield b"".join(ex.map(lambda b: zlib.decompress(mv[b[0] + 18:b[0] + b[1] - 8], -15), blocks[g:g + group]))
+
+
+class KDBReader:
+    """The slurped view of a .kdb file: `.metadata`, `.k`, `.kmer_ids`, `.counts`, `.frequencies`
+    (kmerdb/fileutil.py:KDBReader with slurp=True, sort=False, :308-377).  The row loop runs on the GPU
+    (kdb_reader_*, kdb_read.cuh); header YAML and BGZF inflate stay on the host."""
+
+    def __init__(self, path, slurp=True, device=0, threads=8):
+        from . import _native
+        self._filepath = path
+        with open(path, "rb") as fh:
+            raw = fh.read()
+        delim = HEADER_DELIMITER.encode("ascii")
+        pieces = _inflate_groups(raw, threads)
+        head = b""
+        for piece in pieces:
+            head += piece
+            if delim in head:
+                break
+        if delim not in head:
+            raise ValueError("Requires kmerdb format YAML header. Body is .tsv format table, .bgzf file.")
+        cut = head.index(delim)
+        self.metadata = yaml.safe_load(head[:cut].decode("utf-8"))
+        self.k = self.metadata["k"]
+        self.kmer_ids = self.counts = self.frequencies = None
+        if not slurp:
+            return
+        n = 4 ** self.k
+        with _native.RowReader(self.k, device) as rd:
+            rest = head[cut + len(delim):]
+            for piece in pieces:
+                buf = rest + piece if rest else piece
+                end = buf.rfind(b"\n") + 1
+                rd.feed(memoryview(buf)[:end])
+                rest = buf[end:]
+            rd.feed(rest)
+            rc, counts, ids, n_rows, err_row = rd.finish()
+        if rc:
+            cls, msg = _ROW_ERRORS[rc]
+            raise cls("{0} (row {1} of {2})".format(msg, err_row, path))
+        self.counts, self.kmer_ids = counts, ids
+        self.frequencies = counts.astype(np.float64) / n              # fileutil.py:362 float(count)/N, N = 4^k
+
+    def slurp(self):
+        return self.counts
+
+
+def open_kdb(path, mode="r", slurp=True, device=0):
+    """fileutil.open(path, 'r', slurp=...) for reading."""
+    if mode != "r":
+        raise ValueError("kmerdb_b200.kdbfile.open_kdb reads; use write_kdb to write")
+    return KDBReader(path, slurp=slurp, device=device)
+
+
+def read_kdb(path, device=0):
+    """(metadata dict, counts uint64[4^k]) of a .kdb file written by kmerdb or by write_kdb."""
+    r = KDBReader(path, device=device)
+    return r.metadata, r.counts
+
+
+def matrix_from(paths, column_names=None, device=0):
+    """`kmerdb matrix from a.kdb b.kdb ...` collation (kmerdb/__init__.py:844-896): (profiles uint64[4^k, n], columns)."""
+    import os
+    ks = [KDBReader(f, slurp=False).k for f in paths]
+    if not all(k == ks[0] for k in ks):
+        raise TypeError("One or more files did not have k set to be equal to {0}".format(ks[0]))
+    profiles = np.empty((4 ** ks[0], len(paths)), dtype=np.uint64)
+    for j, f in enumerate(paths):
+        profiles[:, j] = KDBReader(f, device=device).counts
+    columns = list(column_names) if column_names is not None else [os.path.basename(f).split(".")[0] for f in paths]
+    if len(columns) != len(paths):
+        raise RuntimeError("Number of column names {0} does not match number of input files {1}...".format(len(columns), len(paths)))
+    return profiles, columns
+
+
+def read_kdb_host(path):
+    """The reference's row loop on the host (slow; kept for the tests as the checker of the GPU reader)."""
     with gzip.open(path, "rt") as fh:
         text = fh.read()
     head, _, body = text.partition(HEADER_DELIMITER)

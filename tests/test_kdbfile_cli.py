@@ -40,7 +40,7 @@ def test_write_kdb_layout_and_rows(tmp_path):
     for i in (0, 1, 77, 4095):
         # kmerdb/__init__.py:1990 formats np.uint64 and np.float64 with str.format
         assert rows[i] == "{0}\t{1}\t{2}\t{3}".format(i, i, np.uint64(counts[i]), np.divide(counts, total)[i])
-    md2, c2 = kdbfile.read_kdb(path)
+    md2, c2 = kdbfile.read_kdb_host(path)
     assert md2["k"] == 6 and md2["files"][0]["filename"] == "x.fa" and np.array_equal(c2, counts)
 
 
