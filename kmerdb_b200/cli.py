@@ -92,16 +92,23 @@ def make_graph(args):
     """kmerdb/__init__.py:1635-1788: one 8-column row per adjacent k-mer pair (rows rendered on the host)."""
     if not args.kdbg.endswith(".kdbg"):
         raise IOError("kmerdb graph expects a '.kdbg' suffixed output file")        # __init__.py:1663-1664
+    N = 4 ** args.k
+    counts = np.zeros(N, dtype="uint64")
     rows, metas = [], []
     for f in args.input:
-        data, meta, _counts = graph.make_edges_from_fasta(f, args.k, quiet=args.quiet, canonicalize=not args.do_not_canonicalize,
-                                                          replace_with_none=args.replace_with_none, device=args.device)
+        data, meta, counts_ = graph.make_edges_from_fasta(f, args.k, quiet=args.quiet, canonicalize=not args.do_not_canonicalize,
+                                                           replace_with_none=args.replace_with_none, device=args.device)
         rows += data
+        counts = counts + counts_                                                  # __init__.py:1676
         metas.append(meta)
     body = "".join("{0}\t{1}\t{2}\t{3}\t{4}\t{5}\t{6}\t{7}\n".format(i, sid, p1, i1, kmer.id_to_kmer(i1, args.k), p2, i2, kmer.id_to_kmer(i2, args.k))
                    for i, (sid, p1, i1, p2, i2) in enumerate(rows))             # __init__.py:1756-1762
+    if not args.quiet:
+        sys.stdout.write(body)
+    unique = int(np.count_nonzero(counts))
+    unique_nullomers = N - unique if args.do_not_canonicalize else int((N / 2) - unique)    # __init__.py:1712
     md = OrderedDict({"version": REFERENCE_VERSION, "metadata_blocks": 1, "k": args.k, "total_kmers": sum(m["total_kmers"] for m in metas),
-                      "sorted": False, "n1_dtype": "uint64", "n2_dtype": "uint64", "weights_dtype": "uint64", "tags": [], "files": metas})
+                      "unique_kmers": unique, "unique_nullomers": unique_nullomers, "sorted": args.sorted, "tags": [], "files": metas})   # :1714-1724
     head, _ = kdbfile.header_bytes(md)
     with open(args.kdbg, "wb") as fh:
         for o in range(0, len(head), 65536):
