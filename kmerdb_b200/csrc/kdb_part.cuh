@@ -51,19 +51,24 @@ __device__ __forceinline__ void red_aggregated(unsigned int* tab32, uint32_t id)
     if ((threadIdx.x & 31) == __ffs(peers) - 1) atomicAdd(tab32 + id, (unsigned int)__popc(peers));
 }
 
+// Two sweeps over the 32 letters of a thread: sweep A only counts (bucket histogram), the CTA scans the histogram into
+// per-bucket cursors, sweep B recomputes each id and takes its place from the cursor.  Nothing but the packed words is
+// kept in registers between the sweeps, so three CTAs fit one SM (the register array of a one-sweep rank sort allows two),
+// and a crowded bucket needs no special case (no rank is packed beside the id).
+// 32 bits of the 96-bit string w0:w1:w2 (most significant first) starting at bit o; o is a compile-time constant after unrolling.
+__device__ __forceinline__ uint32_t ext96(uint32_t w0, uint32_t w1, uint32_t w2, int o) {
+    return o < 32 ? (o == 0 ? w0 : __funnelshift_l(w1, w0, o)) : (o < 64 ? (o == 32 ? w1 : __funnelshift_l(w2, w1, o - 32)) : (w2 << (o - 64)));
+}
 template <int K, bool CANON>
-__global__ void __launch_bounds__(kPartThreads, 2) k3p_partition(const PartParams P) {
+__global__ void __launch_bounds__(kPartThreads, 3) k3p_partition(const PartParams P) {
     constexpr int PB = payload_bits(K);
-    constexpr int NB = 1 << (2 * K - PB);                           // buckets
-    constexpr int RBITS = 32 - 2 * K;                               // rank bits kept beside the id in one register
-    constexpr uint32_t RCAP = (1u << RBITS) - 1u;                   // ranks >= RCAP take the direct RED path
+    constexpr int NBITS = 2 * K - PB, NB = 1 << NBITS;              // buckets
     constexpr uint32_t mask = (1u << (2 * K)) - 1u;
     constexpr int PER = (NB + kPartThreads - 1) / kPartThreads;     // buckets per thread in the scan
-    extern __shared__ uint32_t s_dyn_part[];                        // (kTile + 3 NB) words, see k3p_smem_bytes
+    extern __shared__ uint32_t s_dyn_part[];                        // (kTile + 2 NB + 32) words, see k3p_smem_bytes
     uint32_t* const s_sorted = s_dyn_part;                          // ids of the tile, grouped by bucket
-    uint32_t* const s_hist = s_dyn_part + kTile;
-    uint32_t* const s_off = s_hist + NB;
-    uint32_t* const s_delta = s_off + NB;                           // stream index of sorted entry j = s_delta[bucket] + j
+    uint32_t* const s_hist = s_dyn_part + kTile;                    // sweep A: entries per bucket; sweep B: next free sorted slot
+    uint32_t* const s_delta = s_hist + NB + 32;                     // stream index of sorted entry j = s_delta[bucket] + j (32 dummy counters sit between)
     __shared__ uint32_t s_warp[kPartThreads / 32];
     __shared__ unsigned long long s_red[kPartThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -87,11 +92,9 @@ __global__ void __launch_bounds__(kPartThreads, 2) k3p_partition(const PartParam
         for (int i = tid; i < NB; i += kPartThreads) s_hist[i] = 0;
         __syncthreads();
 
-        // ---- phase 1: ids of my 32 letters, rank inside their bucket ------------------------------
-        uint32_t item[32];                                           // id | rank << 2K, or ~0 = nothing to store
+        // ---- sweep A: bucket histogram of my 32 letters -------------------------------------------
         const bool active = (uint32_t)ltid * 32 < n;
-        bool generic = false;
-        uint32_t cur0 = 0, cur1 = 0, prev = 0, wb = 0, nn_cur = 0, nn_prev = 0;
+        uint32_t cur0 = 0, cur1 = 0, prev = 0, wb = 0;
         if (active) {
             const uint32_t* codes = reg + kPackHdr;
             cur0 = codes[2 * ltid];
@@ -101,54 +104,57 @@ __global__ void __launch_bounds__(kPartThreads, 2) k3p_partition(const PartParam
             if (P.smear) wb = smear_w(ltid ? reg[kPackHdr + kPackCodes + ltid - 1] : reg[3], wb, P.smear);
             if (!P.skip_n) {
                 const uint32_t* nnw = reg + kPackHdr + kPackCodes + kPackBits;
-                nn_cur = nnw[ltid];
-                nn_prev = ltid ? nnw[ltid - 1] : reg[2];
-                generic = (nn_cur | (nn_prev & ((1u << (K - 1)) - 1u))) != 0;
+                const uint32_t nn_cur = nnw[ltid], nn_prev = ltid ? nnw[ltid - 1] : reg[2];
+                if ((nn_cur | (nn_prev & ((1u << (K - 1)) - 1u))) != 0) {
+                    // expansion mode with N near by: generic path, direct REDs; nothing of this thread enters the sort
+                    const unsigned long long S0 = ((unsigned long long)prev << 32) | cur0, S1 = ((unsigned long long)cur0 << 32) | cur1;
+                    const unsigned long long NS = ((unsigned long long)nn_prev << 32) | nn_cur;
+                    for (int e = 0; e < 32; e++) {
+                        if (!(wb & (0x80000000u >> e))) continue;
+                        const uint32_t f = (uint32_t)((e < 16 ? S0 : S1) >> (30 - 2 * (e & 15))) & mask;
+                        const uint32_t nm = (uint32_t)(NS >> (31 - e)) & ((1u << K) - 1u);
+                        if (nm) kmers += expand_window(P.tab32, K, CANON, f, nm);
+                        else {
+                            uint32_t id = f;
+                            if (CANON) { const uint32_t r = revcomp32(f, K); id = r < f ? r : f; }
+                            atomicAdd(P.tab32 + id, 1u);
+                            kmers++;
+                        }
+                    }
+                    wb = 0;
+                }
             }
         }
-        if (active && !generic) {
-            const uint32_t r2 = CANON ? rc_word(cur1) : 0u, r1 = CANON ? rc_word(cur0) : 0u, r0 = CANON ? rc_word(prev) : 0u;
+        // Ids stay top-aligned (the 2K id bits on top, later letters below them): min() of the two strands is decided by
+        // the id bits alone, and bucket / payload / id come out by shifts without a mask.
+        const uint32_t r2 = CANON ? rc_word(cur1) : 0u, r1 = CANON ? rc_word(cur0) : 0u, r0 = CANON ? rc_word(prev) : 0u;
+        auto window_top = [&](int e) -> uint32_t {                     // window ending at my letter e
+            uint32_t m = ext96(prev, cur0, cur1, 2 * (17 + e - K));
+            if (CANON) { const uint32_t rc = ext96(r2, r1, r0, 62 - 2 * e); m = rc < m ? rc : m; }
+            return m;
+        };
+        // A letter without a window bumps a per-lane dummy counter behind the histogram instead of branching around the
+        // atomic: the compiler wraps every conditional shared atomic in its own branch + reconvergence barrier (three
+        // extra instructions per entry, and no overlap between entries); 93 % of the letters of a read have a window.
+        uint32_t* const dummy = s_hist + NB + lane;
+        if (wb) {
 #pragma unroll
             for (int e = 0; e < 32; e++) {
-                uint32_t it = 0xFFFFFFFFu;
-                if (wb & (0x80000000u >> e)) {
-                    uint32_t id = (e < 16 ? __funnelshift_r(cur0, prev, 30 - 2 * (e & 15)) : __funnelshift_r(cur1, cur0, 30 - 2 * (e & 15))) & mask;
-                    if (CANON) { const uint32_t rc = shr96_rt(r2, r1, r0, 34 + 2 * e - 2 * K) & mask; id = rc < id ? rc : id; }
-                    const uint32_t rank = atomicAdd(&s_hist[id >> PB], 1u);
-                    if (rank < RCAP) it = id | (rank << (2 * K));
-                    else red_aggregated(P.tab32, id);                // a bucket this crowded inside one tile: count directly
-                }
-                item[e] = it;
+                const bool valid = (wb & (0x80000000u >> e)) != 0;
+                uint32_t b = window_top(e) >> (32 - NBITS);
+                asm volatile("" : "+r"(b));                              // (keeps the id arithmetic out of a branch the compiler would build for the select)
+                atomicAdd(valid ? s_hist + b : dummy, 1u);
             }
             kmers += __popc(wb);
-        } else {
-#pragma unroll
-            for (int e = 0; e < 32; e++) item[e] = 0xFFFFFFFFu;
-            if (active) {                                            // expansion mode with N near by: generic path, direct REDs
-                const unsigned long long S0 = ((unsigned long long)prev << 32) | cur0, S1 = ((unsigned long long)cur0 << 32) | cur1;
-                const unsigned long long NS = ((unsigned long long)nn_prev << 32) | nn_cur;
-                for (int e = 0; e < 32; e++) {
-                    if (!(wb & (0x80000000u >> e))) continue;
-                    const uint32_t f = (uint32_t)((e < 16 ? S0 : S1) >> (30 - 2 * (e & 15))) & mask;
-                    const uint32_t nm = (uint32_t)(NS >> (31 - e)) & ((1u << K) - 1u);
-                    if (nm) kmers += expand_window(P.tab32, K, CANON, f, nm);
-                    else {
-                        uint32_t id = f;
-                        if (CANON) { const uint32_t r = revcomp32(f, K); id = r < f ? r : f; }
-                        atomicAdd(P.tab32 + id, 1u);
-                        kmers++;
-                    }
-                }
-            }
         }
         __syncthreads();
 
-        // ---- phase 2: exclusive scan of the bucket counts; claim room in the global streams ----------
+        // ---- scan: bucket counts -> cursors; claim room in the global streams ------------------------
         uint32_t cnt[PER], sum = 0;
 #pragma unroll
         for (int j = 0; j < PER; j++) {
             const int b = tid * PER + j;
-            cnt[j] = b < NB ? min(s_hist[b], RCAP) : 0u;
+            cnt[j] = b < NB ? s_hist[b] : 0u;
             sum += cnt[j];
         }
         uint32_t inc = sum;
@@ -163,36 +169,38 @@ __global__ void __launch_bounds__(kPartThreads, 2) k3p_partition(const PartParam
         for (int j = 0; j < PER; j++) {
             const int b = tid * PER + j;
             if (b < NB) {
-                s_off[b] = base;
-                base += cnt[j];
+                s_hist[b] = base;
                 uint32_t dl = 0xFFFFFFFFu;
                 if (cnt[j]) {
                     const uint32_t gb = atomicAdd(P.cursor + b, cnt[j]);
                     if (gb + cnt[j] > P.cap) atomicMin(P.fail_base + b, gb);                          // does not fit: RED path
-                    else dl = (uint32_t)b * P.cap + gb - (base - cnt[j]);                             // (host keeps n_buckets * cap < 2^32)
+                    else dl = (uint32_t)b * P.cap + gb - base;                                        // (host keeps n_buckets * cap < 2^32)
                 }
                 s_delta[b] = dl;
+                base += cnt[j];
             }
         }
         __syncthreads();
 
-        // ---- phase 3: scatter my ids to their sorted place ----------------------------------------------
+        // ---- sweep B: every id takes the next slot of its bucket ------------------------------------------
+        if (wb) {
 #pragma unroll
-        for (int e = 0; e < 32; e++) {
-            const uint32_t it = item[e];
-            if (it != 0xFFFFFFFFu) {
-                const uint32_t id = it & mask;
-                s_sorted[s_off[id >> PB] + (it >> (2 * K))] = id;
+            for (int e = 0; e < 32; e++) {
+                const bool valid = (wb & (0x80000000u >> e)) != 0;
+                const uint32_t m = window_top(e);
+                const uint32_t pos = atomicAdd(valid ? s_hist + (m >> (32 - NBITS)) : dummy, 1u);
+                if (valid) s_sorted[pos] = m;
             }
         }
         __syncthreads();
 
-        // ---- phase 4: the sorted array leaves as payload runs, one entry per thread ----------------------
+        // ---- the sorted array leaves as payload runs, one entry per thread ----------------------
+#pragma unroll 4
         for (uint32_t j = tid; j < total; j += kPartThreads) {
-            const uint32_t id = s_sorted[j];
-            const uint32_t dl = s_delta[id >> PB];
-            if (dl != 0xFFFFFFFFu) P.stream[dl + j] = (uint16_t)(id & ((1u << PB) - 1u));
-            else atomicAdd(P.tab32 + id, 1u);
+            const uint32_t m = s_sorted[j];
+            const uint32_t dl = s_delta[m >> (32 - NBITS)];
+            if (dl != 0xFFFFFFFFu) P.stream[dl + j] = (uint16_t)((m >> (32 - 2 * K)) & ((1u << PB) - 1u));
+            else red_aggregated(P.tab32, m >> (32 - 2 * K));         // stream of this bucket is full (low-complexity input): equal ids sit side by side
         }
       }
     }
@@ -253,7 +261,7 @@ __global__ void __launch_bounds__(kBucketThreads) k3p_count(const uint16_t* __re
     for (int i = tid; i < (1 << kTableBits); i += kBucketThreads) { const unsigned int x = s_tab[i]; if (x) atomicAdd(dst + i, x); }
 }
 
-__host__ inline size_t k3p_smem_bytes(int k) { return (size_t)(kTile + 3 * (1 << (2 * k - payload_bits(k)))) * sizeof(uint32_t); }
+__host__ inline size_t k3p_smem_bytes(int k) { return (size_t)(kTile + 2 * (1 << (2 * k - payload_bits(k))) + 32) * sizeof(uint32_t); }
 
 typedef void (*k3p_fn)(const PartParams);
 template <int K>
