@@ -223,6 +223,8 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
         const size_t dyn = k3p_smem_bytes(k);
         if ((e = cudaFuncSetAttribute((const void*)ctx->part_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)) != cudaSuccess) return fail("smem attr", e);
         if ((e = cudaFuncSetAttribute((const void*)k3p_count, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << kTableBits)) != cudaSuccess) return fail("smem attr", e);
+        if ((e = cudaFuncSetAttribute((const void*)k3p_count16, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024)) != cudaSuccess) return fail("smem attr", e);
+        if (payload_bits(k) == 16 && !getenv("KDB_COUNT_SUBPASSES")) ctx->subs = 0;       // 0: one pass with packed 16-bit counters (k3p_count16)
         if (!rc) rc = occupancy_grid(ctx->part_kernel, kPartThreads, dyn, &ctx->part_grid);
         if ((e = cudaMalloc(&ctx->cursor, 2 * ctx->n_buckets * sizeof(unsigned int))) != cudaSuccess) return fail("cudaMalloc cursor", e);
     }
@@ -311,8 +313,9 @@ static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigne
         ctx->part_kernel<<<grid, kPartThreads, k3p_smem_bytes(ctx->k), st>>>(Q);
         CK(cudaGetLastError());
         CK(cudaEventRecord(ctx->ev[7], st));
-        k3p_count<<<ctx->n_buckets * ctx->parts * ctx->subs, kBucketThreads, 4 << kTableBits, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->subs,
-                                                                                                  payload_bits(ctx->k), ctx->tab32);
+        if (ctx->subs == 0) k3p_count16<<<ctx->n_buckets, kCount16Threads, 128 * 1024, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->tab32);
+        else k3p_count<<<ctx->n_buckets * ctx->parts * ctx->subs, kBucketThreads, 4 << kTableBits, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->subs,
+                                                                                                       payload_bits(ctx->k), ctx->tab32);
         CK(cudaGetLastError());
         ctx->timing.total_launches++;
     } else {

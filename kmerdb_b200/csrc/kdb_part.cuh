@@ -261,6 +261,60 @@ __global__ void __launch_bounds__(kBucketThreads) k3p_count(const uint16_t* __re
     for (int i = tid; i < (1 << kTableBits); i += kBucketThreads) { const unsigned int x = s_tab[i]; if (x) atomicAdd(dst + i, x); }
 }
 
+// 16-bit payloads (k = 13, 14): the 65536 bins of a bucket as 16-bit counters, two per shared word (128 KiB), counted in ONE
+// pass over the stream.  The counters are exact: every update is one 32-bit atomicAdd that returns the word it found, so the
+// thread whose +1 wraps the low counter (it found 0xFFFF there) knows it — it moves 65536 to the global bin and takes the
+// carry back out of the high counter; an update that carries out of (or borrows into) the 32-bit word knows that too from
+// the value it found and moves 65536 to / from the global bin of the high counter.  The word is an integer mod 2^32 and
+// every crossing of 2^32 is seen by exactly the update that caused it, so  bin = counter + global part  holds in any
+// interleaving.
+constexpr int kCount16Threads = 1024;
+__device__ __forceinline__ void add16(unsigned int* s_tab, uint32_t bin, unsigned int* gdst) {
+    const uint32_t w = bin >> 1;
+    if ((bin & 1u) == 0) {
+        const uint32_t old = atomicAdd(&s_tab[w], 1u);
+        if ((old & 0xFFFFu) == 0xFFFFu) {
+            atomicAdd(gdst + 2 * w, 65536u);
+            if (old == 0xFFFFFFFFu) atomicAdd(gdst + 2 * w + 1, 65536u);
+            const uint32_t old2 = atomicSub(&s_tab[w], 0x10000u);
+            if ((old2 >> 16) == 0) atomicSub(gdst + 2 * w + 1, 65536u);
+        }
+    } else {
+        const uint32_t old = atomicAdd(&s_tab[w], 0x10000u);
+        if ((old >> 16) == 0xFFFFu) atomicAdd(gdst + 2 * w + 1, 65536u);
+    }
+}
+// grid = n_buckets; one CTA counts one bucket stream
+__global__ void __launch_bounds__(kCount16Threads) k3p_count16(const uint16_t* __restrict__ stream, const unsigned int* __restrict__ cursor,
+                                                               const unsigned int* __restrict__ fail_base, unsigned int cap,
+                                                               unsigned int* __restrict__ tab32) {
+    extern __shared__ unsigned int s_tab[];                           // 32768 words
+    const int tid = threadIdx.x;
+    const uint32_t b = blockIdx.x;
+    uint32_t end = cursor[b];
+    { const uint32_t fb = fail_base[b]; end = end < fb ? end : fb; end = end < cap ? end : cap; }
+    if (end == 0) return;
+    for (int i = tid; i < 32768; i += kCount16Threads) s_tab[i] = 0;
+    __syncthreads();
+    unsigned int* dst = tab32 + ((size_t)b << 16);
+    const uint4* src = reinterpret_cast<const uint4*>(stream + (size_t)b * cap);
+    const uint32_t units = (end + 7) >> 3;
+    for (uint32_t u = tid; u < units; u += kCount16Threads) {
+        const uint4 v = __ldcs(src + u);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        const uint32_t valid = min(8u, end - 8 * u);
+#pragma unroll
+        for (int q = 0; q < 8; q++)
+            if ((uint32_t)q < valid) add16(s_tab, (w[q >> 1] >> (16 * (q & 1))) & 0xFFFFu, dst);
+    }
+    __syncthreads();
+    for (int i = tid; i < 32768; i += kCount16Threads) {
+        const unsigned int x = s_tab[i];
+        if (x & 0xFFFFu) atomicAdd(dst + 2 * i, x & 0xFFFFu);
+        if (x >> 16) atomicAdd(dst + 2 * i + 1, x >> 16);
+    }
+}
+
 __host__ inline size_t k3p_smem_bytes(int k) { return (size_t)(kTile + 2 * (1 << (2 * k - payload_bits(k))) + 32) * sizeof(uint32_t); }
 
 typedef void (*k3p_fn)(const PartParams);

@@ -57,6 +57,7 @@ def _cmp_oracle(data, k, fastq=False, skip_n=True, canonical=True, threads=8):
             assert st[a] == ost[b], a
         nul = p.nullomers()
         assert np.array_equal(nul, np.nonzero(ocounts == 0)[0].astype(np.uint64))
+        return counts
 
 
 def _random_fasta(rng, n_rec, min_len, max_len, width, alphabet="ACGT", p=None, crlf=False):
@@ -233,3 +234,23 @@ def test_configs1_full_vector_vs_oracle():
     assert hashlib.sha256(counts.tobytes()).hexdigest() == hashlib.sha256(ocounts.tobytes()).hexdigest()
     for a in ("total_reads", "total_kmers", "unique_kmers", "sum_len", "min_len", "max_len", "mono"):
         assert st[a] == ost[a], a
+
+
+@pytest.mark.gpu
+@pytest.mark.parametrize("k,canonical", [(13, True), (13, False), (14, True)])
+def test_packed_16bit_counters_wrap_exactly(k, canonical):
+    """k = 13, 14 count the 65536 bins of a bucket as 16-bit counters, two per shared word (k3p_count16).  Two bins far above
+    65535 in the two halves of ONE word, fed concurrently, exercise every carry / borrow path; full vector equality with the
+    oracle.  (The input must be large: a bucket stream takes 3x the average bucket load of the pass before the rest of a
+    crowded bucket is counted by direct REDs.)"""
+    rng = np.random.default_rng(k)
+    n = 9_000_000 if k == 13 else 16_000_000
+    pat = np.frombuffer(("A" * k + "A" * (k - 1) + "C").encode(), dtype=np.uint8).reshape(2, k)      # forward ids 0 and 1
+    which = rng.choice(3, size=n, p=[0.5, 0.4, 0.1])
+    rec = np.empty((n, k + 3), dtype=np.uint8)
+    rec[:, 0] = ord(">"); rec[:, 1] = 10; rec[:, k + 2] = 10
+    rec[:, 2:k + 2] = np.frombuffer(b"ACGT", dtype=np.uint8)[rng.integers(0, 4, size=(n, k), dtype=np.uint8)]
+    for j in (0, 1):
+        rec[which == j, 2:k + 2] = pat[j]
+    counts = _cmp_oracle(rec.reshape(-1).tobytes(), k, canonical=canonical)
+    assert counts[0] > 4_000_000 and counts[1] > 3_000_000
