@@ -43,7 +43,7 @@ json.dump(out, open(os.path.join(root, "profiles", "ncu_full_%s.json" % tag), "w
 for name, e in out.items():
     print(name, json.dumps(e))
 for name, e in out.items():
-    if name.startswith("k3p_partition"):
+    if name.startswith("k3p_partition<12") and "--no-traffic" not in sys.argv:
         rd, wr = e["dram__bytes_read.sum"] * 1e6, e["dram__bytes_write.sum"] * 1e6
         t = {"kernel": name.replace(" ", ""), "source": "ncu --set full --clock-control none, profiles/ncu_full_%s.json (%d bytes of text per launch)" % (tag, text_bytes),
              "text_bytes_per_launch": text_bytes, "dram_bytes_read": rd, "dram_bytes_write": wr, "dram_bytes_per_launch": rd + wr,
