@@ -54,7 +54,7 @@ struct kdb_ctx {
     // bucket-partitioned count (8 <= k <= 12)
     bool partitioned = false;
     k3p_fn part_kernel = nullptr;
-    int part_grid = 0, n_buckets = 0, parts = 1;
+    int part_grid = 0, n_buckets = 0, parts = 1, hist_threads = 0;
     int subs = 1;
     uint16_t* stream = nullptr;
     size_t stream_cap = 0;
@@ -183,7 +183,7 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
     kdb_ctx* ctx = new kdb_ctx();
     ctx->device = device; ctx->k = k; ctx->flags = flags;
     ctx->fastq = flags & KDB_FASTQ; ctx->canonical = flags & KDB_CANONICAL; ctx->skip_n = flags & KDB_SKIP_N;
-    ctx->smem_hist = k <= 7;
+    ctx->smem_hist = k <= 8;
     ctx->short_k = (flags & KDB_EDGE_KPLUS1) ? k - 1 : k;
     ctx->nbins = 1ull << (2 * k);
     auto fail = [&](const char* what, cudaError_t e) -> kdb_ctx* {
@@ -209,12 +209,13 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
     // launch geometry: persistent CTAs, a whole number per SM
     int rc;
     ctx->hist_kernel = k3_kernel(k, ctx->canonical);
-    ctx->hist_dyn = ctx->smem_hist ? ctx->nbins * sizeof(unsigned int) : 0;
+    ctx->hist_dyn = ctx->smem_hist ? (k == 8 ? ctx->nbins / 2 : ctx->nbins) * sizeof(unsigned int) : 0;
     if (ctx->hist_dyn > 48 * 1024 &&
         (e = cudaFuncSetAttribute((const void*)ctx->hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->hist_dyn)) != cudaSuccess)
         return fail("smem attr", e);
-    rc = occupancy_grid(ctx->hist_kernel, kHistThreads, ctx->hist_dyn, &ctx->hist_grid);
-    ctx->partitioned = k >= 8 && k <= 14 && !getenv("KDB_NO_PARTITION");
+    ctx->hist_threads = k == 8 ? 2 * kHistThreads : kHistThreads;      // k = 8: one 128 KiB table per SM, two tiles side by side
+    rc = occupancy_grid(ctx->hist_kernel, ctx->hist_threads, ctx->hist_dyn, &ctx->hist_grid);
+    ctx->partitioned = k >= 9 && k <= 14 && !getenv("KDB_NO_PARTITION");
     if (ctx->partitioned) {
         ctx->part_kernel = k3p_kernel(k, ctx->canonical);
         ctx->n_buckets = 1 << (2 * k - payload_bits(k));
@@ -321,8 +322,9 @@ static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigne
     } else {
         HistParams H{};
         H.packed = src->packed; H.n_tiles = n_tiles; H.skip_n = ctx->skip_n; H.smear = smear; H.tab32 = ctx->tab32; H.acc = ctx->acc;
-        const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->hist_grid);
-        ctx->hist_kernel<<<grid, kHistThreads, ctx->hist_dyn, st>>>(H);
+        const unsigned int sides = ctx->hist_threads / kHistThreads;
+        const int grid = (int)std::min<unsigned int>((n_tiles + sides - 1) / sides, (unsigned int)ctx->hist_grid);
+        ctx->hist_kernel<<<grid, ctx->hist_threads, ctx->hist_dyn, st>>>(H);
         CK(cudaGetLastError());
         CK(cudaEventRecord(ctx->ev[7], st));
     }

@@ -5,7 +5,8 @@
 // letters of a tile's packed region (two code words + the word before them as the k-1 letter halo)
 // and emits one update per set W bit.  K is a template parameter so every shift is an immediate.
 //   k <= 7 : per-CTA shared-memory table (ATOMS), flushed once per CTA with RED
-//   k >= 8 : red.global.add.u32 into the u32 working table (L2-resident up to k = 12)
+//   k = 8  : the same with the 65536 bins as packed 16-bit counters that hand their overflow to the global table (add16)
+//   k >= 9 : red.global.add.u32 into the u32 working table (L2-resident up to k = 12)
 // N windows in expansion mode (kmer.py:550-565) take a generic per-letter path.
 #pragma once
 #include "kdb_common.cuh"
@@ -51,8 +52,27 @@ __device__ __forceinline__ uint32_t shr96(uint32_t w2, uint32_t w1, uint32_t w0)
     else return w2 >> (S - 64);
 }
 
+// 65536 bins as 16-bit counters, two per shared word (128 KiB): k = 8 directly, k = 13 / 14 per bucket (k3p_count16).  The counters are exact: every update is one 32-bit atomicAdd that returns the word it found, so the
+// thread whose +1 wraps the low counter (it found 0xFFFF there) knows it — it moves 65536 to the global bin and takes the
+// carry back out of the high counter; an update that carries out of (or borrows into) the 32-bit word knows that too from
+// the value it found and moves 65536 to / from the global bin of the high counter.  The word is an integer mod 2^32 and
+// every crossing of 2^32 is seen by exactly the update that caused it, so  bin = counter + global part  holds in any
+// interleaving.
+__device__ __forceinline__ void add16(unsigned int* s_tab, uint32_t bin, unsigned int* gdst) {
+    const uint32_t w = bin >> 1, sh = (bin & 1u) << 4;
+    const uint32_t old = atomicAdd(&s_tab[w], 1u << sh);
+    if (((old >> sh) & 0xFFFFu) == 0xFFFFu) {                        // my +1 wrapped my counter (once per 65536 updates of a bin)
+        if (sh == 0) {
+            atomicAdd(gdst + 2 * w, 65536u);
+            if (old == 0xFFFFFFFFu) atomicAdd(gdst + 2 * w + 1, 65536u);       // the carry also ran out of the word
+            const uint32_t old2 = atomicSub(&s_tab[w], 0x10000u);               // take the carry back out of the high counter
+            if ((old2 >> 16) == 0) atomicSub(gdst + 2 * w + 1, 65536u);        // (borrowed from beyond the word)
+        } else atomicAdd(gdst + 2 * w + 1, 65536u);
+    }
+}
+
 template <int K, bool CANON, bool SMEM, int E>
-__device__ __forceinline__ void emit_window(unsigned int* tab, uint32_t prev, uint32_t cur0, uint32_t cur1,
+__device__ __forceinline__ void emit_window(unsigned int* tab, unsigned int* gtab, uint32_t prev, uint32_t cur0, uint32_t cur1,
                                             uint32_t r2, uint32_t r1, uint32_t r0, uint32_t wb) {
     constexpr uint32_t mask = K == 16 ? 0xffffffffu : ((1u << (2 * K)) - 1u);
     if (wb & (0x80000000u >> E)) {
@@ -61,21 +81,22 @@ __device__ __forceinline__ void emit_window(unsigned int* tab, uint32_t prev, ui
             const uint32_t rc = shr96<34 + 2 * E - 2 * K>(r2, r1, r0) & mask;
             id = rc < id ? rc : id;
         }
-        atomicAdd(tab + id, 1u);
+        if (SMEM && K == 8) add16(tab, id, gtab);
+        else atomicAdd(tab + id, 1u);
     }
 }
 
 template <int K, bool CANON, bool SMEM, int E>
 struct EmitAll {
-    static __device__ __forceinline__ void run(unsigned int* tab, uint32_t prev, uint32_t cur0, uint32_t cur1,
+    static __device__ __forceinline__ void run(unsigned int* tab, unsigned int* gtab, uint32_t prev, uint32_t cur0, uint32_t cur1,
                                                uint32_t r2, uint32_t r1, uint32_t r0, uint32_t wb) {
-        emit_window<K, CANON, SMEM, E>(tab, prev, cur0, cur1, r2, r1, r0, wb);
-        EmitAll<K, CANON, SMEM, E + 1>::run(tab, prev, cur0, cur1, r2, r1, r0, wb);
+        emit_window<K, CANON, SMEM, E>(tab, gtab, prev, cur0, cur1, r2, r1, r0, wb);
+        EmitAll<K, CANON, SMEM, E + 1>::run(tab, gtab, prev, cur0, cur1, r2, r1, r0, wb);
     }
 };
 template <int K, bool CANON, bool SMEM>
 struct EmitAll<K, CANON, SMEM, 32> {
-    static __device__ __forceinline__ void run(unsigned int*, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t) {}
+    static __device__ __forceinline__ void run(unsigned int*, unsigned int*, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t, uint32_t) {}
 };
 
 // kmer.py:550-565, :586-621: every ACGT substitution of the N positions gets +1.
@@ -99,19 +120,21 @@ __device__ __noinline__ unsigned long long expand_window(unsigned int* tab, int 
 }
 
 template <int K, bool CANON, bool SMEM>
-__global__ void __launch_bounds__(kHistThreads) k3_count(const HistParams P) {
+__global__ void __launch_bounds__((SMEM && K == 8) ? 2 * kHistThreads : kHistThreads) k3_count(const HistParams P) {          // blockDim.x = kHistThreads, or twice that (two tiles side by side)
     extern __shared__ unsigned int s_tab[];
-    __shared__ unsigned long long s_red[kHistThreads / 32];
-    constexpr uint32_t nbins = 1u << (2 * (K < 16 ? K : 15));     // SMEM only for K <= 7
+    __shared__ unsigned long long s_red[2 * kHistThreads / 32];
+    constexpr uint32_t nbins = 1u << (2 * (K < 16 ? K : 15));     // SMEM only for K <= 8
+    constexpr bool PACK = SMEM && K == 8;                         // k = 8: 65536 bins as packed 16-bit counters (add16)
+    constexpr uint32_t nwords = PACK ? nbins / 2 : nbins;
     constexpr uint32_t mask = K == 16 ? 0xffffffffu : ((1u << (2 * K)) - 1u);
-    const int tid = threadIdx.x;
+    const int tid = threadIdx.x & (kHistThreads - 1), side = threadIdx.x / kHistThreads, sides = blockDim.x / kHistThreads;
     unsigned int* tab = SMEM ? s_tab : P.tab32;
     if (SMEM) {
-        for (uint32_t i = tid; i < nbins; i += kHistThreads) s_tab[i] = 0;
+        for (uint32_t i = threadIdx.x; i < nwords; i += blockDim.x) s_tab[i] = 0;
         __syncthreads();
     }
     unsigned long long kmers = 0;
-    for (unsigned int tile = blockIdx.x; tile < P.n_tiles; tile += gridDim.x) {
+    for (unsigned int tile = blockIdx.x * sides + side; tile < P.n_tiles; tile += gridDim.x * sides) {
         const uint32_t* reg = P.packed + (size_t)tile * kPackStride;
         const uint32_t n = reg[0];
         if ((uint32_t)tid * 32 >= n) continue;
@@ -131,7 +154,7 @@ __global__ void __launch_bounds__(kHistThreads) k3_count(const HistParams P) {
         }
         if (!generic) {
             const uint32_t r2 = CANON ? rc_word(cur1) : 0u, r1 = CANON ? rc_word(cur0) : 0u, r0 = CANON ? rc_word(prev) : 0u;
-            EmitAll<K, CANON, SMEM, 0>::run(tab, prev, cur0, cur1, r2, r1, r0, wb);
+            EmitAll<K, CANON, SMEM, 0>::run(tab, P.tab32, prev, cur0, cur1, r2, r1, r0, wb);
             kmers += __popc(wb);
         } else {
             const unsigned long long S0 = ((unsigned long long)prev << 32) | cur0, S1 = ((unsigned long long)cur0 << 32) | cur1;
@@ -140,26 +163,32 @@ __global__ void __launch_bounds__(kHistThreads) k3_count(const HistParams P) {
                 if (!(wb & (0x80000000u >> e))) continue;
                 const uint32_t f = (uint32_t)((e < 16 ? S0 : S1) >> (30 - 2 * (e & 15))) & mask;
                 const uint32_t nm = (uint32_t)(NS >> (31 - e)) & ((1u << K) - 1u);
-                if (nm) kmers += expand_window(tab, K, CANON, f, nm);
+                unsigned int* const gen = PACK ? P.tab32 : tab;       // (the generic path counts straight into the global table when the shared one is packed)
+                if (nm) kmers += expand_window(gen, K, CANON, f, nm);
                 else {
                     uint32_t id = f;
                     if (CANON) { const uint32_t r = revcomp32(f, K); id = r < f ? r : f; }
-                    atomicAdd(tab + id, 1u);
+                    atomicAdd(gen + id, 1u);
                     kmers++;
                 }
             }
         }
     }
     for (int d = 16; d; d >>= 1) kmers += __shfl_xor_sync(0xffffffffu, kmers, d);
-    if ((tid & 31) == 0) s_red[tid >> 5] = kmers;
+    if ((threadIdx.x & 31) == 0) s_red[threadIdx.x >> 5] = kmers;
     __syncthreads();
-    if (tid == 0) {
+    if (threadIdx.x == 0) {
         unsigned long long s = 0;
-        for (int w = 0; w < kHistThreads / 32; w++) s += s_red[w];
+        for (int w = 0; w < (int)blockDim.x / 32; w++) s += s_red[w];
         if (s) atomicAdd(&P.acc->total_kmers, s);
     }
     if (SMEM) {
-        for (uint32_t i = tid; i < nbins; i += kHistThreads) { const unsigned int x = s_tab[i]; if (x) atomicAdd(P.tab32 + i, x); }
+        __syncthreads();
+        for (uint32_t i = threadIdx.x; i < nwords; i += blockDim.x) {
+            const unsigned int x = s_tab[i];
+            if (PACK) { if (x & 0xFFFFu) atomicAdd(P.tab32 + 2 * i, x & 0xFFFFu); if (x >> 16) atomicAdd(P.tab32 + 2 * i + 1, x >> 16); }
+            else if (x) atomicAdd(P.tab32 + i, x);
+        }
     }
 }
 
@@ -167,7 +196,7 @@ typedef void (*k3_fn)(const HistParams);
 
 template <int K>
 __host__ inline k3_fn k3_select(bool canon) {
-    constexpr bool smem = K <= 7;
+    constexpr bool smem = K <= 8;
     return canon ? (k3_fn)k3_count<K, true, smem> : (k3_fn)k3_count<K, false, smem>;
 }
 

@@ -261,29 +261,8 @@ __global__ void __launch_bounds__(kBucketThreads) k3p_count(const uint16_t* __re
     for (int i = tid; i < (1 << kTableBits); i += kBucketThreads) { const unsigned int x = s_tab[i]; if (x) atomicAdd(dst + i, x); }
 }
 
-// 16-bit payloads (k = 13, 14): the 65536 bins of a bucket as 16-bit counters, two per shared word (128 KiB), counted in ONE
-// pass over the stream.  The counters are exact: every update is one 32-bit atomicAdd that returns the word it found, so the
-// thread whose +1 wraps the low counter (it found 0xFFFF there) knows it — it moves 65536 to the global bin and takes the
-// carry back out of the high counter; an update that carries out of (or borrows into) the 32-bit word knows that too from
-// the value it found and moves 65536 to / from the global bin of the high counter.  The word is an integer mod 2^32 and
-// every crossing of 2^32 is seen by exactly the update that caused it, so  bin = counter + global part  holds in any
-// interleaving.
+// 16-bit payloads (k = 13, 14): the 65536 bins of a bucket as packed 16-bit counters (add16, kdb_hist.cuh), counted in ONE pass.
 constexpr int kCount16Threads = 1024;
-__device__ __forceinline__ void add16(unsigned int* s_tab, uint32_t bin, unsigned int* gdst) {
-    const uint32_t w = bin >> 1;
-    if ((bin & 1u) == 0) {
-        const uint32_t old = atomicAdd(&s_tab[w], 1u);
-        if ((old & 0xFFFFu) == 0xFFFFu) {
-            atomicAdd(gdst + 2 * w, 65536u);
-            if (old == 0xFFFFFFFFu) atomicAdd(gdst + 2 * w + 1, 65536u);
-            const uint32_t old2 = atomicSub(&s_tab[w], 0x10000u);
-            if ((old2 >> 16) == 0) atomicSub(gdst + 2 * w + 1, 65536u);
-        }
-    } else {
-        const uint32_t old = atomicAdd(&s_tab[w], 0x10000u);
-        if ((old >> 16) == 0xFFFFu) atomicAdd(gdst + 2 * w + 1, 65536u);
-    }
-}
 // grid = n_buckets; one CTA counts one bucket stream
 __global__ void __launch_bounds__(kCount16Threads) k3p_count16(const uint16_t* __restrict__ stream, const unsigned int* __restrict__ cursor,
                                                                const unsigned int* __restrict__ fail_base, unsigned int cap,

@@ -237,14 +237,14 @@ def test_configs1_full_vector_vs_oracle():
 
 
 @pytest.mark.gpu
-@pytest.mark.parametrize("k,canonical", [(13, True), (13, False), (14, True)])
+@pytest.mark.parametrize("k,canonical", [(8, True), (8, False), (13, True), (13, False), (14, True)])
 def test_packed_16bit_counters_wrap_exactly(k, canonical):
-    """k = 13, 14 count the 65536 bins of a bucket as 16-bit counters, two per shared word (k3p_count16).  Two bins far above
+    """k = 8 counts its 65536 bins, k = 13, 14 the 65536 bins of a bucket, as 16-bit counters, two per shared word (add16).  Two bins far above
     65535 in the two halves of ONE word, fed concurrently, exercise every carry / borrow path; full vector equality with the
     oracle.  (The input must be large: a bucket stream takes 3x the average bucket load of the pass before the rest of a
     crowded bucket is counted by direct REDs.)"""
     rng = np.random.default_rng(k)
-    n = 9_000_000 if k == 13 else 16_000_000
+    n = {8: 30_000_000, 13: 9_000_000, 14: 16_000_000}[k]      # k = 8: one shared table per CTA, 148 CTAs share the reads
     pat = np.frombuffer(("A" * k + "A" * (k - 1) + "C").encode(), dtype=np.uint8).reshape(2, k)      # forward ids 0 and 1
     which = rng.choice(3, size=n, p=[0.5, 0.4, 0.1])
     rec = np.empty((n, k + 3), dtype=np.uint8)
