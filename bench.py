@@ -119,7 +119,7 @@ def run_reference(args):
             "config": workload_config(args, args.gpus),
             "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    _emit(line)
 
 
 def workload_config(args, n_gpus):
@@ -282,13 +282,28 @@ def run_b200(args):
             dt, ost = time_oracle(text, k, threads)
             line["cpu_baseline"] = {"value": args.cpu_reads * READ_LEN / dt, "unit": UNIT, "cores": threads, "kind": "port",
                                     "sample": "first %d reads of the same stream, oracle/kmerdb_oracle.c on %d threads, %.1f s" % (args.cpu_reads, threads, dt)}
-        print(json.dumps(line), flush=True)
+        _emit(line)
     if world > 1:
         dist.barrier()
         dist.destroy_process_group()
 
 
+_JSON_OUT = None
+
+
+def _emit(line):
+    """The one JSON line goes to the process's real stdout; everything a library prints (NCCL's version banner, warnings)
+    was moved to stderr by main()."""
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(line) + "\n")
+    out.flush()
+
+
 def main():
+    global _JSON_OUT
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)                                   # fd 1 -> stderr for the rest of the run (C libraries included)
     ap = argparse.ArgumentParser()
     ap.add_argument("--gpus", type=int, default=1)
     ap.add_argument("--steps", type=int, default=20)
