@@ -23,22 +23,23 @@ def _unordered_u64(i):
 
 
 def combine_partials(part16, dist, device, dst=0):
-    """Reduce the 16-word scalar packs of all ranks to `dst`.  Returns the combined pack on dst, None elsewhere.
-    Sums are exact in two's complement; min/max use an order-preserving map of uint64 into int64."""
+    """Combine the 16-word scalar packs of all ranks.  Returns the combined pack on dst, None elsewhere.
+    One collective (all_gather of 128 bytes per rank) and one copy each way; the words are then folded on the host:
+    sums wrap like the device's uint64 arithmetic, min / max are taken on the unsigned values."""
     import torch
-    p = np.asarray(part16, dtype=np.uint64)
-    sums = torch.from_numpy(p[SUM_WORDS].view(np.int64).copy()).to(device)
-    mins = torch.from_numpy(_ordered_i64(p[list(MIN_WORDS)]).copy()).to(device)
-    maxs = torch.from_numpy(_ordered_i64(p[list(MAX_WORDS)]).copy()).to(device)
-    dist.reduce(sums, dst=dst, op=dist.ReduceOp.SUM)
-    dist.reduce(mins, dst=dst, op=dist.ReduceOp.MIN)
-    dist.reduce(maxs, dst=dst, op=dist.ReduceOp.MAX)
+    p = np.ascontiguousarray(part16, dtype=np.uint64)
+    mine = torch.from_numpy(p.view(np.int64).copy()).to(device)
+    world = dist.get_world_size()
+    allp = torch.empty(world * 16, dtype=torch.int64, device=device)
+    dist.all_gather_into_tensor(allp, mine)
     if dist.get_rank() != dst:
         return None
+    g = allp.cpu().numpy().view(np.uint64).reshape(world, 16)
     out = np.zeros(16, dtype=np.uint64)
-    out[SUM_WORDS] = sums.cpu().numpy().view(np.uint64)
-    out[list(MIN_WORDS)] = _unordered_u64(mins.cpu().numpy())
-    out[list(MAX_WORDS)] = _unordered_u64(maxs.cpu().numpy())
+    with np.errstate(over="ignore"):
+        out[SUM_WORDS] = g[:, SUM_WORDS].sum(axis=0, dtype=np.uint64)
+    out[list(MIN_WORDS)] = g[:, list(MIN_WORDS)].min(axis=0)
+    out[list(MAX_WORDS)] = g[:, list(MAX_WORDS)].max(axis=0)
     return out
 
 
