@@ -56,6 +56,7 @@ struct kdb_ctx {
     k3p_fn part_kernel = nullptr;
     int part_grid = 0, n_buckets = 0, parts = 1, hist_threads = 0;
     int subs = 1;
+    bool wide = false;
     uint16_t* stream = nullptr;
     size_t stream_cap = 0;
     unsigned int* cursor = nullptr;             // n_buckets cursors + n_buckets fail bases
@@ -220,12 +221,14 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
         ctx->part_kernel = k3p_kernel(k, ctx->canonical);
         ctx->n_buckets = 1 << (2 * k - payload_bits(k));
         ctx->subs = 1 << (payload_bits(k) - kTableBits);
+        ctx->wide = payload_bits(k) > 16;                                                   // 32-bit stream entries (k = 14)
         ctx->parts = std::max(1, (1776 + ctx->n_buckets - 1) / ctx->n_buckets);
         const size_t dyn = k3p_smem_bytes(k);
         if ((e = cudaFuncSetAttribute((const void*)ctx->part_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)) != cudaSuccess) return fail("smem attr", e);
         if ((e = cudaFuncSetAttribute((const void*)k3p_count, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << kTableBits)) != cudaSuccess) return fail("smem attr", e);
         if ((e = cudaFuncSetAttribute((const void*)k3p_count16, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024)) != cudaSuccess) return fail("smem attr", e);
-        if (payload_bits(k) == 16 && !getenv("KDB_COUNT_SUBPASSES")) ctx->subs = 0;       // 0: one pass with packed 16-bit counters (k3p_count16)
+        if ((e = cudaFuncSetAttribute((const void*)k3p_count16w, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024)) != cudaSuccess) return fail("smem attr", e);
+        if (payload_bits(k) >= 16) ctx->subs = 0;                                           // 0: packed 16-bit counters (k3p_count16 / k3p_count16w)
         if (!rc) rc = occupancy_grid(ctx->part_kernel, kPartThreads, dyn, &ctx->part_grid);
         if ((e = cudaMalloc(&ctx->cursor, 2 * ctx->n_buckets * sizeof(unsigned int))) != cudaSuccess) return fail("cudaMalloc cursor", e);
     }
@@ -304,7 +307,7 @@ static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigne
         const unsigned int cap = (unsigned int)((3 * avg + kTile + 7) & ~7ull);   // >= kTile: keeps s_delta (kdb_part.cuh) from wrapping
         if ((unsigned long long)cap * ctx->n_buckets >= 0xFFFFFFFFull) { ctx->err = "bucket stream index exceeds 32 bits"; return KDB_E_ARG; }
         // the bucket streams live in the leader: the k of a sweep are counted one after the other on one stream
-        if (int rc = ensure(src, (void**)&src->stream, &src->stream_cap, (size_t)cap * ctx->n_buckets, sizeof(uint16_t))) { ctx->err = src->err; return rc; }
+        if (int rc = ensure(src, (void**)&src->stream, &src->stream_cap, (size_t)cap * ctx->n_buckets * (ctx->wide ? 2 : 1), sizeof(uint16_t))) { ctx->err = src->err; return rc; }
         CK(cudaMemsetAsync(ctx->cursor, 0, ctx->n_buckets * sizeof(unsigned int), st));
         CK(cudaMemsetAsync(ctx->cursor + ctx->n_buckets, 0xFF, ctx->n_buckets * sizeof(unsigned int), st));
         PartParams Q{};
@@ -314,7 +317,8 @@ static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigne
         ctx->part_kernel<<<grid, kPartThreads, k3p_smem_bytes(ctx->k), st>>>(Q);
         CK(cudaGetLastError());
         CK(cudaEventRecord(ctx->ev[7], st));
-        if (ctx->subs == 0) k3p_count16<<<ctx->n_buckets, kCount16Threads, 128 * 1024, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->tab32);
+        if (ctx->wide) k3p_count16w<<<ctx->n_buckets * 4, kCount16Threads, 128 * 1024, st>>>(reinterpret_cast<const uint32_t*>(src->stream), Q.cursor, Q.fail_base, cap, ctx->tab32);
+        else if (ctx->subs == 0) k3p_count16<<<ctx->n_buckets, kCount16Threads, 128 * 1024, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->tab32);
         else k3p_count<<<ctx->n_buckets * ctx->parts * ctx->subs, kBucketThreads, 4 << kTableBits, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->subs,
                                                                                                        payload_bits(ctx->k), ctx->tab32);
         CK(cudaGetLastError());

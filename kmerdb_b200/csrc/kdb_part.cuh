@@ -20,9 +20,10 @@
 namespace kdb {
 
 constexpr int kTableBits = 14;                         // 16384 bins x 4 B = 64 KiB shared count table
-// payload bits kept in the 16-bit stream entries: 14 for k <= 12 (one table per bucket); 16 for k = 13, 14
-// (the bucket is counted in 4 sub-passes of 14 bits each, so the bucket count stays at 1024 / 4096)
-__host__ __device__ constexpr int payload_bits(int k) { return k <= 12 ? 14 : 16; }
+// payload bits of a stream entry: 14 for k <= 12 (one 16384-bin table per bucket, 16-bit entries); 16 for k = 13 (65536 packed
+// 16-bit counters per bucket, k3p_count16); 18 for k = 14 (32-bit entries, 1024 buckets, four sub-passes of 16 bits: with 16-bit
+// payloads k = 14 needs 4096 buckets, which leaves 4 entries per bucket per tile — 8-byte runs and one cursor bump per 4 keys)
+__host__ __device__ constexpr int payload_bits(int k) { return k <= 12 ? 14 : (k == 13 ? 16 : 18); }
 constexpr int kPartThreads = 512;                      // 512 threads x 32 letters = one full tile
 constexpr int kBucketThreads = 256;
 
@@ -32,7 +33,7 @@ struct PartParams {
     int skip_n;
     int smear;                   // k - (k the packed stream was encoded for), kdb_hist.cuh smear_w
     unsigned int* tab32;
-    uint16_t* stream;            // n_buckets * cap entries
+    uint16_t* stream;            // n_buckets * cap entries (32-bit entries when payload_bits > 16)
     unsigned int* cursor;        // n_buckets: entries claimed so far
     unsigned int* fail_base;     // n_buckets: lowest base of a run that did not fit (0xFFFFFFFF = none)
     unsigned int cap;            // entries per bucket (multiple of 8)
@@ -199,7 +200,10 @@ __global__ void __launch_bounds__(kPartThreads, 3) k3p_partition(const PartParam
         for (uint32_t j = tid; j < total; j += kPartThreads) {
             const uint32_t m = s_sorted[j];
             const uint32_t dl = s_delta[m >> (32 - NBITS)];
-            if (dl != 0xFFFFFFFFu) P.stream[dl + j] = (uint16_t)((m >> (32 - 2 * K)) & ((1u << PB) - 1u));
+            if (dl != 0xFFFFFFFFu) {
+                if (PB > 16) reinterpret_cast<uint32_t*>(P.stream)[dl + j] = (m >> (32 - 2 * K)) & ((1u << PB) - 1u);
+                else P.stream[dl + j] = (uint16_t)((m >> (32 - 2 * K)) & ((1u << PB) - 1u));
+            }
             else red_aggregated(P.tab32, m >> (32 - 2 * K));         // stream of this bucket is full (low-complexity input): equal ids sit side by side
         }
       }
@@ -285,6 +289,48 @@ __global__ void __launch_bounds__(kCount16Threads) k3p_count16(const uint16_t* _
 #pragma unroll
         for (int q = 0; q < 8; q++)
             if ((uint32_t)q < valid) add16(s_tab, (w[q >> 1] >> (16 * (q & 1))) & 0xFFFFu, dst);
+    }
+    __syncthreads();
+    for (int i = tid; i < 32768; i += kCount16Threads) {
+        const unsigned int x = s_tab[i];
+        if (x & 0xFFFFu) atomicAdd(dst + 2 * i, x & 0xFFFFu);
+        if (x >> 16) atomicAdd(dst + 2 * i + 1, x >> 16);
+    }
+}
+
+// 18-bit payloads in 32-bit entries (k = 14): grid = n_buckets * 4; CTA (b, sub) counts the entries of bucket b whose payload
+// bits above 16 equal sub (the four CTAs of a bucket run next to each other: the re-reads hit L2)
+__global__ void __launch_bounds__(kCount16Threads) k3p_count16w(const uint32_t* __restrict__ stream, const unsigned int* __restrict__ cursor,
+                                                                const unsigned int* __restrict__ fail_base, unsigned int cap,
+                                                                unsigned int* __restrict__ tab32) {
+    extern __shared__ unsigned int s_tab[];                           // 32768 words
+    const int tid = threadIdx.x;
+    const uint32_t b = blockIdx.x >> 2, sub = blockIdx.x & 3u;
+    uint32_t end = cursor[b];
+    { const uint32_t fb = fail_base[b]; end = end < fb ? end : fb; end = end < cap ? end : cap; }
+    if (end == 0) return;
+    for (int i = tid; i < 32768; i += kCount16Threads) s_tab[i] = 0;
+    __syncthreads();
+    unsigned int* dst = tab32 + ((size_t)b << 18) + ((size_t)sub << 16);
+    const uint4* src = reinterpret_cast<const uint4*>(stream + (size_t)b * cap);
+    const uint32_t units = (end + 3) >> 2;
+    // four 16-byte loads in flight per thread: one CTA per SM has to cover the L2 latency on its own
+    for (uint32_t u0 = 0; u0 < units; u0 += 4 * kCount16Threads) {
+        uint4 v[4];
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const uint32_t u = u0 + r * kCount16Threads + tid;
+            v[r] = u < units ? __ldg(src + u) : make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);    // (payloads have 18 bits: no sub matches)
+        }
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const uint32_t u = u0 + r * kCount16Threads + tid;
+            const uint32_t w[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
+            const uint32_t valid = u < units ? min(4u, end - 4 * u) : 0u;
+#pragma unroll
+            for (int q = 0; q < 4; q++)
+                if ((uint32_t)q < valid && (w[q] >> 16) == sub) add16(s_tab, w[q] & 0xFFFFu, dst);
+        }
     }
     __syncthreads();
     for (int i = tid; i < 32768; i += kCount16Threads) {
