@@ -186,6 +186,14 @@ int kdb_reader_feed(kdb_reader* r, const uint8_t* text, size_t n_bytes);
 int kdb_reader_finish(kdb_reader* r, uint64_t* counts, uint64_t* kmer_ids, uint64_t* n_rows, uint64_t* err_row);
 void kdb_reader_destroy(kdb_reader* r);
 
+/* ---- Pearson correlation of count profiles (kmerdb/distance.pyx:108-152 `correlation`, one call per pair of samples in
+ * kmerdb.distances, kmerdb/__init__.py:733-742) ------------------------------------------------------
+ * profiles: host, sample-major [n_samples][n_bins] (the transposed matrix of __init__.py:720).  out: [n_samples][n_samples],
+ * out[i][j] = ssxy / sqrt(ssxx * ssyy); NaN where a profile is constant, as the reference's division gives.
+ * mode 0: the arithmetic of the reference as compiled (float32 mean, residuals and products — `cdef float x_bar`, distance.pyx:118 —
+ *         summed in extended precision); mode 1: float64 throughout (the textbook coefficient). */
+int kdb_correlation_matrix(int device, const uint64_t* profiles, size_t n_samples, size_t n_bins, int mode, double* out);
+
 /* Synthetic benchmark input: n_reads records of read_len i.i.d. uniform ACGT letters,
  * FASTA framing ">%09d\n" + letters + "\n" (or FASTQ framing), written straight into HBM.
  * read index = first_read + i; counter-based generator, reproducible on the host

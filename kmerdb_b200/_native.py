@@ -20,7 +20,7 @@ EXPORTS = [
     "kdb_synth_host", "kdb_microbench_atomics", "kdb_dev_alloc", "kdb_dev_free", "kdb_host_alloc_pinned",
     "kdb_host_free_pinned", "kdb_memcpy_h2d", "kdb_memcpy_d2h",
     "kdb_edge_rows", "kdb_edge_weights", "kdb_minimizers_compat", "kdb_minimizers", "kdb_attach", "kdb_format_rows", "kdb_minimizers_batch",
-    "kdb_reader_create", "kdb_reader_feed", "kdb_reader_finish", "kdb_reader_destroy",
+    "kdb_reader_create", "kdb_reader_feed", "kdb_reader_finish", "kdb_reader_destroy", "kdb_correlation_matrix",
 ]
 
 
@@ -79,6 +79,7 @@ def lib():
         ("kdb_minimizers_compat", [ci, vp, sz, ci, u64, vp, vp, sz, ctypes.POINTER(sz)]),
         ("kdb_minimizers", [ci, vp, sz, ci, ci, vp, vp, sz, ctypes.POINTER(sz)]),
         ("kdb_minimizers_batch", [ci, vp, sz, vp, sz, ci, ci, vp, vp, vp, sz, ctypes.POINTER(sz)]),
+        ("kdb_correlation_matrix", [ci, vp, sz, sz, ci, vp]),
         ("kdb_reader_feed", [vp, vp, sz]), ("kdb_reader_finish", [vp, vp, vp, ctypes.POINTER(u64), ctypes.POINTER(u64)]),
     ]:
         fn = getattr(L, name)
@@ -429,3 +430,14 @@ class RowReader:
             self.close()
         except Exception:
             pass
+
+
+def correlation_matrix(profiles, mode=0, device=0):
+    """kdb_correlation_matrix: float64[n, n] Pearson coefficients of the rows of `profiles` (uint64[n, 4^k])."""
+    x = np.ascontiguousarray(profiles, dtype=np.uint64)
+    if x.ndim != 2:
+        raise ValueError("correlation_matrix expects a 2-d array, one profile per row")
+    out = np.empty((x.shape[0], x.shape[0]), dtype=np.float64)
+    if lib().kdb_correlation_matrix(int(device), x.ctypes.data, x.shape[0], x.shape[1], int(mode), out.ctypes.data):
+        raise NativeError("kdb_correlation_matrix: " + _err())
+    return out

@@ -20,6 +20,7 @@
 #include "kdb_graph.cuh"
 #include "kdb_rows.cuh"
 #include "kdb_read.cuh"
+#include "kdb_corr.cuh"
 
 using namespace kdb;
 
@@ -1148,5 +1149,51 @@ extern "C" int kdb_reader_finish(kdb_reader* r, uint64_t* counts, uint64_t* kmer
     if (err != ~0ull) { if (err_row) *err_row = err >> 3; return KDB_R_BASE + (int)(err & 7); }
     if (counts) CK(cudaMemcpy(counts, r->d_counts.p, r->n_bins * 8, cudaMemcpyDeviceToHost));
     if (kmer_ids) CK(cudaMemcpy(kmer_ids, r->d_ids.p, r->n_bins * 8, cudaMemcpyDeviceToHost));
+    return KDB_OK;
+}
+
+// ---- Pearson correlation of count profiles (kmerdb/distance.pyx:108-152, called per pair at __init__.py:733-742) ----
+extern "C" int kdb_correlation_matrix(int device, const uint64_t* profiles, size_t n_samples, size_t n_bins, int mode, double* out) {
+    kdb_ctx* ctx = nullptr;
+    if (!profiles || !out || n_samples == 0 || n_bins == 0 || n_samples > 4096 || (mode != 0 && mode != 1)) return KDB_E_ARG;
+    CK(cudaSetDevice(device));
+    const int n = (int)n_samples;
+    const unsigned int blocks = (unsigned int)std::min<size_t>(148 * 8, (n_bins + kCorrThreads - 1) / kCorrThreads);
+    constexpr int Q = kCorrTile * kCorrTile;
+    DevBuf d_x, d_sums, d_mean, d_part;
+    CK(d_x.alloc(n_samples * n_bins * 8)); CK(d_sums.alloc(n_samples * 8)); CK(d_mean.alloc(n_samples * 8)); CK(d_part.alloc((size_t)blocks * Q * sizeof(DD)));
+    CK(cudaMemcpy(d_x.p, profiles, n_samples * n_bins * 8, cudaMemcpyHostToDevice));
+    CK(cudaMemset(d_sums.p, 0, n_samples * 8));
+    k11_sums<<<dim3(blocks, (unsigned int)n), kCorrThreads>>>(d_x.as<unsigned long long>(), n_bins, d_sums.as<unsigned long long>());
+    CK(cudaGetLastError());
+    std::vector<unsigned long long> sums(n);
+    CK(cudaMemcpy(sums.data(), d_sums.p, n_samples * 8, cudaMemcpyDeviceToHost));
+    std::vector<double> mean(n);
+    for (int s = 0; s < n; s++) {
+        const double m = (double)sums[s] / (double)n_bins;                  // np.sum(a) / total_kmers in float64 (distance.pyx:118)
+        mean[s] = mode == 0 ? (double)(float)m : m;                         // `cdef float x_bar`
+    }
+    CK(cudaMemcpy(d_mean.p, mean.data(), n_samples * 8, cudaMemcpyHostToDevice));
+    std::vector<long double> S((size_t)n * n, 0.0L);
+    std::vector<DD> part((size_t)blocks * Q);
+    for (int i0 = 0; i0 < n; i0 += kCorrTile)
+        for (int j0 = i0; j0 < n; j0 += kCorrTile) {
+            if (mode == 0) k11_products<0><<<blocks, kCorrThreads>>>(d_x.as<unsigned long long>(), n_bins, n, d_mean.as<double>(), i0, j0, d_part.as<DD>());
+            else k11_products<1><<<blocks, kCorrThreads>>>(d_x.as<unsigned long long>(), n_bins, n, d_mean.as<double>(), i0, j0, d_part.as<DD>());
+            CK(cudaGetLastError());
+            CK(cudaMemcpy(part.data(), d_part.p, part.size() * sizeof(DD), cudaMemcpyDeviceToHost));
+            for (int a = 0; a < kCorrTile && i0 + a < n; a++)
+                for (int b = 0; b < kCorrTile && j0 + b < n; b++) {
+                    long double acc = 0.0L;                                  // the reference's `long double` sums (distance.pyx:111-116)
+                    for (unsigned int blk = 0; blk < blocks; blk++) { const DD v = part[(size_t)blk * Q + a * kCorrTile + b]; acc += (long double)v.hi; acc += (long double)v.lo; }
+                    S[(size_t)(i0 + a) * n + (j0 + b)] = acc;
+                    S[(size_t)(j0 + b) * n + (i0 + a)] = acc;
+                }
+        }
+    for (int i = 0; i < n; i++)
+        for (int j = 0; j < n; j++) {
+            const double prod = (double)(S[(size_t)i * n + i] * S[(size_t)j * n + j]);       // np.sqrt receives a Python float (distance.pyx:151)
+            out[(size_t)i * n + j] = (double)(S[(size_t)i * n + j] / (long double)std::sqrt(prod));
+        }
     return KDB_OK;
 }
