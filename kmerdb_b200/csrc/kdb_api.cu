@@ -211,7 +211,7 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
     // launch geometry: persistent CTAs, a whole number per SM
     int rc;
     ctx->hist_kernel = k3_kernel(k, ctx->canonical);
-    ctx->hist_dyn = ctx->smem_hist ? (k == 8 ? ctx->nbins / 2 : ctx->nbins) * sizeof(unsigned int) : 0;
+    ctx->hist_dyn = ctx->smem_hist ? ((k == 8 ? ctx->nbins / 2 : ctx->nbins) + 32) * sizeof(unsigned int) : 0;     // + 32 per-lane dummy words (kdb_hist.cuh)
     if (ctx->hist_dyn > 48 * 1024 &&
         (e = cudaFuncSetAttribute((const void*)ctx->hist_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)ctx->hist_dyn)) != cudaSuccess)
         return fail("smem attr", e);

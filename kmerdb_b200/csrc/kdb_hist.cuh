@@ -52,23 +52,30 @@ __device__ __forceinline__ uint32_t shr96(uint32_t w2, uint32_t w1, uint32_t w0)
     else return w2 >> (S - 64);
 }
 
+// 32 bits of the 96-bit string w0:w1:w2 (most significant first) starting at bit o; o is a compile-time constant after unrolling.
+__device__ __forceinline__ uint32_t ext96(uint32_t w0, uint32_t w1, uint32_t w2, int o) {
+    return o < 32 ? (o == 0 ? w0 : __funnelshift_l(w1, w0, o)) : (o < 64 ? (o == 32 ? w1 : __funnelshift_l(w2, w1, o - 32)) : (w2 << (o - 64)));
+}
+
 // 65536 bins as 16-bit counters, two per shared word (128 KiB): k = 8 directly, k = 13 / 14 per bucket (k3p_count16).  The counters are exact: every update is one 32-bit atomicAdd that returns the word it found, so the
 // thread whose +1 wraps the low counter (it found 0xFFFF there) knows it — it moves 65536 to the global bin and takes the
 // carry back out of the high counter; an update that carries out of (or borrows into) the 32-bit word knows that too from
 // the value it found and moves 65536 to / from the global bin of the high counter.  The word is an integer mod 2^32 and
 // every crossing of 2^32 is seen by exactly the update that caused it, so  bin = counter + global part  holds in any
 // interleaving.
+// what the update that found `old` in word w owes when its +1 (at bit sh) wrapped its 16-bit counter
+__device__ __forceinline__ void add16_fix(unsigned int* s_tab, uint32_t w, uint32_t sh, uint32_t old, unsigned int* gdst) {
+    if (sh == 0) {
+        atomicAdd(gdst + 2 * w, 65536u);
+        if (old == 0xFFFFFFFFu) atomicAdd(gdst + 2 * w + 1, 65536u);       // the carry also ran out of the word
+        const uint32_t old2 = atomicSub(&s_tab[w], 0x10000u);               // take the carry back out of the high counter
+        if ((old2 >> 16) == 0) atomicSub(gdst + 2 * w + 1, 65536u);        // (borrowed from beyond the word)
+    } else atomicAdd(gdst + 2 * w + 1, 65536u);
+}
 __device__ __forceinline__ void add16(unsigned int* s_tab, uint32_t bin, unsigned int* gdst) {
     const uint32_t w = bin >> 1, sh = (bin & 1u) << 4;
     const uint32_t old = atomicAdd(&s_tab[w], 1u << sh);
-    if (((old >> sh) & 0xFFFFu) == 0xFFFFu) {                        // my +1 wrapped my counter (once per 65536 updates of a bin)
-        if (sh == 0) {
-            atomicAdd(gdst + 2 * w, 65536u);
-            if (old == 0xFFFFFFFFu) atomicAdd(gdst + 2 * w + 1, 65536u);       // the carry also ran out of the word
-            const uint32_t old2 = atomicSub(&s_tab[w], 0x10000u);               // take the carry back out of the high counter
-            if ((old2 >> 16) == 0) atomicSub(gdst + 2 * w + 1, 65536u);        // (borrowed from beyond the word)
-        } else atomicAdd(gdst + 2 * w + 1, 65536u);
-    }
+    if (((old >> sh) & 0xFFFFu) == 0xFFFFu) add16_fix(s_tab, w, sh, old, gdst);    // once per 65536 updates of a bin
 }
 
 template <int K, bool CANON, bool SMEM, int E>
@@ -154,7 +161,25 @@ __global__ void __launch_bounds__((SMEM && K == 8) ? 2 * kHistThreads : kHistThr
         }
         if (!generic) {
             const uint32_t r2 = CANON ? rc_word(cur1) : 0u, r1 = CANON ? rc_word(cur0) : 0u, r0 = CANON ? rc_word(prev) : 0u;
-            EmitAll<K, CANON, SMEM, 0>::run(tab, P.tab32, prev, cur0, cur1, r2, r1, r0, wb);
+            if (SMEM) {
+                // shared tables: ids top-aligned (no masks), and a letter without a window bumps a per-lane dummy word behind the
+                // table, so that the atomics are unconditional and pipeline (see k3p_partition, kdb_part.cuh)
+                unsigned int* const dummy = s_tab + nwords + (threadIdx.x & 31);
+#pragma unroll
+                for (int e = 0; e < 32; e++) {
+                    const bool valid = (wb & (0x80000000u >> e)) != 0;
+                    uint32_t m = ext96(prev, cur0, cur1, 2 * (17 + e - K));
+                    if (CANON) { const uint32_t rc = ext96(r2, r1, r0, 62 - 2 * e); m = rc < m ? rc : m; }
+                    uint32_t id = m >> (32 - 2 * K);
+                    asm volatile("" : "+r"(id));                         // (keeps the id arithmetic out of a branch built for the select)
+                    if (!PACK) atomicAdd(valid ? s_tab + id : dummy, 1u);
+                    else {
+                        const uint32_t w = id >> 1, sh = (id & 1u) << 4;
+                        const uint32_t old = atomicAdd(valid ? s_tab + w : dummy, 1u << sh);
+                        if (valid && ((old >> sh) & 0xFFFFu) == 0xFFFFu) add16_fix(s_tab, w, sh, old, P.tab32);
+                    }
+                }
+            } else EmitAll<K, CANON, SMEM, 0>::run(tab, P.tab32, prev, cur0, cur1, r2, r1, r0, wb);
             kmers += __popc(wb);
         } else {
             const unsigned long long S0 = ((unsigned long long)prev << 32) | cur0, S1 = ((unsigned long long)cur0 << 32) | cur1;

@@ -56,10 +56,6 @@ __device__ __forceinline__ void red_aggregated(unsigned int* tab32, uint32_t id)
 // per-bucket cursors, sweep B recomputes each id and takes its place from the cursor.  Nothing but the packed words is
 // kept in registers between the sweeps, so three CTAs fit one SM (the register array of a one-sweep rank sort allows two),
 // and a crowded bucket needs no special case (no rank is packed beside the id).
-// 32 bits of the 96-bit string w0:w1:w2 (most significant first) starting at bit o; o is a compile-time constant after unrolling.
-__device__ __forceinline__ uint32_t ext96(uint32_t w0, uint32_t w1, uint32_t w2, int o) {
-    return o < 32 ? (o == 0 ? w0 : __funnelshift_l(w1, w0, o)) : (o < 64 ? (o == 32 ? w1 : __funnelshift_l(w2, w1, o - 32)) : (w2 << (o - 64)));
-}
 template <int K, bool CANON>
 __global__ void __launch_bounds__(kPartThreads, 3) k3p_partition(const PartParams P) {
     constexpr int PB = payload_bits(K);
