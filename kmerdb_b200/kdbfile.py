@@ -17,6 +17,15 @@ _BGZF_EOF = bytes.fromhex("1f8b08040000000000ff0600424302001b0003000000000000000
 _BLOCK = 65536 - 256                                     # payload per BGZF block (Bio.bgzf writes <= 65536; leave room for incompressible data)
 
 
+def _host_threads():
+    """Threads for the deflate / inflate pools: the CPUs this process may run on, at most 32."""
+    import os
+    try:
+        return max(1, min(32, len(os.sched_getaffinity(0))))
+    except AttributeError:
+        return max(1, min(32, os.cpu_count() or 1))
+
+
 def bgzf_block(data, level=6):
     """One BGZF block (gzip member with the BC extra field holding the block size)."""
     c = zlib.compressobj(level, zlib.DEFLATED, -15, zlib.DEF_MEM_LEVEL, 0)
@@ -62,11 +71,12 @@ def count_strings(counts, total_kmers):
     return uniq, off, b"".join(strs)
 
 
-def write_kdb_gpu(path, metadata, counts, device=0, threads=8, quiet=True, rows_per_call=1 << 22):
+def write_kdb_gpu(path, metadata, counts, device=0, threads=None, quiet=True, rows_per_call=1 << 22):
     """write_kdb with the rows assembled on the GPU (kdb_format_rows); BGZF deflate on host threads."""
     from . import _native
     head, md = header_bytes(metadata)
     uniq, off, blob = count_strings(counts, md["total_kmers"])
+    threads = threads or _host_threads()
 
     def deflate(buf):
         return b"".join(bgzf_block(bytes(buf[o:o + _BLOCK])) for o in range(0, len(buf), _BLOCK))
@@ -87,11 +97,12 @@ def write_kdb_gpu(path, metadata, counts, device=0, threads=8, quiet=True, rows_
     return md
 
 
-def write_kdb(path, metadata, counts, threads=8, quiet=True, rows_per_task=1 << 15):
+def write_kdb(path, metadata, counts, threads=None, quiet=True, rows_per_task=1 << 15):
     """Write `<path>`: header block(s), 4^k rows, BGZF EOF marker (rows formatted on the host)."""
     head, md = header_bytes(metadata)
     total = md["total_kmers"]
     n = len(counts)
+    threads = threads or _host_threads()
 
     def task(lo):
         body = format_rows(lo, counts[lo:lo + rows_per_task], total)
@@ -116,7 +127,7 @@ _ROW_ERRORS = {33: (AssertionError, "kmerdb.fileutil.KDBReader requires .kdb fil
                37: (ValueError, "a k-mer id appears on two rows")}
 
 
-def _inflate_groups(raw, threads=8, group=2048):
+def _inflate_groups(raw, threads=None, group=2048):
     """The inflated text of a BGZF file, yielded in pieces of `group` blocks (inflate on a thread pool)."""
     from .parse import _bgzf_blocks
     blocks = _bgzf_blocks(raw)
@@ -124,7 +135,7 @@ def _inflate_groups(raw, threads=8, group=2048):
         yield gzip.decompress(raw)
         return
     mv = memoryview(raw)
-    with ThreadPoolExecutor(max_workers=threads) as ex:
+    with ThreadPoolExecutor(max_workers=threads or _host_threads()) as ex:
         for g in range(0, len(blocks), group):
             yield b"".join(ex.map(lambda b: zlib.decompress(mv[b[0] + 18:b[0] + b[1] - 8], -15), blocks[g:g + group]))
 
@@ -134,7 +145,7 @@ class KDBReader:
     (kmerdb/fileutil.py:KDBReader with slurp=True, sort=False, :308-377).  The row loop runs on the GPU
     (kdb_reader_*, kdb_read.cuh); header YAML and BGZF inflate stay on the host."""
 
-    def __init__(self, path, slurp=True, device=0, threads=8):
+    def __init__(self, path, slurp=True, device=0, threads=None):
         from . import _native
         self._filepath = path
         with open(path, "rb") as fh:

@@ -110,6 +110,54 @@ def _checksums_async(raw):
     return result
 
 
+def _read_and_hash(filepath, chunk=32 << 20):
+    """The raw bytes of the file, and a callable giving (md5, sha256) of them (kmerdb/util.py:35-50).  The file is read in
+    pieces straight into one buffer; two host threads hash the pieces as they arrive (hashlib releases the GIL) and go on
+    hashing while the caller feeds the GPU."""
+    import queue
+    import threading
+    size = os.path.getsize(filepath)
+    buf = bytearray(size)
+    mv = memoryview(buf)
+    hashes = (hashlib.md5(), hashlib.sha256())
+    queues = (queue.Queue(), queue.Queue())
+
+    def work(h, q):
+        while True:
+            piece = q.get()
+            if piece is None:
+                return
+            h.update(piece)
+
+    threads = [threading.Thread(target=work, args=hq, daemon=True) for hq in zip(hashes, queues)]
+    for t in threads:
+        t.start()
+    off = 0
+    tail = b""
+    with open(filepath, "rb", buffering=0) as fh:
+        while off < size:
+            n = fh.readinto(mv[off:min(size, off + chunk)])
+            if not n:
+                break
+            for q in queues:
+                q.put(mv[off:off + n])
+            off += n
+        if off == size:
+            tail = fh.read()                                     # the file grew while it was read
+            if tail:
+                for q in queues:
+                    q.put(tail)
+    for q in queues:
+        q.put(None)
+    raw = mv[:off] if not tail else bytes(mv[:off]) + tail
+
+    def result():
+        for t in threads:
+            t.join()
+        return hashes[0].hexdigest(), hashes[1].hexdigest()
+    return raw, result
+
+
 def _file_format(filepath):
     if is_fasta(filepath):
         return "fasta"
@@ -327,9 +375,7 @@ def parsefile(filepath, k, replace_with_none=True, canonicalize=True, device=0, 
         raise TypeError("kmerdb.parse.parsefile expects an int as its second positional argument")
     elif type(replace_with_none) is not bool:
         raise TypeError("kmerdb.parse.parsefile expects the keyword argument 'replace_with_none' to be a bool")
-    with open(filepath, "rb") as fh:
-        raw = fh.read()
-    sums = _checksums_async(raw)                               # hashes of the raw bytes, computed beside the GPU work
+    raw, sums = _read_and_hash(filepath)                       # hashes of the raw bytes, computed beside the read and the GPU work
     try:
         data = _read_text_bytes(filepath, raw)
         fmt = _file_format(filepath)

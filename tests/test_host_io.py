@@ -28,3 +28,19 @@ def test_async_checksums_match_util_checksum(tmp_path):
     p = str(tmp_path / "x.bin")
     open(p, "wb").write(raw)
     assert parse._checksums_async(raw)() == parse.checksum(p) == (hashlib.md5(raw).hexdigest(), hashlib.sha256(raw).hexdigest())
+
+
+def test_read_and_hash_streams_the_file(tmp_path):
+    """parse._read_and_hash: the bytes and the two digests of kmerdb/util.py:35-50, hashed while the file is read."""
+    import hashlib
+    import numpy as np
+    from kmerdb_b200 import parse
+    rng = np.random.default_rng(0)
+    for size, chunk in ((0, 1 << 20), (1, 1 << 20), (1000003, 4096), (3 << 20, 1 << 20)):
+        p = tmp_path / ("f%d.bin" % size)
+        data = rng.integers(0, 256, size=size, dtype=np.uint8).tobytes()
+        p.write_bytes(data)
+        raw, sums = parse._read_and_hash(str(p), chunk=chunk)
+        assert bytes(raw) == data
+        assert sums() == (hashlib.md5(data).hexdigest(), hashlib.sha256(data).hexdigest())
+        assert sums() == parse.checksum(str(p))
