@@ -42,19 +42,24 @@ def _profile(args, k, files, precomputed=None):
         if precomputed is not None:
             c, meta = precomputed[i]
         else:
-            c, meta, _nullomers = parse.parsefile(f, k, replace_with_none=args.no_ambiguous, canonicalize=not args.do_not_canonicalize,
-                                                  device=args.device)
+            # the per-file metadata arrives as a callable: md5 / sha256 of a large file finish seconds after its counts
+            c, meta, _nullomers = parse.parsefile_deferred(f, k, replace_with_none=args.no_ambiguous, canonicalize=not args.do_not_canonicalize,
+                                                           device=args.device)
         counts = counts + c                                        # __init__.py:1890
         file_metadata.append(meta)
     total = int(np.sum(counts))
     unique = int(np.count_nonzero(counts))
     unique_nullomers = N - unique if args.do_not_canonicalize else int((N / 2) - unique)      # __init__.py:1903
-    metadata = OrderedDict({"version": REFERENCE_VERSION, "metadata_blocks": 1, "k": k, "total_kmers": total, "unique_kmers": unique,
-                            "unique_nullomers": unique_nullomers, "sorted": args.sorted, "tags": [], "files": file_metadata})
+
+    def metadata():
+        return OrderedDict({"version": REFERENCE_VERSION, "metadata_blocks": 1, "k": k, "total_kmers": total, "unique_kmers": unique,
+                            "unique_nullomers": unique_nullomers, "sorted": args.sorted, "tags": [],
+                            "files": [m() if callable(m) else m for m in file_metadata]})
     if args.sorted:
         sys.stderr.write("--sorted is broken in kmerdb v0.9.6 (undefined names at kmerdb/__init__.py:1974-1975); rows are written in id order\n")
     out = "{0}.{1}.kdb".format(args.output_name, k)                 # __init__.py:1954
-    kdbfile.write_kdb_gpu(out, metadata, counts, device=args.device, quiet=args.quiet)
+    # up to k = 12 the compressed body (about 100 MB) waits in memory for the header; larger tables take the header first
+    kdbfile.write_kdb_gpu(out, metadata if k <= 12 else metadata(), counts, device=args.device, quiet=args.quiet, total_kmers=total)
     sys.stderr.write("\n\n\nFinal stats:\n\n\n")
     sys.stderr.write("Total k-mers processed: {0}\n".format(total))
     sys.stderr.write("Unique nullomer count:   {0}\n".format(unique_nullomers))

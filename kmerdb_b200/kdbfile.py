@@ -71,29 +71,44 @@ def count_strings(counts, total_kmers):
     return uniq, off, b"".join(strs)
 
 
-def write_kdb_gpu(path, metadata, counts, device=0, threads=None, quiet=True, rows_per_call=1 << 22):
-    """write_kdb with the rows assembled on the GPU (kdb_format_rows); BGZF deflate on host threads."""
+def write_kdb_gpu(path, metadata, counts, device=0, threads=None, quiet=True, rows_per_call=1 << 22, total_kmers=None):
+    """write_kdb with the rows assembled on the GPU (kdb_format_rows); BGZF deflate on host threads.
+    `metadata` may be a callable (with `total_kmers` given): the body is then formatted and compressed first and the
+    callable is asked when the header is written (the file checksums of a large input finish later than its counts)."""
     from . import _native
-    head, md = header_bytes(metadata)
-    uniq, off, blob = count_strings(counts, md["total_kmers"])
+    deferred = callable(metadata)
+    if deferred and total_kmers is None:
+        raise ValueError("write_kdb_gpu: a deferred header needs total_kmers for the frequency column")
+    if not deferred:
+        head, md = header_bytes(metadata)
+        total_kmers = md["total_kmers"]
+    uniq, off, blob = count_strings(counts, total_kmers)
     threads = threads or _host_threads()
 
     def deflate(buf):
         return b"".join(bgzf_block(bytes(buf[o:o + _BLOCK])) for o in range(0, len(buf), _BLOCK))
 
-    with open(path, "wb") as fh:
-        for o in range(0, len(head), 65536):
-            fh.write(bgzf_block(head[o:o + 65536]))
-        with ThreadPoolExecutor(max_workers=threads) as ex:
-            for lo in range(0, len(counts), rows_per_call):
-                text = _native.format_rows(counts[lo:lo + rows_per_call], lo, uniq, off, blob, device=device)
-                if not quiet:
-                    sys.stdout.write(text.tobytes().decode("ascii"))
-                step = _BLOCK * 32
-                mv = memoryview(text)
-                for blobz in ex.map(deflate, [mv[o:o + step] for o in range(0, len(text), step)]):
-                    fh.write(blobz)
-        fh.write(_BGZF_EOF)
+    def body(ex):
+        for lo in range(0, len(counts), rows_per_call):
+            text = _native.format_rows(counts[lo:lo + rows_per_call], lo, uniq, off, blob, device=device)
+            if not quiet:
+                sys.stdout.write(text.tobytes().decode("ascii"))
+            step = _BLOCK * 32
+            mv = memoryview(text)
+            yield from ex.map(deflate, [mv[o:o + step] for o in range(0, len(text), step)])
+
+    with ThreadPoolExecutor(max_workers=threads) as ex:
+        held = list(body(ex)) if deferred else None            # compressed body in memory while the header is still unknown
+        if deferred:
+            head, md = header_bytes(metadata())
+            if md["total_kmers"] != total_kmers:
+                raise ValueError("write_kdb_gpu: the deferred header disagrees with total_kmers")
+        with open(path, "wb") as fh:
+            for o in range(0, len(head), 65536):
+                fh.write(bgzf_block(head[o:o + 65536]))
+            for blobz in (held if deferred else body(ex)):
+                fh.write(blobz)
+            fh.write(_BGZF_EOF)
     return md
 
 

@@ -367,6 +367,14 @@ def parsefile(filepath, k, replace_with_none=True, canonicalize=True, device=0, 
     """Drop-in for kmerdb.parse.parsefile (kmerdb/parse.py:90-163).
 
     :returns: (counts uint64[4**k], file_metadata dict, nullomer_array uint64)"""
+    counts, meta_fn, nullomer_array = parsefile_deferred(filepath, k, replace_with_none, canonicalize, device, with_mononucleotides)
+    return counts, meta_fn(), nullomer_array
+
+
+def parsefile_deferred(filepath, k, replace_with_none=True, canonicalize=True, device=0, with_mononucleotides=False):
+    """parsefile whose file_metadata comes as a callable: the count vector is ready after the device job (tens of
+    milliseconds), md5 / sha256 of a large file take the host seconds longer — the CLI formats and compresses the rows in
+    the meantime and asks for the metadata when it writes the header."""
     if filepath is None or type(filepath) is not str:
         raise TypeError("kmerdb.parse.parsefile expects a str as its first positional argument")
     elif not os.path.exists(filepath):
@@ -380,10 +388,15 @@ def parsefile(filepath, k, replace_with_none=True, canonicalize=True, device=0, 
         data = _read_text_bytes(filepath, raw)
         fmt = _file_format(filepath)
         prof = profile_bytes(data, k, fmt, replace_with_none, bool(canonicalize), device)
-    finally:
-        md5, sha256 = sums()
+    except BaseException:
+        sums()                                                 # (join the hashing threads before the raise leaves)
+        raise
     assert prof.nullomers == len(prof.nullomer_array), "Internal Error: kmerdb.parse.parsefile() found inconsistencies between two ways of counting nullomers. Internal error."
-    meta = prof.file_metadata(filepath, md5, sha256)
-    if with_mononucleotides:
-        meta["mononucleotides"] = prof.mononucleotides        # legacy header field (README.md:31)
-    return prof.counts, meta, prof.nullomer_array
+
+    def file_metadata():
+        md5, sha256 = sums()
+        meta = prof.file_metadata(filepath, md5, sha256)
+        if with_mononucleotides:
+            meta["mononucleotides"] = prof.mononucleotides    # legacy header field (README.md:31)
+        return meta
+    return prof.counts, file_metadata, prof.nullomer_array
