@@ -221,15 +221,15 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
     if (ctx->partitioned) {
         ctx->part_kernel = k3p_kernel(k, ctx->canonical);
         ctx->n_buckets = 1 << (2 * k - payload_bits(k));
-        ctx->subs = 1 << (payload_bits(k) - kTableBits);
+        ctx->subs = payload_bits(k) >= 16 ? 0 : 1;                                          // 0: packed 16-bit counters (k3p_count16 / k3p_count16w)
         ctx->wide = payload_bits(k) > 16;                                                   // 32-bit stream entries (k = 14)
-        ctx->parts = std::max(1, (1776 + ctx->n_buckets - 1) / ctx->n_buckets);
+        ctx->parts = std::max(1, ((payload_bits(k) == 15 ? 888 : 1776) + ctx->n_buckets - 1) / ctx->n_buckets);
         const size_t dyn = k3p_smem_bytes(k);
         if ((e = cudaFuncSetAttribute((const void*)ctx->part_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)) != cudaSuccess) return fail("smem attr", e);
-        if ((e = cudaFuncSetAttribute((const void*)k3p_count, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << kTableBits)) != cudaSuccess) return fail("smem attr", e);
+        if ((e = cudaFuncSetAttribute((const void*)k3p_count<14>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << 14)) != cudaSuccess) return fail("smem attr", e);
+        if ((e = cudaFuncSetAttribute((const void*)k3p_count<15>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << 15)) != cudaSuccess) return fail("smem attr", e);
         if ((e = cudaFuncSetAttribute((const void*)k3p_count16, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024)) != cudaSuccess) return fail("smem attr", e);
         if ((e = cudaFuncSetAttribute((const void*)k3p_count16w, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024)) != cudaSuccess) return fail("smem attr", e);
-        if (payload_bits(k) >= 16) ctx->subs = 0;                                           // 0: packed 16-bit counters (k3p_count16 / k3p_count16w)
         if (!rc) rc = occupancy_grid(ctx->part_kernel, kPartThreads, dyn, &ctx->part_grid);
         if ((e = cudaMalloc(&ctx->cursor, 2 * ctx->n_buckets * sizeof(unsigned int))) != cudaSuccess) return fail("cudaMalloc cursor", e);
     }
@@ -320,8 +320,8 @@ static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigne
         CK(cudaEventRecord(ctx->ev[7], st));
         if (ctx->wide) k3p_count16w<<<ctx->n_buckets * 4, kCount16Threads, 128 * 1024, st>>>(reinterpret_cast<const uint32_t*>(src->stream), Q.cursor, Q.fail_base, cap, ctx->tab32);
         else if (ctx->subs == 0) k3p_count16<<<ctx->n_buckets, kCount16Threads, 128 * 1024, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->tab32);
-        else k3p_count<<<ctx->n_buckets * ctx->parts * ctx->subs, kBucketThreads, 4 << kTableBits, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->subs,
-                                                                                                       payload_bits(ctx->k), ctx->tab32);
+        else if (payload_bits(ctx->k) == 15) k3p_count<15><<<ctx->n_buckets * ctx->parts, 1024, 4 << 15, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->tab32);
+        else k3p_count<14><<<ctx->n_buckets * ctx->parts, kBucketThreads, 4 << 14, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->tab32);
         CK(cudaGetLastError());
         ctx->timing.total_launches++;
     } else {

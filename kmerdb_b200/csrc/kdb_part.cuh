@@ -19,11 +19,12 @@
 
 namespace kdb {
 
-constexpr int kTableBits = 14;                         // 16384 bins x 4 B = 64 KiB shared count table
-// payload bits of a stream entry: 14 for k <= 12 (one 16384-bin table per bucket, 16-bit entries); 16 for k = 13 (65536 packed
+
+// payload bits of a stream entry: 14 for k <= 11 and 15 for k = 12 (one 16384- / 32768-bin table per bucket, 16-bit entries: 512
+// buckets at k = 12 sort faster than 1024 — fewer cursors to scan and bump per tile, longer runs); 16 for k = 13 (65536 packed
 // 16-bit counters per bucket, k3p_count16); 18 for k = 14 (32-bit entries, 1024 buckets, four sub-passes of 16 bits: with 16-bit
 // payloads k = 14 needs 4096 buckets, which leaves 4 entries per bucket per tile — 8-byte runs and one cursor bump per 4 keys)
-__host__ __device__ constexpr int payload_bits(int k) { return k <= 12 ? 14 : (k == 13 ? 16 : 18); }
+__host__ __device__ constexpr int payload_bits(int k) { return k <= 11 ? 14 : (k == 12 ? 15 : (k == 13 ? 16 : 18)); }
 constexpr int kPartThreads = 512;                      // 512 threads x 32 letters = one full tile
 constexpr int kBucketThreads = 256;
 
@@ -215,16 +216,16 @@ __global__ void __launch_bounds__(kPartThreads, 3) k3p_partition(const PartParam
     }
 }
 
-// One work item = (bucket, part, sub).  grid = n_buckets * parts * subs; sub selects the payloads whose bits
-// above kTableBits equal it (subs = 1 for k <= 12; 4 for k = 13, 14: the four CTAs of a bucket part run next to
-// each other, so the re-reads of the stream hit L2).
-__global__ void __launch_bounds__(kBucketThreads) k3p_count(const uint16_t* __restrict__ stream, const unsigned int* __restrict__ cursor,
-                                                            const unsigned int* __restrict__ fail_base, unsigned int cap, int parts, int subs,
-                                                            int pb, unsigned int* __restrict__ tab32) {
+// One work item = (bucket, part): grid = n_buckets * parts.  The payloads of one bucket are counted into a shared table of
+// 2^TB bins (TB = payload bits: 14 -> 64 KiB, three CTAs of 256 threads per SM; 15 -> 128 KiB, one CTA of 1024 threads) and the
+// table is flushed with coalesced REDs.
+template <int TB>
+__global__ void __launch_bounds__(TB == 14 ? kBucketThreads : 1024) k3p_count(const uint16_t* __restrict__ stream, const unsigned int* __restrict__ cursor,
+                                                                              const unsigned int* __restrict__ fail_base, unsigned int cap, int parts,
+                                                                              unsigned int* __restrict__ tab32) {
     extern __shared__ unsigned int s_tab[];
-    const int tid = threadIdx.x;
-    const uint32_t sub = blockIdx.x % subs, bp = blockIdx.x / subs;
-    const uint32_t b = bp / parts, part = bp % parts;
+    const uint32_t tid = threadIdx.x, nthr = blockDim.x;
+    const uint32_t b = blockIdx.x / parts, part = blockIdx.x % parts;
     uint32_t end = cursor[b];
     { const uint32_t fb = fail_base[b]; end = end < fb ? end : fb; end = end < cap ? end : cap; }
     if (end == 0) return;
@@ -232,33 +233,20 @@ __global__ void __launch_bounds__(kBucketThreads) k3p_count(const uint16_t* __re
     const uint32_t units = (end + 7) >> 3, per = (units + parts - 1) / parts;
     const uint32_t u0 = part * per, u1 = min(units, u0 + per);
     if (u0 >= u1) return;
-    for (int i = tid; i < (1 << kTableBits); i += kBucketThreads) s_tab[i] = 0;
+    for (uint32_t i = tid; i < (1u << TB); i += nthr) s_tab[i] = 0;
     __syncthreads();
     const uint4* src = reinterpret_cast<const uint4*>(stream + (size_t)b * cap);
-    if (subs == 1) {
-        for (uint32_t u = u0 + tid; u < u1; u += kBucketThreads) {
-            const uint4 v = __ldcs(src + u);
-            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-            const uint32_t valid = min(8u, end - 8 * u);
+    for (uint32_t u = u0 + tid; u < u1; u += nthr) {
+        const uint4 v = __ldcs(src + u);
+        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+        const uint32_t valid = min(8u, end - 8 * u);
 #pragma unroll
-            for (int q = 0; q < 8; q++)
-                if ((uint32_t)q < valid) atomicAdd(&s_tab[(w[q >> 1] >> (16 * (q & 1))) & 0x3FFFu], 1u);
-        }
-    } else {
-        for (uint32_t u = u0 + tid; u < u1; u += kBucketThreads) {
-            const uint4 v = __ldg(src + u);
-            const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-            const uint32_t valid = min(8u, end - 8 * u);
-#pragma unroll
-            for (int q = 0; q < 8; q++) {
-                const uint32_t pl = (w[q >> 1] >> (16 * (q & 1))) & 0xFFFFu;
-                if ((uint32_t)q < valid && (pl >> kTableBits) == sub) atomicAdd(&s_tab[pl & 0x3FFFu], 1u);
-            }
-        }
+        for (int q = 0; q < 8; q++)
+            if ((uint32_t)q < valid) atomicAdd(&s_tab[(w[q >> 1] >> (16 * (q & 1))) & ((1u << TB) - 1u)], 1u);
     }
     __syncthreads();
-    unsigned int* dst = tab32 + ((size_t)b << pb) + ((size_t)sub << kTableBits);
-    for (int i = tid; i < (1 << kTableBits); i += kBucketThreads) { const unsigned int x = s_tab[i]; if (x) atomicAdd(dst + i, x); }
+    unsigned int* dst = tab32 + ((size_t)b << TB);
+    for (uint32_t i = tid; i < (1u << TB); i += nthr) { const unsigned int x = s_tab[i]; if (x) atomicAdd(dst + i, x); }
 }
 
 // 16-bit payloads (k = 13, 14): the 65536 bins of a bucket as packed 16-bit counters (add16, kdb_hist.cuh), counted in ONE pass.
