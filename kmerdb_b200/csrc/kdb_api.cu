@@ -318,7 +318,7 @@ static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigne
         ctx->part_kernel<<<grid, kPartThreads, k3p_smem_bytes(ctx->k), st>>>(Q);
         CK(cudaGetLastError());
         CK(cudaEventRecord(ctx->ev[7], st));
-        if (ctx->wide) k3p_count16w<<<ctx->n_buckets * 4, kCount16Threads, 128 * 1024, st>>>(reinterpret_cast<const uint32_t*>(src->stream), Q.cursor, Q.fail_base, cap, ctx->tab32);
+        if (ctx->wide) k3p_count16w<<<ctx->n_buckets << (payload_bits(ctx->k) - 16), kCount16Threads, 128 * 1024, st>>>(reinterpret_cast<const uint32_t*>(src->stream), Q.cursor, Q.fail_base, cap, payload_bits(ctx->k), ctx->tab32);
         else if (ctx->subs == 0) k3p_count16<<<ctx->n_buckets, kCount16Threads, 128 * 1024, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->tab32);
         else if (payload_bits(ctx->k) == 15) k3p_count<15><<<ctx->n_buckets * ctx->parts, 1024, 4 << 15, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->tab32);
         else k3p_count<14><<<ctx->n_buckets * ctx->parts, kBucketThreads, 4 << 14, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->tab32);

@@ -17,14 +17,18 @@
 #include "kdb_encode.cuh"
 #include "kdb_hist.cuh"
 
+#ifndef KDB_PB14
+#define KDB_PB14 17      // payload bits at k = 14 (measured, 10 M reads: 17 -> partition 5.93 + count 3.24 ms; 18 -> 3.93 + 5.71 ms)
+#endif
+
 namespace kdb {
 
 
 // payload bits of a stream entry: 14 for k <= 11 and 15 for k = 12 (one 16384- / 32768-bin table per bucket, 16-bit entries: 512
 // buckets at k = 12 sort faster than 1024 — fewer cursors to scan and bump per tile, longer runs); 16 for k = 13 (65536 packed
-// 16-bit counters per bucket, k3p_count16); 18 for k = 14 (32-bit entries, 1024 buckets, four sub-passes of 16 bits: with 16-bit
+// 16-bit counters per bucket, k3p_count16); 17 for k = 14 (32-bit entries, 2048 buckets, two sub-passes of 16 bits: with 16-bit
 // payloads k = 14 needs 4096 buckets, which leaves 4 entries per bucket per tile — 8-byte runs and one cursor bump per 4 keys)
-__host__ __device__ constexpr int payload_bits(int k) { return k <= 11 ? 14 : (k == 12 ? 15 : (k == 13 ? 16 : 18)); }
+__host__ __device__ constexpr int payload_bits(int k) { return k <= 11 ? 14 : (k == 12 ? 15 : (k == 13 ? 16 : KDB_PB14)); }
 constexpr int kPartThreads = 512;                      // 512 threads x 32 letters = one full tile
 constexpr int kBucketThreads = 256;
 
@@ -285,17 +289,18 @@ __global__ void __launch_bounds__(kCount16Threads) k3p_count16(const uint16_t* _
 // 18-bit payloads in 32-bit entries (k = 14): grid = n_buckets * 4; CTA (b, sub) counts the entries of bucket b whose payload
 // bits above 16 equal sub (the four CTAs of a bucket run next to each other: the re-reads hit L2)
 __global__ void __launch_bounds__(kCount16Threads) k3p_count16w(const uint32_t* __restrict__ stream, const unsigned int* __restrict__ cursor,
-                                                                const unsigned int* __restrict__ fail_base, unsigned int cap,
+                                                                const unsigned int* __restrict__ fail_base, unsigned int cap, int pb,
                                                                 unsigned int* __restrict__ tab32) {
     extern __shared__ unsigned int s_tab[];                           // 32768 words
     const int tid = threadIdx.x;
-    const uint32_t b = blockIdx.x >> 2, sub = blockIdx.x & 3u;
+    const uint32_t subs = 1u << (pb - 16);
+    const uint32_t b = blockIdx.x / subs, sub = blockIdx.x % subs;
     uint32_t end = cursor[b];
     { const uint32_t fb = fail_base[b]; end = end < fb ? end : fb; end = end < cap ? end : cap; }
     if (end == 0) return;
     for (int i = tid; i < 32768; i += kCount16Threads) s_tab[i] = 0;
     __syncthreads();
-    unsigned int* dst = tab32 + ((size_t)b << 18) + ((size_t)sub << 16);
+    unsigned int* dst = tab32 + ((size_t)b << pb) + ((size_t)sub << 16);
     const uint4* src = reinterpret_cast<const uint4*>(stream + (size_t)b * cap);
     const uint32_t units = (end + 3) >> 2;
     // four 16-byte loads in flight per thread: one CTA per SM has to cover the L2 latency on its own
