@@ -58,6 +58,7 @@ struct kdb_ctx {
     int part_grid = 0, n_buckets = 0, parts = 1, hist_threads = 0;
     int subs = 1;
     bool wide = false;
+    bool slotted = false;                       // k3s_partition (buckets = low id bits) instead of the two-sweep k3p_partition
     uint16_t* stream = nullptr;
     size_t stream_cap = 0;
     unsigned int* cursor = nullptr;             // n_buckets cursors + n_buckets fail bases
@@ -219,12 +220,13 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
     rc = occupancy_grid(ctx->hist_kernel, ctx->hist_threads, ctx->hist_dyn, &ctx->hist_grid);
     ctx->partitioned = k >= 9 && k <= 14 && !getenv("KDB_NO_PARTITION");
     if (ctx->partitioned) {
-        ctx->part_kernel = k3p_kernel(k, ctx->canonical);
+        ctx->slotted = k <= 12 && !getenv("KDB_TWO_SWEEP");
+        ctx->part_kernel = ctx->slotted ? k3s_kernel(k, ctx->canonical) : k3p_kernel(k, ctx->canonical);
         ctx->n_buckets = 1 << (2 * k - payload_bits(k));
         ctx->subs = payload_bits(k) >= 16 ? 0 : 1;                                          // 0: packed 16-bit counters (k3p_count16 / k3p_count16w)
         ctx->wide = payload_bits(k) > 16;                                                   // 32-bit stream entries (k = 14)
         ctx->parts = std::max(1, ((payload_bits(k) == 15 ? 888 : 1776) + ctx->n_buckets - 1) / ctx->n_buckets);
-        const size_t dyn = k3p_smem_bytes(k);
+        const size_t dyn = ctx->slotted ? k3s_smem_bytes(k) : k3p_smem_bytes(k);
         if ((e = cudaFuncSetAttribute((const void*)ctx->part_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)) != cudaSuccess) return fail("smem attr", e);
         if ((e = cudaFuncSetAttribute((const void*)k3p_count<14>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << 14)) != cudaSuccess) return fail("smem attr", e);
         if ((e = cudaFuncSetAttribute((const void*)k3p_count<15>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << 15)) != cudaSuccess) return fail("smem attr", e);
@@ -305,7 +307,8 @@ static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigne
         // every window ends on a text byte, so (hi - lo) bounds the entries of the pass; canonical ids of
         // uniform sequence load the lowest bucket with 2x the average, hence the 3x head room
         const unsigned long long avg = (hi - lo) / ctx->n_buckets + 1;
-        const unsigned int cap = (unsigned int)((3 * avg + kTile + 7) & ~7ull);   // >= kTile: keeps s_delta (kdb_part.cuh) from wrapping
+        // (low-bit buckets of the slotted partition are uniform on uniform sequence: 2x head room)
+        const unsigned int cap = (unsigned int)(((ctx->slotted ? 2 : 3) * avg + kTile + 7) & ~7ull);   // >= kTile: keeps s_delta (kdb_part.cuh) from wrapping
         if ((unsigned long long)cap * ctx->n_buckets >= 0xFFFFFFFFull) { ctx->err = "bucket stream index exceeds 32 bits"; return KDB_E_ARG; }
         // the bucket streams live in the leader: the k of a sweep are counted one after the other on one stream
         if (int rc = ensure(src, (void**)&src->stream, &src->stream_cap, (size_t)cap * ctx->n_buckets * (ctx->wide ? 2 : 1), sizeof(uint16_t))) { ctx->err = src->err; return rc; }
@@ -315,13 +318,13 @@ static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigne
         Q.packed = src->packed; Q.n_tiles = n_tiles; Q.skip_n = ctx->skip_n; Q.smear = smear; Q.tab32 = ctx->tab32; Q.stream = src->stream;
         Q.cursor = ctx->cursor; Q.fail_base = ctx->cursor + ctx->n_buckets; Q.cap = cap; Q.acc = ctx->acc;
         const int grid = (int)std::min<unsigned int>((n_tiles + 1) / 2, (unsigned int)ctx->part_grid);   // work unit = two tiles
-        ctx->part_kernel<<<grid, kPartThreads, k3p_smem_bytes(ctx->k), st>>>(Q);
+        ctx->part_kernel<<<grid, kPartThreads, ctx->slotted ? k3s_smem_bytes(ctx->k) : k3p_smem_bytes(ctx->k), st>>>(Q);
         CK(cudaGetLastError());
         CK(cudaEventRecord(ctx->ev[7], st));
         if (ctx->wide) k3p_count16w<<<ctx->n_buckets << (payload_bits(ctx->k) - 16), kCount16Threads, 128 * 1024, st>>>(reinterpret_cast<const uint32_t*>(src->stream), Q.cursor, Q.fail_base, cap, payload_bits(ctx->k), ctx->tab32);
         else if (ctx->subs == 0) k3p_count16<<<ctx->n_buckets, kCount16Threads, 128 * 1024, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->tab32);
-        else if (payload_bits(ctx->k) == 15) k3p_count<15><<<ctx->n_buckets * ctx->parts, 1024, 4 << 15, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->tab32);
-        else k3p_count<14><<<ctx->n_buckets * ctx->parts, kBucketThreads, 4 << 14, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->tab32);
+        else if (payload_bits(ctx->k) == 15) k3p_count<15><<<ctx->n_buckets * ctx->parts, 1024, 4 << 15, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->tab32, ctx->slotted ? 2 * ctx->k - 15 : 0);
+        else k3p_count<14><<<ctx->n_buckets * ctx->parts, kBucketThreads, 4 << 14, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->tab32, ctx->slotted ? 2 * ctx->k - 14 : 0);
         CK(cudaGetLastError());
         ctx->timing.total_launches++;
     } else {

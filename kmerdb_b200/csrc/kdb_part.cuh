@@ -226,7 +226,7 @@ __global__ void __launch_bounds__(kPartThreads, 3) k3p_partition(const PartParam
 template <int TB>
 __global__ void __launch_bounds__(TB == 14 ? kBucketThreads : 1024) k3p_count(const uint16_t* __restrict__ stream, const unsigned int* __restrict__ cursor,
                                                                               const unsigned int* __restrict__ fail_base, unsigned int cap, int parts,
-                                                                              unsigned int* __restrict__ tab32) {
+                                                                              unsigned int* __restrict__ tab32, int low_bits) {   // low_bits != 0: buckets are the id's low bits (k3s_partition)
     extern __shared__ unsigned int s_tab[];
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
     const uint32_t b = blockIdx.x / parts, part = blockIdx.x % parts;
@@ -249,6 +249,10 @@ __global__ void __launch_bounds__(TB == 14 ? kBucketThreads : 1024) k3p_count(co
             if ((uint32_t)q < valid) atomicAdd(&s_tab[(w[q >> 1] >> (16 * (q & 1))) & ((1u << TB) - 1u)], 1u);
     }
     __syncthreads();
+    if (low_bits) {                                                   // bin p of bucket b is id (p << low_bits) | b: one RED per sector, L2-resident table
+        for (uint32_t i = tid; i < (1u << TB); i += nthr) { const unsigned int x = s_tab[i]; if (x) atomicAdd(tab32 + (((size_t)i << low_bits) | b), x); }
+        return;
+    }
     unsigned int* dst = tab32 + ((size_t)b << TB);
     for (uint32_t i = tid; i < (1u << TB); i += nthr) { const unsigned int x = s_tab[i]; if (x) atomicAdd(dst + i, x); }
 }
@@ -329,11 +333,176 @@ __global__ void __launch_bounds__(kCount16Threads) k3p_count16w(const uint32_t* 
     }
 }
 
+// ---- single-sweep slotted partition (r02) ----------------------------------------------------------------------
+// One returning shared atomic + one predicated 2-byte store per key (the two-sweep sort above pays a histogram atomic, a cursor
+// atomic and a scatter store, and builds every id twice).  Every bucket owns a fixed range of C slots in shared memory;
+// pos = atomicAdd(&cnt[b], 1) is the slot, so there is no scan and no second pass over the letters.  Buckets are the LOW bits of
+// the id: for canonical ids (min of the two strands) the high bits are skewed 2:0 over the id range, the low bits are uniform, so
+// one slot count fits every bucket and the slot address is b * C + pos with C an immediate.  The payload is the id's high bits;
+// k3p_count<TB, true> puts bin p of bucket b back at tab32[p << NBITS | b].  A key that finds its bucket full (pos >= C: about
+// +4 sigma of a dense tile on uniform sequence; low-complexity sequence does it all the time) is remembered in a per-thread bit
+// mask and goes to the global table directly after the loop (warp-aggregated REDs), so the result is exact for any input.
+#ifndef KDB_SLOT_SIGMAS
+#define KDB_SLOT_SIGMAS 4
+#endif
+__host__ __device__ constexpr int slot_count(int nb) {
+    // dense text: kTile letters per unit; mean + KDB_SLOT_SIGMAS sigma, rounded up to a multiple of 8
+    int mean = kTile / nb, s = 1;
+    while (s * s < mean) s++;
+    return (mean + KDB_SLOT_SIGMAS * s + 7) & ~7;
+}
+__host__ inline size_t k3s_smem_bytes(int k) {
+    const int nb = 1 << (2 * k - payload_bits(k));
+    return (size_t)(2 * nb + 32) * sizeof(uint32_t) + (size_t)nb * slot_count(nb) * sizeof(uint16_t);
+}
+
+template <int K, bool CANON>
+__global__ void __launch_bounds__(kPartThreads, 3) k3s_partition(const PartParams P) {
+    constexpr int PB = payload_bits(K) <= 16 ? payload_bits(K) : 16;   // (instantiated, never launched, for k = 14)
+    constexpr int NBITS = 2 * K - PB, NB = 1 << NBITS;
+    constexpr int C = slot_count(NB);
+    constexpr uint32_t mask = (1u << (2 * K)) - 1u;
+    extern __shared__ uint32_t s_dyn_part[];                        // NB counters, 32 dummies, NB global bases, NB * C 16-bit slots
+    uint32_t* const s_cnt = s_dyn_part;
+    uint32_t* const s_gb = s_dyn_part + NB + 32;
+    uint16_t* const s_slot = reinterpret_cast<uint16_t*>(s_gb + NB);
+    __shared__ unsigned long long s_red[kPartThreads / 32];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    unsigned long long kmers = 0;
+
+    const unsigned int n_units = (P.n_tiles + 1) / 2;               // work unit = two packed tiles (see k3p_partition)
+    for (unsigned int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
+      const unsigned int tA = 2 * unit, tB = tA + 1;
+      const uint32_t nA = P.packed[(size_t)tA * kPackStride], nB = tB < P.n_tiles ? P.packed[(size_t)tB * kPackStride] : 0u;
+      const bool both = nA <= kTile / 2 && nB <= kTile / 2;
+      const int n_half = (both || tB >= P.n_tiles) ? 1 : 2;
+      for (int half = 0; half < n_half; half++) {
+        const bool onB = both ? tid >= kPartThreads / 2 : half == 1;
+        const int ltid = both ? (tid & (kPartThreads / 2 - 1)) : tid;
+        const uint32_t* reg = P.packed + (size_t)(onB ? tB : tA) * kPackStride;
+        const uint32_t n = onB ? nB : nA;
+        __syncthreads();                                            // the copy-out of the unit before is done with s_cnt / s_slot
+        for (int i = tid; i < NB; i += kPartThreads) s_cnt[i] = 0;
+        __syncthreads();
+
+        const bool active = (uint32_t)ltid * 32 < n;
+        uint32_t cur0 = 0, cur1 = 0, prev = 0, wb = 0;
+        if (active) {
+            const uint32_t* codes = reg + kPackHdr;
+            cur0 = codes[2 * ltid];
+            cur1 = (uint32_t)ltid * 32 + 16 < n ? codes[2 * ltid + 1] : 0u;
+            prev = ltid ? codes[2 * ltid - 1] : reg[1];
+            wb = reg[kPackHdr + kPackCodes + ltid];
+            if (P.smear) wb = smear_w(ltid ? reg[kPackHdr + kPackCodes + ltid - 1] : reg[3], wb, P.smear);
+            if (!P.skip_n) {
+                const uint32_t* nnw = reg + kPackHdr + kPackCodes + kPackBits;
+                const uint32_t nn_cur = nnw[ltid], nn_prev = ltid ? nnw[ltid - 1] : reg[2];
+                if ((nn_cur | (nn_prev & ((1u << (K - 1)) - 1u))) != 0) {
+                    // expansion mode with N near by: generic path, direct REDs; nothing of this thread enters the slots
+                    const unsigned long long S0 = ((unsigned long long)prev << 32) | cur0, S1 = ((unsigned long long)cur0 << 32) | cur1;
+                    const unsigned long long NS = ((unsigned long long)nn_prev << 32) | nn_cur;
+                    for (int e = 0; e < 32; e++) {
+                        if (!(wb & (0x80000000u >> e))) continue;
+                        const uint32_t f = (uint32_t)((e < 16 ? S0 : S1) >> (30 - 2 * (e & 15))) & mask;
+                        const uint32_t nm = (uint32_t)(NS >> (31 - e)) & ((1u << K) - 1u);
+                        if (nm) kmers += expand_window(P.tab32, K, CANON, f, nm);
+                        else {
+                            uint32_t id = f;
+                            if (CANON) { const uint32_t r = revcomp32(f, K); id = r < f ? r : f; }
+                            atomicAdd(P.tab32 + id, 1u);
+                            kmers++;
+                        }
+                    }
+                    wb = 0;
+                }
+            }
+        }
+        const uint32_t r2 = CANON ? rc_word(cur1) : 0u, r1 = CANON ? rc_word(cur0) : 0u, r0 = CANON ? rc_word(prev) : 0u;
+        auto window_top = [&](int e) -> uint32_t {                     // window ending at my letter e, id bits on top
+            uint32_t m = ext96(prev, cur0, cur1, 2 * (17 + e - K));
+            if (CANON) { const uint32_t rc = ext96(r2, r1, r0, 62 - 2 * e); m = rc < m ? rc : m; }
+            return m;
+        };
+        uint32_t* const dummy = s_cnt + NB + lane;                     // a letter without a window bumps a per-lane dummy (no branch)
+        uint32_t ovf = 0;
+        if (wb) {
+#pragma unroll
+            for (int e = 0; e < 32; e++) {
+                const bool valid = (wb & (0x80000000u >> e)) != 0;
+                const uint32_t m = window_top(e);
+                uint32_t b = (m >> (32 - 2 * K)) & (uint32_t)(NB - 1);
+                asm volatile("" : "+r"(b));                              // (keeps the id arithmetic out of a branch the compiler would build for the select)
+                const uint32_t pos = atomicAdd(valid ? s_cnt + b : dummy, 1u);
+                const bool fits = valid && pos < (uint32_t)C;
+                if (fits) s_slot[b * C + pos] = (uint16_t)(m >> (32 - PB));
+                if (valid && !fits) ovf |= 0x80000000u >> e;
+            }
+            kmers += __popc(wb);
+        }
+        if (ovf) {                                                     // bucket full: these keys go straight to the table
+            const unsigned long long S0 = ((unsigned long long)prev << 32) | cur0, S1 = ((unsigned long long)cur0 << 32) | cur1;
+            while (ovf) {
+                const int e = __clz(ovf);
+                ovf &= ~(0x80000000u >> e);
+                const uint32_t f = (uint32_t)((e < 16 ? S0 : S1) >> (30 - 2 * (e & 15))) & mask;
+                uint32_t id = f;
+                if (CANON) { const uint32_t r = revcomp32(f, K); id = r < f ? r : f; }
+                red_aggregated(P.tab32, id);
+            }
+        }
+        __syncthreads();
+
+        // ---- one global cursor bump per non-empty bucket ---------------------------------------------------
+        for (int b = tid; b < NB; b += kPartThreads) {
+            const uint32_t c = min(s_cnt[b], (uint32_t)C);
+            uint32_t gb = 0xFFFFFFFFu;
+            if (c) {
+                const uint32_t g = atomicAdd(P.cursor + b, c);
+                if (g + c > P.cap) atomicMin(P.fail_base + b, g);       // does not fit: RED path below
+                else gb = (uint32_t)b * P.cap + g;                      // (host keeps n_buckets * cap < 2^32)
+            }
+            s_gb[b] = gb;
+        }
+        __syncthreads();
+
+        // ---- the slots leave as payload runs ------------------------------------------------------------------
+#pragma unroll 4
+        for (uint32_t j = tid; j < (uint32_t)(NB * C); j += kPartThreads) {
+            const uint32_t b = j / (uint32_t)C, r = j - b * (uint32_t)C;
+            if (r < s_cnt[b]) {
+                const uint32_t gb = s_gb[b];
+                const uint32_t p = s_slot[j];
+                if (gb != 0xFFFFFFFFu) P.stream[gb + r] = (uint16_t)p;
+                else red_aggregated(P.tab32, (p << NBITS) | b);         // stream of this bucket is full (low-complexity input)
+            }
+        }
+      }
+    }
+    for (int d = 16; d; d >>= 1) kmers += __shfl_xor_sync(0xffffffffu, kmers, d);
+    __syncthreads();
+    if (lane == 0) s_red[warp] = kmers;
+    __syncthreads();
+    if (tid == 0) {
+        unsigned long long s = 0;
+        for (int w = 0; w < kPartThreads / 32; w++) s += s_red[w];
+        if (s) atomicAdd(&P.acc->total_kmers, s);
+    }
+}
+
 __host__ inline size_t k3p_smem_bytes(int k) { return (size_t)(kTile + 2 * (1 << (2 * k - payload_bits(k))) + 32) * sizeof(uint32_t); }
 
 typedef void (*k3p_fn)(const PartParams);
 template <int K>
 __host__ inline k3p_fn k3p_select(bool canon) { return canon ? (k3p_fn)k3p_partition<K, true> : (k3p_fn)k3p_partition<K, false>; }
+template <int K>
+__host__ inline k3p_fn k3s_select(bool canon) { return canon ? (k3p_fn)k3s_partition<K, true> : (k3p_fn)k3s_partition<K, false>; }
+__host__ inline k3p_fn k3s_kernel(int k, bool canon) {              // slotted single-sweep partition: 16-bit stream entries only
+    switch (k) {
+        case 9: return k3s_select<9>(canon);   case 10: return k3s_select<10>(canon);
+        case 11: return k3s_select<11>(canon); case 12: return k3s_select<12>(canon);
+    }
+    return nullptr;
+}
 __host__ inline k3p_fn k3p_kernel(int k, bool canon) {
     switch (k) {
         case 8: return k3p_select<8>(canon);   case 9: return k3p_select<9>(canon);
