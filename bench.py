@@ -97,28 +97,102 @@ def time_oracle(text, k, threads):
     return dt, st
 
 
+_REF_PARSE = None
+
+
+def reference_python():
+    """The UNMODIFIED reference package (oracle/_ref, put there by oracle/make_ref.sh; it travels to the GPU box with the
+    snapshot) imported against real Biopython when the box has it, else against the test-only shim tests/_bio_shim.
+    Returns kmerdb.parse or None when oracle/_ref is absent."""
+    global _REF_PARSE
+    if _REF_PARSE is None:
+        ref = os.path.join(ROOT, "oracle", "_ref")
+        if not os.path.isfile(os.path.join(ref, "kmerdb", "parse.py")):
+            return None
+        import logging
+        logging.disable(logging.CRITICAL)
+        try:
+            import Bio  # noqa: F401
+        except Exception:
+            sys.path.insert(0, os.path.join(ROOT, "tests", "_bio_shim"))
+        sys.path.insert(0, ref)
+        from kmerdb import parse
+        _REF_PARSE = parse
+    return _REF_PARSE
+
+
+def time_reference_python(text, k):
+    """One call of the reference's parse.parsefile (kmerdb/parse.py:90) on `text` written to a FASTA file; 1 core."""
+    import tempfile
+    parse = reference_python()
+    with tempfile.TemporaryDirectory() as d:
+        path = os.path.join(d, "sample.fa")
+        with open(path, "wb") as fh:
+            fh.write(text)
+        t0 = time.perf_counter()
+        counts, meta, _nul = parse.parsefile(path, k, replace_with_none=True, canonicalize=True)
+        dt = time.perf_counter() - t0
+    return dt, {"total_kmers": int(meta["total_kmers"]), "unique_kmers": int(meta["unique_kmers"]), "total_reads": int(meta["total_reads"])}
+
+
+def cpu_legs(k, ref_reads, port_reads):
+    """The two CPU baselines on bounded prefixes of the bench's own synthetic stream (oracle/synth.py restates the
+    generator in NumPy: nothing of the product is loaded): the reference's Python on 1 core (with the fixed 4^k cost of
+    kmerdb/parse.py:139-140 measured on a one-read file and shown beside it) and the C port on all host threads."""
+    from oracle import synth
+    out = {}
+    threads = host_threads()
+    if reference_python() is not None:
+        dt0, _ = time_reference_python(synth.fasta(0, 1, READ_LEN, SEED), k)
+        dt, st = time_reference_python(synth.fasta(0, ref_reads, READ_LEN, SEED), k)
+        out["cpu_baseline"] = {"value": ref_reads * READ_LEN / dt, "unit": UNIT, "cores": 1, "kind": "reference",
+                               "sample": "first %d reads of the same stream through the unmodified kmerdb.parse.parsefile (oracle/_ref, Biopython %s), %.1f s"
+                                         % (ref_reads, "shim tests/_bio_shim" if "tests/_bio_shim" in " ".join(sys.path) else "installed", dt),
+                               "fixed_4k_setup_s": dt0, "value_without_fixed_setup": ref_reads * READ_LEN / max(dt - dt0, 1e-9), "result": st}
+    text = synth.fasta(0, port_reads, READ_LEN, SEED)
+    dtp, _ = time_oracle(text, k, threads)
+    port = {"value": port_reads * READ_LEN / dtp, "unit": UNIT, "cores": threads, "kind": "port",
+            "sample": "first %d reads of the same stream, oracle/kmerdb_oracle.c on %d threads, %.1f s" % (port_reads, threads, dtp)}
+    if "cpu_baseline" in out:
+        out["cpu_baseline_port"] = port
+    else:
+        out["cpu_baseline"] = port
+    return out
+
+
 def run_reference(args):
-    """--impl reference: the reference's CPU algorithm for the path (oracle port: the reference is
-    pure Python with no compilable sources) on all host threads, bounded sample."""
+    """--impl reference: the reference's own CPU implementation of the path — the unmodified Python of kmerdb v0.9.6
+    (kmerdb.parse.parsefile, single process, 1 core: all it can use) — on a bounded prefix of the workload per step.
+    The C port on all host threads is reported beside it (cpu_baseline_port).  Falls back to the port alone only when
+    oracle/_ref is missing."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    from kmerdb_b200 import _native
+    from oracle import synth
+    have_ref = reference_python() is not None
+    n_reads = args.ref_reads if have_ref else args.cpu_reads
+    text = synth.fasta(0, n_reads, READ_LEN, SEED)
     threads = host_threads()
-    n_reads = args.cpu_reads
-    text = _native.synth_host(n_reads, READ_LEN, seed=SEED)
+
+    def step():
+        return time_reference_python(text, args.k)[0] if have_ref else time_oracle(text, args.k, threads)[0]
     for _ in range(args.warmup):
-        time_oracle(text, args.k, threads)
-    times = [time_oracle(text, args.k, threads)[0] for _ in range(args.steps)]
+        step()
+    times = [step() for _ in range(args.steps)]
     dt = sum(times)
     value = n_reads * READ_LEN * args.steps / dt
-    sample = "first %d of the synthetic %d bp reads (FASTA, seed %d) per step" % (n_reads, READ_LEN, SEED)
+    legs = cpu_legs(args.k, args.ref_reads, args.cpu_reads)
+    base = dict(legs["cpu_baseline"])
+    base["value"] = value
+    base["sample"] = "first %d of the synthetic %d bp reads (FASTA, seed %d) per step; %s" % (n_reads, READ_LEN, SEED, base["sample"])
+    cfg = workload_config(args, args.gpus)
+    cfg["timed_sample"] = "%d reads (%d bases) per step: a bounded prefix of the workload, not the %d reads of the GPU arm" % (n_reads, n_reads * READ_LEN, args.reads)
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
-            "vs_baseline": None, "dtype": "u32", "data": "synthetic",
-            "config": workload_config(args, args.gpus),
-            "cpu_baseline": {"value": value, "unit": UNIT, "cores": threads, "kind": "port", "sample": sample},
+            "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": cfg, "cpu_baseline": base,
             "e2e": {"value": value, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    if "cpu_baseline_port" in legs:
+        line["cpu_baseline_port"] = legs["cpu_baseline_port"]
     _emit(line)
 
 
@@ -277,11 +351,7 @@ def run_b200(args):
             "result_check": {"total_kmers": stats["total_kmers"], "unique_kmers": stats["unique_kmers"], "total_reads": stats["total_reads"]},
         }
         if not args.no_cpu_baseline:
-            threads = host_threads()
-            text = pin_text.array[: args.cpu_reads * rb]
-            dt, ost = time_oracle(text, k, threads)
-            line["cpu_baseline"] = {"value": args.cpu_reads * READ_LEN / dt, "unit": UNIT, "cores": threads, "kind": "port",
-                                    "sample": "first %d reads of the same stream, oracle/kmerdb_oracle.c on %d threads, %.1f s" % (args.cpu_reads, threads, dt)}
+            line.update(cpu_legs(k, args.ref_reads, args.cpu_reads))
         _emit(line)
     if world > 1:
         dist.barrier()
@@ -311,7 +381,8 @@ def main():
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
     ap.add_argument("--reads", type=int, default=10_000_000, help="reads per GPU (configs[1]: 10M x 150 bp)")
     ap.add_argument("--k", type=int, default=12)
-    ap.add_argument("--cpu-reads", type=int, default=2_000_000, help="bounded sample for the CPU legs")
+    ap.add_argument("--cpu-reads", type=int, default=2_000_000, help="bounded sample for the C-port CPU leg")
+    ap.add_argument("--ref-reads", type=int, default=2_000, help="bounded sample (reads per step) for the Python reference")
     ap.add_argument("--no-cpu-baseline", action="store_true")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":

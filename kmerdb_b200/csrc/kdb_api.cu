@@ -13,6 +13,7 @@
 #include "kdb_common.cuh"
 #include "kdb_scan.cuh"
 #include "kdb_encode.cuh"
+#include "kdb_encode2.cuh"
 #include "kdb_hist.cuh"
 #include "kdb_part.cuh"
 #include "kdb_final.cuh"
@@ -62,6 +63,17 @@ struct kdb_ctx {
     uint16_t* stream = nullptr;
     size_t stream_cap = 0;
     unsigned int* cursor = nullptr;             // n_buckets cursors + n_buckets fail bases
+    // single-pass tokeniser (k2s_encode): look-back status words, border records, ticket, device-resident carry
+    bool single_pass = false;
+    TileLook* look = nullptr;                   // n_tiles status words, then n_tiles TileRec (one allocation)
+    TileRec* trec = nullptr;
+    size_t look_cap = 0;
+    unsigned int* ticket = nullptr;
+    PassCarry* pcarry = nullptr;                // two copies: a pass reads [pc_idx], writes [pc_idx ^ 1]
+    int pc_idx = 0;
+    uint8_t* zero_row = nullptr;                // 64 zero bytes: tensor map base for a pass shorter than one row
+    void* null_scratch = nullptr;               // kdb_nullomers: per-block zero counts and offsets
+    size_t null_cap = 0;
     // host mirrors
     ScanCarry h_carry{};
     bool have_carry = false;
@@ -91,6 +103,36 @@ struct kdb_ctx {
             return KDB_E_CUDA;                                                                     \
         }                                                                                          \
     } while (0)
+
+struct DevBuf {                      // scoped device allocation: freed on every exit path, CK() returns included
+    void* p = nullptr;
+    ~DevBuf() { if (p) cudaFree(p); }
+    cudaError_t alloc(size_t n) { return cudaMalloc(&p, n ? n : 16); }
+    template <typename T> T* as() { return static_cast<T*>(p); }
+};
+
+// cuTensorMapEncodeTiled through the runtime's driver entry point (no link against libcuda)
+typedef CUresult (*tensor_map_encode_fn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*, const cuuint32_t*,
+                                         const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+static tensor_map_encode_fn tensor_map_encoder() {
+    static tensor_map_encode_fn fn = nullptr;
+    if (!fn) {
+        void* p = nullptr;
+        cudaDriverEntryPointQueryResult q;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &p, cudaEnableDefault, &q) == cudaSuccess && q == cudaDriverEntryPointSuccess) fn = (tensor_map_encode_fn)p;
+    }
+    return fn;
+}
+// The text of one pass as rows of 64 bytes; box = one 16 KiB tile (256 rows); 64-byte swizzle = the layout k2s_encode reads with
+// conflict-free LDS.128.  Only whole rows are part of the tensor: rows past the end arrive as zeros.
+static bool make_text_map(CUtensorMap* m, const uint8_t* base, unsigned long long rows) {
+    const cuuint64_t dims[2] = {(cuuint64_t)kChunk, (cuuint64_t)rows};
+    const cuuint64_t strides[1] = {(cuuint64_t)kChunk};
+    const cuuint32_t box[2] = {(cuuint32_t)kChunk, (cuuint32_t)kThreads};
+    const cuuint32_t estr[2] = {1, 1};
+    return tensor_map_encoder()(m, CU_TENSOR_MAP_DATA_TYPE_UINT8, 2, const_cast<uint8_t*>(base), dims, strides, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                                CU_TENSOR_MAP_SWIZZLE_64B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE) == CUDA_SUCCESS;
+}
 
 static void build_class_lut(uint8_t* lut) {
     for (int c = 0; c < 256; c++) {
@@ -132,6 +174,7 @@ extern "C" void kdb_destroy(kdb_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaFree(ctx->tab32); cudaFree(ctx->tab64); cudaFree(ctx->acc); cudaFree(ctx->carry); cudaFree(ctx->carry_len);
     cudaFree(ctx->tile_sum); /* tile_state lives inside the tile_sum allocation */ cudaFree(ctx->rec_len); cudaFree(ctx->feed_buf); cudaFree(ctx->packed); cudaFree(ctx->stream); cudaFree(ctx->cursor);
+    cudaFree(ctx->look); /* trec lives inside the look allocation */ cudaFree(ctx->ticket); cudaFree(ctx->pcarry); cudaFree(ctx->zero_row); cudaFree(ctx->null_scratch);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     for (auto& e : ctx->ev_copy) cudaEventDestroy(e);
     if (ctx->ev_job0) cudaEventDestroy(ctx->ev_job0);
@@ -150,6 +193,8 @@ static int reset_state(kdb_ctx* ctx) {
     CK(cudaMemcpyAsync(ctx->acc, &a, sizeof a, cudaMemcpyHostToDevice, ctx->s_compute));
     CK(cudaMemsetAsync(ctx->carry, 0, sizeof(ScanCarry), ctx->s_compute));
     CK(cudaMemsetAsync(ctx->carry_len, 0, 2 * sizeof(unsigned long long), ctx->s_compute));
+    CK(cudaMemsetAsync(ctx->pcarry, 0, 2 * sizeof(PassCarry), ctx->s_compute));
+    ctx->pc_idx = 0;
     CK(cudaStreamSynchronize(ctx->s_compute));
     ctx->h_carry = ScanCarry{};
     ctx->have_carry = false; ctx->carry_rec_id = 0; ctx->fq_rec_base = 0; ctx->bytes_since_fold = 0;
@@ -209,6 +254,12 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
     if ((e = cudaMalloc(&ctx->acc, sizeof(Accum))) != cudaSuccess) return fail("cudaMalloc acc", e);
     if ((e = cudaMalloc(&ctx->carry, sizeof(ScanCarry))) != cudaSuccess) return fail("cudaMalloc carry", e);
     if ((e = cudaMalloc(&ctx->carry_len, 2 * sizeof(unsigned long long))) != cudaSuccess) return fail("cudaMalloc carry_len", e);
+    if ((e = cudaMalloc(&ctx->pcarry, 2 * sizeof(PassCarry))) != cudaSuccess) return fail("cudaMalloc pcarry", e);
+    if ((e = cudaMalloc(&ctx->ticket, sizeof(unsigned int))) != cudaSuccess) return fail("cudaMalloc ticket", e);
+    if ((e = cudaMalloc(&ctx->zero_row, 256)) != cudaSuccess) return fail("cudaMalloc zero_row", e);
+    if ((e = cudaMemset(ctx->zero_row, 0, 256)) != cudaSuccess) return fail("cudaMemset zero_row", e);
+    ctx->single_pass = !getenv("KDB_TWO_PASS");
+    if (ctx->single_pass && !tensor_map_encoder()) { g_last_error = "cuTensorMapEncodeTiled is not available from this driver"; kdb_destroy(ctx); return nullptr; }
     // launch geometry: persistent CTAs, a whole number per SM
     int rc;
     ctx->hist_kernel = k3_kernel(k, ctx->canonical);
@@ -228,14 +279,15 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
         ctx->parts = std::max(1, ((payload_bits(k) == 15 ? 888 : 1776) + ctx->n_buckets - 1) / ctx->n_buckets);
         const size_t dyn = ctx->slotted ? k3s_smem_bytes(k) : k3p_smem_bytes(k);
         if ((e = cudaFuncSetAttribute((const void*)ctx->part_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)dyn)) != cudaSuccess) return fail("smem attr", e);
-        if ((e = cudaFuncSetAttribute((const void*)k3p_count<14>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << 14)) != cudaSuccess) return fail("smem attr", e);
-        if ((e = cudaFuncSetAttribute((const void*)k3p_count<15>, cudaFuncAttributeMaxDynamicSharedMemorySize, 4 << 15)) != cudaSuccess) return fail("smem attr", e);
+        if ((e = cudaFuncSetAttribute((const void*)k3p_count<14>, cudaFuncAttributeMaxDynamicSharedMemorySize, (4 << 14) + 128)) != cudaSuccess) return fail("smem attr", e);
+        if ((e = cudaFuncSetAttribute((const void*)k3p_count<15>, cudaFuncAttributeMaxDynamicSharedMemorySize, (4 << 15) + 128)) != cudaSuccess) return fail("smem attr", e);
         if ((e = cudaFuncSetAttribute((const void*)k3p_count16, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024)) != cudaSuccess) return fail("smem attr", e);
         if ((e = cudaFuncSetAttribute((const void*)k3p_count16w, cudaFuncAttributeMaxDynamicSharedMemorySize, 128 * 1024)) != cudaSuccess) return fail("smem attr", e);
         if (!rc) rc = occupancy_grid(ctx->part_kernel, kPartThreads, dyn, &ctx->part_grid);
         if ((e = cudaMalloc(&ctx->cursor, 2 * ctx->n_buckets * sizeof(unsigned int))) != cudaSuccess) return fail("cudaMalloc cursor", e);
     }
-    if (!rc) rc = ctx->fastq ? occupancy_grid(k2_encode<true>, kThreads, 0, &ctx->encode_grid) : occupancy_grid(k2_encode<false>, kThreads, 0, &ctx->encode_grid);
+    if (!rc && ctx->single_pass) rc = ctx->fastq ? occupancy_grid(k2s_encode<true>, kThreads, 0, &ctx->encode_grid) : occupancy_grid(k2s_encode<false>, kThreads, 0, &ctx->encode_grid);
+    else if (!rc) rc = ctx->fastq ? occupancy_grid(k2_encode<true>, kThreads, 0, &ctx->encode_grid) : occupancy_grid(k2_encode<false>, kThreads, 0, &ctx->encode_grid);
     if (rc) { kdb_destroy(ctx); return nullptr; }
     if (reset_state(ctx)) { g_last_error = ctx->err; kdb_destroy(ctx); return nullptr; }
     if ((e = cudaGetLastError()) != cudaSuccess) return fail("kdb_create", e);
@@ -323,8 +375,8 @@ static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigne
         CK(cudaEventRecord(ctx->ev[7], st));
         if (ctx->wide) k3p_count16w<<<ctx->n_buckets << (payload_bits(ctx->k) - 16), kCount16Threads, 128 * 1024, st>>>(reinterpret_cast<const uint32_t*>(src->stream), Q.cursor, Q.fail_base, cap, payload_bits(ctx->k), ctx->tab32);
         else if (ctx->subs == 0) k3p_count16<<<ctx->n_buckets, kCount16Threads, 128 * 1024, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->tab32);
-        else if (payload_bits(ctx->k) == 15) k3p_count<15><<<ctx->n_buckets * ctx->parts, 1024, 4 << 15, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->tab32, ctx->slotted ? 2 * ctx->k - 15 : 0);
-        else k3p_count<14><<<ctx->n_buckets * ctx->parts, kBucketThreads, 4 << 14, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->tab32, ctx->slotted ? 2 * ctx->k - 14 : 0);
+        else if (payload_bits(ctx->k) == 15) k3p_count<15><<<ctx->n_buckets * ctx->parts, 1024, (4 << 15) + 128, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->tab32, ctx->slotted ? 2 * ctx->k - 15 : 0);
+        else k3p_count<14><<<ctx->n_buckets * ctx->parts, kBucketThreads, (4 << 14) + 128, st>>>(src->stream, Q.cursor, Q.fail_base, cap, ctx->parts, ctx->tab32, ctx->slotted ? 2 * ctx->k - 14 : 0);
         CK(cudaGetLastError());
         ctx->timing.total_launches++;
     } else {
@@ -434,10 +486,81 @@ static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, un
     return KDB_OK;
 }
 
+// One pass with the single-pass tokeniser: K2s (ticket order, look-back, TMA staging) -> count stage -> border records.
+// Nothing is read back in the middle: the carry between passes lives on the device.
+static int run_pass2(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, unsigned long long hi, unsigned long long n) {
+    const unsigned int n_tiles = (unsigned int)((hi - lo + kTile - 1) / kTile);
+    if (int rc = ensure(ctx, (void**)&ctx->look, &ctx->look_cap, n_tiles, sizeof(TileLook) + sizeof(TileRec))) return rc;
+    ctx->trec = reinterpret_cast<TileRec*>(ctx->look + ctx->look_cap);
+    if (ctx->bytes_since_fold + (hi - lo) > 0x7fffffffull) if (int rc = fold_now(ctx)) return rc;
+    if (int rc = ensure(ctx, (void**)&ctx->packed, &ctx->packed_cap, (size_t)n_tiles * kPackStride, sizeof(uint32_t))) return rc;
+    CK(cudaGetLastError());
+    CUtensorMap tmap;
+    const unsigned long long rows = (hi - lo) / kChunk;
+    if (!make_text_map(&tmap, rows ? text + lo : ctx->zero_row, rows ? rows : 1)) { ctx->err = "cuTensorMapEncodeTiled failed"; return KDB_E_CUDA; }
+    CK(cudaEventRecord(ctx->ev[0], ctx->s_compute));
+    CK(cudaMemsetAsync(ctx->look, 0, (size_t)n_tiles * sizeof(TileLook), ctx->s_compute));
+    CK(cudaMemsetAsync(ctx->ticket, 0, sizeof(unsigned int), ctx->s_compute));
+    CK(cudaEventRecord(ctx->ev[1], ctx->s_compute));
+    EncodeParams2 P{};
+    P.text = text + lo; P.feed = text; P.lo = lo; P.hi = hi; P.n = n; P.n_tiles = n_tiles; P.k = ctx->k; P.skip_n = ctx->skip_n;
+    P.k_halo = std::max(ctx->k, ctx->k_halo); P.short_k = ctx->short_k; P.packed = ctx->packed; P.look = ctx->look; P.trec = ctx->trec;
+    P.ticket = ctx->ticket; P.carry_in = ctx->pcarry + ctx->pc_idx; P.carry_out = ctx->pcarry + (ctx->pc_idx ^ 1); P.acc = ctx->acc;
+    CK(cudaEventRecord(ctx->ev[2], ctx->s_compute));
+    {
+        const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->encode_grid);
+        if (ctx->fastq) k2s_encode<true><<<grid, kThreads, 0, ctx->s_compute>>>(P, tmap);
+        else k2s_encode<false><<<grid, kThreads, 0, ctx->s_compute>>>(P, tmap);
+        CK(cudaGetLastError());
+    }
+    CK(cudaEventRecord(ctx->ev[6], ctx->s_compute));
+    if (int rc = count_stage(ctx, ctx, n_tiles, lo, hi)) return rc;
+    CK(cudaEventRecord(ctx->ev[3], ctx->s_compute));
+    for (kdb_ctx* f : ctx->followers) {                                  // larger k of a sweep, from the same packed stream
+        CK(cudaEventRecord(f->ev[6], ctx->s_compute));
+        if (int rc = count_stage(f, ctx, n_tiles, lo, hi)) { ctx->err = f->err; return rc; }
+        CK(cudaEventRecord(f->ev[3], ctx->s_compute));
+    }
+    CK(cudaEventRecord(ctx->ev[5], ctx->s_compute));
+    {
+        const int g = (int)((n_tiles + kStitchThreads - 1) / kStitchThreads);
+        if (ctx->fastq) k4_stitch_records<true><<<g, kStitchThreads, 0, ctx->s_compute>>>(ctx->trec, n_tiles, P.carry_in, P.carry_out, ctx->short_k, ctx->acc);
+        else k4_stitch_records<false><<<g, kStitchThreads, 0, ctx->s_compute>>>(ctx->trec, n_tiles, P.carry_in, P.carry_out, ctx->short_k, ctx->acc);
+        CK(cudaGetLastError());
+    }
+    ctx->pc_idx ^= 1;
+    CK(cudaEventRecord(ctx->ev[4], ctx->s_compute));
+    CK(cudaEventSynchronize(ctx->ev[4]));
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1])); ctx->timing.scan_ms += ms;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[6])); ctx->timing.encode_ms += ms;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[6], ctx->ev[3])); ctx->timing.count_ms += ms;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[6], ctx->ev[7])); ctx->timing.partition_ms += ms;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[5], ctx->ev[4])); ctx->timing.final_ms += ms;
+    for (kdb_ctx* f : ctx->followers) {
+        CK(cudaEventElapsedTime(&ms, f->ev[6], f->ev[3])); f->timing.count_ms += ms;
+        CK(cudaEventElapsedTime(&ms, f->ev[6], f->ev[7])); f->timing.partition_ms += ms;
+    }
+    ctx->timing.count_launches++;
+    ctx->timing.total_launches += 3;
+    ctx->bytes_since_fold += hi - lo;
+    return KDB_OK;
+}
+
+// mode bit 0: the open record is complete, check it; bit 1: a feed ended (k4_close_carry)
+static int close_carry2(kdb_ctx* ctx, int mode) {
+    if (ctx->fastq) k4_close_carry<true><<<1, 32, 0, ctx->s_compute>>>(ctx->pcarry + ctx->pc_idx, mode, ctx->short_k, ctx->acc);
+    else k4_close_carry<false><<<1, 32, 0, ctx->s_compute>>>(ctx->pcarry + ctx->pc_idx, mode, ctx->short_k, ctx->acc);
+    CK(cudaGetLastError());
+    ctx->timing.total_launches++;
+    return KDB_OK;
+}
+
 static int begin_feed(kdb_ctx* ctx) {
     if (ctx->leader) { ctx->err = "kdb_feed on a follower: feed its leader"; return KDB_E_STATE; }
     if (ctx->finished) { ctx->err = "kdb_feed after kdb_finish (call kdb_reset first)"; return KDB_E_STATE; }
     if (!ctx->job_started) { CK(cudaEventRecord(ctx->ev_job0, ctx->s_compute)); ctx->job_started = true; }
+    if (ctx->single_pass) return KDB_OK;                                 // (the end of the feed before reset the line indices on the device)
     // line indices restart with every fragment (fragments begin at a record boundary)
     ctx->h_carry.ls_total = 0; ctx->h_carry.last = 0;
     CK(cudaMemcpyAsync(ctx->carry, &ctx->h_carry, sizeof(ScanCarry), cudaMemcpyHostToDevice, ctx->s_compute));
@@ -445,7 +568,10 @@ static int begin_feed(kdb_ctx* ctx) {
 }
 
 static int end_feed(kdb_ctx* ctx, size_t n) {
-    if (ctx->fastq) {
+    if (ctx->single_pass) {
+        // line indices restart with every fragment; a FASTQ fragment ends with a complete record
+        if (int rc = close_carry2(ctx, ctx->fastq ? 3 : 2)) return rc;
+    } else if (ctx->fastq) {
         if (ctx->h_carry.ls_total % 4 != 0) ctx->host_layout = true;   // truncated / blank-line tail: host tokeniser decides
         ctx->fq_rec_base += ctx->h_carry.ls_total / 4;
     }
@@ -459,9 +585,9 @@ extern "C" int kdb_feed_device(kdb_ctx* ctx, const uint8_t* dev_bytes, size_t n)
     if (n == 0) return KDB_OK;
     if (!dev_bytes || ((uintptr_t)dev_bytes & 15)) { ctx->err = "device text must be 16-byte aligned"; return KDB_E_ARG; }
     if (int rc = begin_feed(ctx)) return rc;
-    const unsigned long long pass = 1ull << 30;
+    const unsigned long long pass = ctx->single_pass ? kPassBytes : 1ull << 30;     // (TileLook: the counts of a pass fit 30 bits)
     for (unsigned long long lo = 0; lo < n; lo += pass)
-        if (int rc = run_pass(ctx, dev_bytes, lo, std::min<unsigned long long>(lo + pass, n), n)) return rc;
+        if (int rc = (ctx->single_pass ? run_pass2 : run_pass)(ctx, dev_bytes, lo, std::min<unsigned long long>(lo + pass, n), n)) return rc;
     return end_feed(ctx, n);
 }
 
@@ -486,7 +612,7 @@ extern "C" int kdb_feed_host(kdb_ctx* ctx, const uint8_t* bytes, size_t n) {
     for (size_t i = 0; i < n_pass; i++) {
         const unsigned long long lo = i * pass, hi = std::min<unsigned long long>(lo + pass, n);
         CK(cudaStreamWaitEvent(ctx->s_compute, ctx->ev_copy[i], 0));
-        if (int rc = run_pass(ctx, ctx->feed_buf, lo, hi, n)) return rc;
+        if (int rc = (ctx->single_pass ? run_pass2 : run_pass)(ctx, ctx->feed_buf, lo, hi, n)) return rc;
     }
     float ms = 0;
     CK(cudaEventSynchronize(ctx->ev_copy[n_pass - 1]));
@@ -508,6 +634,12 @@ static int fill_stats(kdb_ctx* ctx) {
     Accum a;
     CK(cudaMemcpyAsync(&a, ctx->acc, sizeof a, cudaMemcpyDeviceToHost, ctx->s_compute));
     CK(cudaStreamSynchronize(ctx->s_compute));
+    if (ctx->single_pass) {
+        PassCarry pc;
+        CK(cudaMemcpyAsync(&pc, ctx->pcarry + ctx->pc_idx, sizeof pc, cudaMemcpyDeviceToHost, ctx->s_compute));
+        CK(cudaStreamSynchronize(ctx->s_compute));
+        ctx->fq_rec_base = pc.fq_rec_base; ctx->h_carry.hdr_total = pc.hdr_total;
+    }
     kdb_stats_t& s = ctx->stats;
     s = kdb_stats_t{};
     s.total_reads = ctx->fastq ? ctx->fq_rec_base : ctx->h_carry.hdr_total;
@@ -558,7 +690,8 @@ extern "C" int kdb_finish(kdb_ctx* ctx) {
     if (ctx->leader) return finish_follower(ctx);
     if (!ctx->job_started) { CK(cudaEventRecord(ctx->ev_job0, ctx->s_compute)); ctx->job_started = true; }
     CK(cudaEventRecord(ctx->ev[0], ctx->s_compute));
-    if (int rc = close_carry_record(ctx)) return rc;
+    if (ctx->single_pass) { if (int rc = close_carry2(ctx, 1)) return rc; }
+    else if (int rc = close_carry_record(ctx)) return rc;
     CK(cudaMemsetAsync(&ctx->acc->unique, 0, sizeof(unsigned long long), ctx->s_compute));
     if (int rc = fold_now(ctx, true)) return rc;
     CK(cudaEventRecord(ctx->ev[1], ctx->s_compute));
@@ -592,9 +725,12 @@ extern "C" int kdb_nullomers(kdb_ctx* ctx, uint64_t* out_ids, size_t cap, size_t
     if (!ctx->finished) { ctx->err = "kdb_nullomers before kdb_finish"; return KDB_E_STATE; }
     if (int rc = set_device(ctx, ctx->device)) return rc;
     const unsigned int blocks = (unsigned int)((ctx->nbins + kNullBlock - 1) / kNullBlock);
-    unsigned int* d_cnt = nullptr; unsigned long long* d_off = nullptr; unsigned long long* d_out = nullptr;
-    CK(cudaMalloc(&d_cnt, blocks * sizeof(unsigned int)));
+    // block counts + offsets: per-context scratch kept between calls (12 B per 2048 bins); ids: scoped, freed on every exit path
+    if (int rc = ensure(ctx, (void**)&ctx->null_scratch, &ctx->null_cap, blocks, sizeof(unsigned int) + sizeof(unsigned long long))) return rc;
+    unsigned long long* d_off = reinterpret_cast<unsigned long long*>(ctx->null_scratch);
+    unsigned int* d_cnt = reinterpret_cast<unsigned int*>(d_off + ctx->null_cap);
     k6_null_count<<<blocks, 256, 0, ctx->s_compute>>>(ctx->tab64, ctx->nbins, d_cnt);
+    CK(cudaGetLastError());
     std::vector<unsigned int> h_cnt(blocks);
     CK(cudaMemcpyAsync(h_cnt.data(), d_cnt, blocks * sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->s_compute));
     CK(cudaStreamSynchronize(ctx->s_compute));
@@ -605,16 +741,15 @@ extern "C" int kdb_nullomers(kdb_ctx* ctx, uint64_t* out_ids, size_t cap, size_t
     ctx->timing.total_launches++;
     const size_t m = std::min<size_t>(cap, (size_t)total);
     if (out_ids && m) {
-        CK(cudaMalloc(&d_off, blocks * sizeof(unsigned long long)));
-        CK(cudaMalloc(&d_out, m * sizeof(unsigned long long)));
+        DevBuf d_out;
+        CK(d_out.alloc(m * sizeof(unsigned long long)));
         CK(cudaMemcpyAsync(d_off, h_off.data(), blocks * sizeof(unsigned long long), cudaMemcpyHostToDevice, ctx->s_compute));
-        k6_null_write<<<blocks, 256, 0, ctx->s_compute>>>(ctx->tab64, ctx->nbins, d_off, d_out, m);
+        k6_null_write<<<blocks, 256, 0, ctx->s_compute>>>(ctx->tab64, ctx->nbins, d_off, d_out.as<unsigned long long>(), m);
         CK(cudaGetLastError());
-        CK(cudaMemcpyAsync(out_ids, d_out, m * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->s_compute));
+        CK(cudaMemcpyAsync(out_ids, d_out.p, m * sizeof(unsigned long long), cudaMemcpyDeviceToHost, ctx->s_compute));
         CK(cudaStreamSynchronize(ctx->s_compute));
         ctx->timing.total_launches++;
     }
-    cudaFree(d_cnt); cudaFree(d_off); cudaFree(d_out);
     return KDB_OK;
 }
 
@@ -668,6 +803,11 @@ extern "C" int kdb_import_partials(kdb_ctx* ctx, const uint64_t* in16) {
     a.layout_flag = in16[11] ? 1 : 0;
     CK(cudaMemcpy(ctx->acc, &a, sizeof a, cudaMemcpyHostToDevice));
     if (ctx->fastq) ctx->fq_rec_base = in16[0]; else ctx->h_carry.hdr_total = in16[0];
+    if (ctx->single_pass) {
+        PassCarry pc{};
+        pc.fq_rec_base = ctx->fq_rec_base; pc.hdr_total = ctx->h_carry.hdr_total;
+        CK(cudaMemcpy(ctx->pcarry + ctx->pc_idx, &pc, sizeof pc, cudaMemcpyHostToDevice));
+    }
     ctx->host_layout = false;
     return KDB_OK;
 }
@@ -711,14 +851,13 @@ extern "C" int kdb_kmer_to_id_batch(int device, const char* kmers, size_t n, int
     uint8_t lut[256];
     build_class_lut(lut);
     CK(cudaMemcpyToSymbol(c_class_lut, lut, 256));
-    char* d_k = nullptr; unsigned long long* d_ids = nullptr;
-    CK(cudaMalloc(&d_k, n * (size_t)k));
-    CK(cudaMalloc(&d_ids, n * sizeof(unsigned long long)));
-    CK(cudaMemcpy(d_k, kmers, n * (size_t)k, cudaMemcpyHostToDevice));
-    k_kmer_to_id<<<(unsigned int)((n + 255) / 256), 256>>>(d_k, n, k, canonical, d_ids);
+    DevBuf d_k, d_ids;                           // scoped: freed on every exit path
+    CK(d_k.alloc(n * (size_t)k));
+    CK(d_ids.alloc(n * sizeof(unsigned long long)));
+    CK(cudaMemcpy(d_k.p, kmers, n * (size_t)k, cudaMemcpyHostToDevice));
+    k_kmer_to_id<<<(unsigned int)((n + 255) / 256), 256>>>(d_k.as<char>(), n, k, canonical, d_ids.as<unsigned long long>());
     CK(cudaGetLastError());
-    CK(cudaMemcpy(ids, d_ids, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
-    cudaFree(d_k); cudaFree(d_ids);
+    CK(cudaMemcpy(ids, d_ids.p, n * sizeof(unsigned long long), cudaMemcpyDeviceToHost));
     return KDB_OK;
 }
 
@@ -824,12 +963,6 @@ extern "C" int kdb_memcpy_d2h(int device, void* dst, const void* src, size_t n) 
 
 // ---- K4: graph edge rows, aggregated edge weights, minimizers (kdb_graph.cuh) -----------------------------
 namespace {
-struct DevBuf {                      // scoped device allocation for the stateless K4 entry points
-    void* p = nullptr;
-    ~DevBuf() { if (p) cudaFree(p); }
-    cudaError_t alloc(size_t n) { return cudaMalloc(&p, n ? n : 16); }
-    template <typename T> T* as() { return static_cast<T*>(p); }
-};
 int upload_lut(kdb_ctx* ctx) {
     uint8_t lut[256];
     build_class_lut(lut);

@@ -58,6 +58,32 @@ struct ScanCarry {
     unsigned int pad;
 };
 
+// ---- single-pass tokeniser (k2s_encode): decoupled look-back over the tiles of a pass --------------------------
+// One status word per tile, written and read whole (no fence is needed around it): [63:62] state (0 nothing, 1 tile aggregate,
+// 2 inclusive prefix of the pass), [61:60] `last`, [59:30] line starts, [29:0] title lines.  A pass is at most 2^29 bytes
+// (kPassBytes), so both counts fit their 30 bits and the two fields add without carrying into each other.
+struct TileLook {
+    unsigned long long w0;
+};
+constexpr unsigned long long kPassBytes = 1ull << 29;
+// What a tile knows about the records that cross its borders (k2s_encode -> k4_stitch_records).
+struct TileRec {
+    unsigned int head_len, head_qlen;   // letters / quality chars from the tile start to its first record start
+    unsigned int tail_len, tail_qlen;   // ... of the record open at the tile end (whole tile when no record starts in it)
+    unsigned int flags;                 // bit 0: a record starts in the tile; bit 1: a record was open before that first start
+    unsigned int pad;
+    unsigned long long head_rec;        // id of the record the first start closes
+};
+// Device-resident state carried from pass to pass and feed to feed (two copies: pass p reads [p & 1], writes [(p + 1) & 1]).
+struct PassCarry {
+    unsigned long long ls_total;        // line starts so far in this feed
+    unsigned long long hdr_total;       // FASTA title lines so far in the file
+    unsigned long long fq_rec_base;     // FASTQ records in earlier feeds
+    unsigned long long olen, oqlen;     // letters / quality chars of the record that is still open
+    unsigned int last;                  // class of the last line start (0 none, 1 other, 2 '>')
+    unsigned int open;                  // a record is open
+};
+
 // Fused scalar reductions (one instance per context, device resident).
 struct Accum {
     unsigned long long total_kmers;

@@ -29,6 +29,12 @@ namespace kdb {
 // 16-bit counters per bucket, k3p_count16); 17 for k = 14 (32-bit entries, 2048 buckets, two sub-passes of 16 bits: with 16-bit
 // payloads k = 14 needs 4096 buckets, which leaves 4 entries per bucket per tile — 8-byte runs and one cursor bump per 4 keys)
 __host__ __device__ constexpr int payload_bits(int k) { return k <= 11 ? 14 : (k == 12 ? 15 : (k == 13 ? 16 : KDB_PB14)); }
+// k3s_partition (below): the bucket of an id is its bits [kBucketShift, kBucketShift + nbits), the payload the bits above and below
+// it squeezed together; this puts them back
+constexpr int kBucketShift = 8;
+__host__ __device__ constexpr uint32_t slotted_id(uint32_t payload, uint32_t bucket, int nbits) {
+    return ((payload >> kBucketShift) << (kBucketShift + nbits)) | (bucket << kBucketShift) | (payload & ((1u << kBucketShift) - 1u));
+}
 constexpr int kPartThreads = 512;                      // 512 threads x 32 letters = one full tile
 constexpr int kBucketThreads = 256;
 
@@ -226,7 +232,7 @@ __global__ void __launch_bounds__(kPartThreads, 3) k3p_partition(const PartParam
 template <int TB>
 __global__ void __launch_bounds__(TB == 14 ? kBucketThreads : 1024) k3p_count(const uint16_t* __restrict__ stream, const unsigned int* __restrict__ cursor,
                                                                               const unsigned int* __restrict__ fail_base, unsigned int cap, int parts,
-                                                                              unsigned int* __restrict__ tab32, int low_bits) {   // low_bits != 0: buckets are the id's low bits (k3s_partition)
+                                                                              unsigned int* __restrict__ tab32, int low_bits) {   // low_bits != 0: the streams come from k3s_partition (bucket = id bits [kBucketShift, kBucketShift + low_bits))
     extern __shared__ unsigned int s_tab[];
     const uint32_t tid = threadIdx.x, nthr = blockDim.x;
     const uint32_t b = blockIdx.x / parts, part = blockIdx.x % parts;
@@ -246,11 +252,11 @@ __global__ void __launch_bounds__(TB == 14 ? kBucketThreads : 1024) k3p_count(co
         const uint32_t valid = min(8u, end - 8 * u);
 #pragma unroll
         for (int q = 0; q < 8; q++)
-            if ((uint32_t)q < valid) atomicAdd(&s_tab[(w[q >> 1] >> (16 * (q & 1))) & ((1u << TB) - 1u)], 1u);
+            if ((uint32_t)q < valid) atomicAdd(&s_tab[min((w[q >> 1] >> (16 * (q & 1))) & 0xFFFFu, (1u << TB) + (tid & 31u))], 1u);   // (0xFFFF pads the runs of k3s_partition: per-lane dummy bins behind the table)
     }
     __syncthreads();
-    if (low_bits) {                                                   // bin p of bucket b is id (p << low_bits) | b: one RED per sector, L2-resident table
-        for (uint32_t i = tid; i < (1u << TB); i += nthr) { const unsigned int x = s_tab[i]; if (x) atomicAdd(tab32 + (((size_t)i << low_bits) | b), x); }
+    if (low_bits) {                                                   // bin p of bucket b (k3s_partition): runs of 2^kBucketShift consecutive ids
+        for (uint32_t i = tid; i < (1u << TB); i += nthr) { const unsigned int x = s_tab[i]; if (x) atomicAdd(tab32 + slotted_id(i, b, low_bits), x); }
         return;
     }
     unsigned int* dst = tab32 + ((size_t)b << TB);
@@ -336,21 +342,21 @@ __global__ void __launch_bounds__(kCount16Threads) k3p_count16w(const uint32_t* 
 // ---- single-sweep slotted partition (r02) ----------------------------------------------------------------------
 // One returning shared atomic + one predicated 2-byte store per key (the two-sweep sort above pays a histogram atomic, a cursor
 // atomic and a scatter store, and builds every id twice).  Every bucket owns a fixed range of C slots in shared memory;
-// pos = atomicAdd(&cnt[b], 1) is the slot, so there is no scan and no second pass over the letters.  Buckets are the LOW bits of
-// the id: for canonical ids (min of the two strands) the high bits are skewed 2:0 over the id range, the low bits are uniform, so
-// one slot count fits every bucket and the slot address is b * C + pos with C an immediate.  The payload is the id's high bits;
-// k3p_count<TB, true> puts bin p of bucket b back at tab32[p << NBITS | b].  A key that finds its bucket full (pos >= C: about
-// +4 sigma of a dense tile on uniform sequence; low-complexity sequence does it all the time) is remembered in a per-thread bit
-// mask and goes to the global table directly after the loop (warp-aggregated REDs), so the result is exact for any input.
-#ifndef KDB_SLOT_SIGMAS
-#define KDB_SLOT_SIGMAS 4
-#endif
-__host__ __device__ constexpr int slot_count(int nb) {
-    // dense text: kTile letters per unit; mean + KDB_SLOT_SIGMAS sigma, rounded up to a multiple of 8
-    int mean = kTile / nb, s = 1;
-    while (s * s < mean) s++;
-    return (mean + KDB_SLOT_SIGMAS * s + 7) & ~7;
-}
+// pos = atomicAdd(&cnt[b], 1) is the slot, so there is no scan and no second pass over the letters.
+// Which bits make the bucket: min(fwd, rc) is decided by the first letters of the two strands, so both ends of a canonical id
+// are skewed (the top NBITS bits 2:0 over the range, the lowest ones with a std of 0.58 of the mean); from bit 6 to bit
+// 2K - NBITS - 6 the bucket loads of uniform sequence are flat (max / mean <= 1.05, measured for k = 9..12).  The bucket is id
+// bits [kBucketShift, kBucketShift + NBITS), the payload the bits above and below it squeezed together (slotted_id puts them
+// back), so one slot count fits every bucket and the slot address is b * C + pos with C an immediate: C = 32768 / NB - 4, nearly twice
+// the load of a tile of dense text (+4.9 sigma at 512 buckets).
+// A bucket that gets more than C keys in one unit (low-complexity sequence) is not slotted at all in that unit: a second sweep
+// (only run when some bucket overflowed) sends every key of such a bucket to the global table directly (warp-aggregated REDs),
+// so the result is exact for any input and the common case carries no per-key overflow bookkeeping.
+// Runs leave padded to 4 entries with 0xFFFF (no bin: k3p_count skips it) as aligned 8-byte stores; the slots are 0xFFFF
+// whenever a sweep begins (filled at kernel start, restored by the copy-out), so the padding costs nothing.
+// (C / 2 = -2 mod 32: the bucket bases spread over 16 banks.  With C = 64 every bucket starts in bank 0 and, since all buckets
+// fill at the same rate, the stores of a warp pile onto the bank of the current fill level: 105 M conflicts per 324 MB instead of 48 M.)
+__host__ __device__ constexpr int slot_count(int nb) { return 32768 / nb - 4; }
 __host__ inline size_t k3s_smem_bytes(int k) {
     const int nb = 1 << (2 * k - payload_bits(k));
     return (size_t)(2 * nb + 32) * sizeof(uint32_t) + (size_t)nb * slot_count(nb) * sizeof(uint16_t);
@@ -360,15 +366,19 @@ template <int K, bool CANON>
 __global__ void __launch_bounds__(kPartThreads, 3) k3s_partition(const PartParams P) {
     constexpr int PB = payload_bits(K) <= 16 ? payload_bits(K) : 16;   // (instantiated, never launched, for k = 14)
     constexpr int NBITS = 2 * K - PB, NB = 1 << NBITS;
-    constexpr int C = slot_count(NB);
+    constexpr int C = slot_count(NB), Q = C / 4;
+    constexpr int S = 32 - 2 * K;                                   // the id sits in the top 2K bits of a window word
     constexpr uint32_t mask = (1u << (2 * K)) - 1u;
     extern __shared__ uint32_t s_dyn_part[];                        // NB counters, 32 dummies, NB global bases, NB * C 16-bit slots
     uint32_t* const s_cnt = s_dyn_part;
     uint32_t* const s_gb = s_dyn_part + NB + 32;
     uint16_t* const s_slot = reinterpret_cast<uint16_t*>(s_gb + NB);
+    unsigned long long* const slot64 = reinterpret_cast<unsigned long long*>(s_slot);
     __shared__ unsigned long long s_red[kPartThreads / 32];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     unsigned long long kmers = 0;
+    for (int i = tid; i < NB * Q; i += kPartThreads) slot64[i] = ~0ull;
+    if (tid < 32) s_cnt[NB + tid] = 0x80000000u;                    // per-lane dummy counters: never below C, so what they return never "fits"
 
     const unsigned int n_units = (P.n_tiles + 1) / 2;               // work unit = two packed tiles (see k3p_partition)
     for (unsigned int unit = blockIdx.x; unit < n_units; unit += gridDim.x) {
@@ -424,56 +434,59 @@ __global__ void __launch_bounds__(kPartThreads, 3) k3s_partition(const PartParam
             return m;
         };
         uint32_t* const dummy = s_cnt + NB + lane;                     // a letter without a window bumps a per-lane dummy (no branch)
-        uint32_t ovf = 0;
         if (wb) {
 #pragma unroll
             for (int e = 0; e < 32; e++) {
                 const bool valid = (wb & (0x80000000u >> e)) != 0;
                 const uint32_t m = window_top(e);
-                uint32_t b = (m >> (32 - 2 * K)) & (uint32_t)(NB - 1);
+                uint32_t b = (m >> (S + kBucketShift)) & (uint32_t)(NB - 1);
                 asm volatile("" : "+r"(b));                              // (keeps the id arithmetic out of a branch the compiler would build for the select)
                 const uint32_t pos = atomicAdd(valid ? s_cnt + b : dummy, 1u);
-                const bool fits = valid && pos < (uint32_t)C;
-                if (fits) s_slot[b * C + pos] = (uint16_t)(m >> (32 - PB));
-                if (valid && !fits) ovf |= 0x80000000u >> e;
+                const uint32_t pay = ((m >> (S + NBITS)) & ~((1u << kBucketShift) - 1u)) | ((m >> S) & ((1u << kBucketShift) - 1u));
+                if (pos < (uint32_t)C) s_slot[b * C + pos] = (uint16_t)pay;
             }
             kmers += __popc(wb);
         }
-        if (ovf) {                                                     // bucket full: these keys go straight to the table
-            const unsigned long long S0 = ((unsigned long long)prev << 32) | cur0, S1 = ((unsigned long long)cur0 << 32) | cur1;
-            while (ovf) {
-                const int e = __clz(ovf);
-                ovf &= ~(0x80000000u >> e);
-                const uint32_t f = (uint32_t)((e < 16 ? S0 : S1) >> (30 - 2 * (e & 15))) & mask;
-                uint32_t id = f;
-                if (CANON) { const uint32_t r = revcomp32(f, K); id = r < f ? r : f; }
-                red_aggregated(P.tab32, id);
-            }
-        }
         __syncthreads();
 
-        // ---- one global cursor bump per non-empty bucket ---------------------------------------------------
+        // ---- one global cursor bump per non-empty bucket: runs are padded to 4 entries so that they leave as 8-byte stores ----
+        bool over = false;
         for (int b = tid; b < NB; b += kPartThreads) {
-            const uint32_t c = min(s_cnt[b], (uint32_t)C);
-            uint32_t gb = 0xFFFFFFFFu;
-            if (c) {
-                const uint32_t g = atomicAdd(P.cursor + b, c);
-                if (g + c > P.cap) atomicMin(P.fail_base + b, g);       // does not fit: RED path below
-                else gb = (uint32_t)b * P.cap + g;                      // (host keeps n_buckets * cap < 2^32)
+            const uint32_t c = s_cnt[b], c4 = (c + 3u) & ~3u;
+            uint32_t gb = 0xFFFFFFFFu;                                  // nothing to copy: empty, overflowed (second sweep), or no room in the stream
+            if (c > (uint32_t)C) over = true;
+            else if (c) {
+                const uint32_t g = atomicAdd(P.cursor + b, c4);
+                if (g + c4 > P.cap) { atomicMin(P.fail_base + b, g); over = true; s_cnt[b] = C + 1; }   // no room: treat like an overflow
+                else gb = ((uint32_t)b * P.cap + g) >> 2;               // (host keeps n_buckets * cap < 2^32; cap is a multiple of 8)
             }
             s_gb[b] = gb;
         }
-        __syncthreads();
+        const int any_over = __syncthreads_or(over);
 
-        // ---- the slots leave as payload runs ------------------------------------------------------------------
+        // ---- the slots leave as payload runs, four entries per thread, and are reset to 0xFFFF ------------------------------
 #pragma unroll 4
-        for (uint32_t j = tid; j < (uint32_t)(NB * C); j += kPartThreads) {
-            const uint32_t b = j / (uint32_t)C, r = j - b * (uint32_t)C;
-            if (r < s_cnt[b]) {
+        for (int i = 0; i < NB * Q / kPartThreads; i++) {
+            const uint32_t j = (uint32_t)tid + (uint32_t)i * kPartThreads, b = j / (uint32_t)Q, r = 4u * (j % (uint32_t)Q);
+            const uint32_t c = s_cnt[b];
+            if (r < c) {
+                const unsigned long long v = slot64[j];
+                slot64[j] = ~0ull;
                 const uint32_t gb = s_gb[b];
-                const uint32_t p = s_slot[j];
-                if (gb != 0xFFFFFFFFu) P.stream[gb + r] = (uint16_t)p;
-                else red_aggregated(P.tab32, (p << NBITS) | b);         // stream of this bucket is full (low-complexity input)
+                if (gb != 0xFFFFFFFFu) reinterpret_cast<unsigned long long*>(P.stream)[gb + (r >> 2)] = v;
+            }
+        }
+        if (any_over) {
+            // ---- second sweep (rare): every key of an overflowed bucket goes straight to the table ---------------------------
+            if (wb) {
+                const unsigned long long S0 = ((unsigned long long)prev << 32) | cur0, S1 = ((unsigned long long)cur0 << 32) | cur1;
+                for (int e = 0; e < 32; e++) {
+                    if (!(wb & (0x80000000u >> e))) continue;
+                    const uint32_t f = (uint32_t)((e < 16 ? S0 : S1) >> (30 - 2 * (e & 15))) & mask;
+                    uint32_t id = f;
+                    if (CANON) { const uint32_t r = revcomp32(f, K); id = r < f ? r : f; }
+                    if (s_cnt[(id >> kBucketShift) & (uint32_t)(NB - 1)] > (uint32_t)C) red_aggregated(P.tab32, id);
+                }
             }
         }
       }

@@ -25,7 +25,10 @@ def _unordered_u64(i):
 def combine_partials(part16, dist, device, dst=0):
     """Combine the 16-word scalar packs of all ranks.  Returns the combined pack on dst, None elsewhere.
     One collective (all_gather of 128 bytes per rank) and one copy each way; the words are then folded on the host:
-    sums wrap like the device's uint64 arithmetic, min / max are taken on the unsigned values."""
+    sums wrap like the device's uint64 arithmetic, min / max are taken on the unsigned values.
+    A rank's first-raise key is (record index inside ITS shard) * 4 + priority; ranks hold consecutive shards of the
+    file, so the key is rebased by the number of records of the ranks before it: the minimum is then the first
+    failing record in FILE order, which is the one the reference raises on (kmerdb/parse.py:128 walks the file once)."""
     import torch
     p = np.ascontiguousarray(part16, dtype=np.uint64)
     mine = torch.from_numpy(p.view(np.int64).copy()).to(device)
@@ -35,8 +38,18 @@ def combine_partials(part16, dist, device, dst=0):
     if dist.get_rank() != dst:
         return None
     g = allp.cpu().numpy().view(np.uint64).reshape(world, 16)
-    out = np.zeros(16, dtype=np.uint64)
+    return fold_partials(g)
+
+
+def fold_partials(g):
+    """g: uint64[world, 16], row r = the pack of rank r (shard r of the file).  Host arithmetic of combine_partials."""
+    g = np.array(g, dtype=np.uint64, copy=True)
+    none = np.uint64(0xFFFFFFFFFFFFFFFF)
     with np.errstate(over="ignore"):
+        base = np.concatenate([[np.uint64(0)], np.cumsum(g[:-1, 0], dtype=np.uint64)])      # records before each shard
+        hit = g[:, 10] != none
+        g[hit, 10] = g[hit, 10] + base[hit] * np.uint64(4)
+        out = np.zeros(16, dtype=np.uint64)
         out[SUM_WORDS] = g[:, SUM_WORDS].sum(axis=0, dtype=np.uint64)
     out[list(MIN_WORDS)] = g[:, list(MIN_WORDS)].min(axis=0)
     out[list(MAX_WORDS)] = g[:, list(MAX_WORDS)].max(axis=0)
@@ -57,11 +70,23 @@ def shard_bounds(data, fmt, world):
     n = a.size
     cuts = [0]
     if fmt == "fastq":
-        lf = np.flatnonzero(a == 10)
-        n_rec = (lf.size + (1 if n and a[-1] != 10 else 0)) // 4
+        # line feeds are counted block by block (no index array of every line feed: 8 B per line of a 31 GB input);
+        # only the block that holds a cut is indexed
+        blk = 1 << 26
+        starts = list(range(0, n, blk))
+        per = [int(np.count_nonzero(a[s:s + blk] == 10)) for s in starts]
+        n_lf = sum(per)
+        n_rec = (n_lf + (1 if n and a[-1] != 10 else 0)) // 4
+        cum = np.concatenate([[0], np.cumsum(per)])
         for r in range(1, world):
             rec = (n_rec * r) // world
-            cuts.append(int(lf[4 * rec - 1]) + 1 if rec > 0 else 0)
+            if rec == 0:
+                cuts.append(0)
+                continue
+            want = 4 * rec - 1                                   # index of the line feed that ends record rec - 1
+            b = int(np.searchsorted(cum, want, side="right")) - 1
+            lf = np.flatnonzero(a[starts[b]:starts[b] + blk] == 10)
+            cuts.append(starts[b] + int(lf[want - int(cum[b])]) + 1)
     else:
         for r in range(1, world):
             t = (n * r) // world
@@ -80,16 +105,25 @@ class CudaArray:
         self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
 
 
-def reduce_profiler(prof, dist, device, dst=0, _cache={}):
+_TABLE_VIEWS = {}
+
+
+def _table_view(prof, device):
+    """torch view of the context's device table.  Keyed by what the view IS (pointer, bins, device), never by the
+    Python object: a closed Profiler's address can be reused by a new one whose table lives elsewhere."""
+    import torch
+    ptr, nb = prof.device_table()
+    key = (int(ptr), int(nb), str(device))
+    if key not in _TABLE_VIEWS:
+        _TABLE_VIEWS.clear()
+        _TABLE_VIEWS[key] = torch.as_tensor(CudaArray(ptr, nb), device=device)
+    return _TABLE_VIEWS[key]
+
+
+def reduce_profiler(prof, dist, device, dst=0):
     """After prof.finish() on every rank: NCCL sum-reduce of the partial tables and scalars to `dst`, then
     the non-additive reductions (unique, nullomers) are recomputed there (kdb_refinalize)."""
-    import torch
-    key = id(prof)
-    if key not in _cache:
-        ptr, nb = prof.device_table()
-        _cache.clear()
-        _cache[key] = torch.as_tensor(CudaArray(ptr, nb), device=device)
-    reduce_table(_cache[key], dist, dst)
+    reduce_table(_table_view(prof, device), dist, dst)
     out = combine_partials(prof.export_partials(), dist, device, dst)
     if out is not None:
         prof.import_partials(out)

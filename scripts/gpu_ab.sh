@@ -3,11 +3,11 @@
 # usage: gpurun --timeout 1200 -- 'bash scripts/gpu_ab.sh TAG "" "KDB_TWO_SWEEP=1"'
 TAG=$1; shift
 O=gpurun_out; mkdir -p $O
-python -m pytest tests -m gpu -x -q > $O/pytest_$TAG.log 2>&1; echo "pytest exit $?" >> $O/pytest_$TAG.log
+timeout 900 python -m pytest tests -m gpu -x -q --timeout 240 > $O/pytest_$TAG.log 2>&1; echo "pytest exit $?" >> $O/pytest_$TAG.log
 tail -4 $O/pytest_$TAG.log
 i=0
 for V in "$@"; do
-  env $V python bench.py --steps 10 --warmup 3 --no-cpu-baseline > $O/bench_${TAG}_$i.json 2> $O/bench_${TAG}_$i.err; echo "bench[$V] exit $?"
+  env $V timeout 300 python bench.py --steps 10 --warmup 3 --no-cpu-baseline > $O/bench_${TAG}_$i.json 2> $O/bench_${TAG}_$i.err; echo "bench[$V] exit $?"
   python - <<PY
 import json
 d=json.load(open('$O/bench_${TAG}_$i.json'))

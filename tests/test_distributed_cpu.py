@@ -95,3 +95,29 @@ def test_order_preserving_map_roundtrip():
     u = np.array([0, 1, 2 ** 63 - 1, 2 ** 63, NONE], dtype=np.uint64)
     i = kd._ordered_i64(u)
     assert np.all(np.diff(i) > 0) and np.array_equal(kd._unordered_u64(i), u)
+
+
+def test_first_raise_is_taken_in_file_order():
+    """a rank's first-raise key counts records inside its own shard.  Shard 1 raising at its record 2 must
+    not beat shard 0 raising at its record 40: the reference meets shard 0's record first (kmerdb/parse.py:128)."""
+    g = np.zeros((3, 16), dtype=np.uint64)
+    g[:, 0] = [100, 50, 70]                       # records per shard
+    g[:, 8] = NONE
+    g[:, 10] = [40 * 4 + 2, 2 * 4 + 0, NONE]      # shard 0: KeyError at its record 40; shard 1: NameError at its record 2
+    out = kd.fold_partials(g)
+    assert int(out[10]) == 40 * 4 + 2 and int(out[0]) == 220
+    g[0, 10] = NONE
+    out = kd.fold_partials(g)
+    assert int(out[10]) == (100 + 2) * 4 + 0      # rebased by the 100 records of shard 0
+    g[1, 10] = NONE
+    assert int(kd.fold_partials(g)[10]) == NONE
+
+
+def test_fastq_shard_bounds_blockwise_equals_full_index(monkeypatch):
+    rng = np.random.default_rng(3)
+    text = "".join("@q%d\n%s\n+\n%s\n" % (i, "A" * int(rng.integers(1, 90)), "I" * 5) for i in range(997)).encode()
+    a = np.frombuffer(text, dtype=np.uint8)
+    lf = np.flatnonzero(a == 10)
+    for world in (2, 3, 8):
+        want = [0] + [int(lf[4 * ((997 * r) // world) - 1]) + 1 for r in range(1, world)] + [len(text)]
+        assert kd.shard_bounds(text, "fastq", world) == want

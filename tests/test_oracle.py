@@ -117,3 +117,13 @@ def test_fixture_B3_B4_cdifficile():
     assert st["mono"] == [1444649, 601738, 590294, 1456466]
     rc, counts, st = oracle.profile(raw, 12, canonical=False, threads=4)   # kmerdb/appmap.py:271-306
     assert (st["total_kmers"], st["unique_kmers"], 4 ** 12 - st["unique_kmers"]) == (4093136, 2267911, 14509305)
+
+
+def test_numpy_synth_equals_the_product_generator():
+    """oracle/synth.py (NumPy Philox-4x32-10, used by bench.py's CPU legs so that the reference arm never loads the
+    product library) against kdb_synth_host (the host twin of the k_synth kernel), byte for byte."""
+    from kmerdb_b200 import _native
+    from oracle import synth
+    assert synth.fasta(0, 700) == bytes(_native.synth_host(700))
+    assert synth.fasta(5_000_000_123, 5) == bytes(_native.synth_host(5, first_read=5_000_000_123))
+    assert synth.fasta(3, 4, read_len=70, seed=99) == bytes(_native.synth_host(4, 70, seed=99, first_read=3))
