@@ -186,7 +186,7 @@ def run_reference(args):
     base["value"] = value
     base["sample"] = "first %d of the synthetic %d bp reads (FASTA, seed %d) per step; %s" % (n_reads, READ_LEN, SEED, base["sample"])
     cfg = workload_config(args, args.gpus)
-    cfg["timed_sample"] = "%d reads (%d bases) per step: a bounded prefix of the workload, not the %d reads of the GPU arm" % (n_reads, n_reads * READ_LEN, args.reads)
+    cfg["timed_sample"] = "%d reads (%d bases) per step: a bounded prefix of the workload, not the %d reads of the GPU arm" % (n_reads, n_reads * READ_LEN, cfg["reads_total"])
     line = {"impl": "reference", "metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": 1e3 * dt / args.steps, "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "u64", "data": "synthetic", "config": cfg, "cpu_baseline": base,
@@ -197,10 +197,15 @@ def run_reference(args):
 
 
 def workload_config(args, n_gpus):
-    return {"workload": "profile k=%d canonical, %d synthetic %d bp reads per GPU, FASTA framing 162 B/record" % (args.k, args.reads, READ_LEN),
-            "k": args.k, "reads_per_gpu": args.reads, "read_len": READ_LEN, "canonical": True, "format": "fasta", "seed": SEED,
-            "l2": "input (%.2f GB per GPU) is larger than L2; no flush needed" % (args.reads * 162 / 1e9),
-            "parallelism": "reads sharded over %d GPU(s); partial 4^k tables sum-reduced to rank 0 with NCCL" % n_gpus if n_gpus > 1 else "1 GPU"}
+    total = getattr(args, "reads_total", None) or args.reads or (10_000_000 if n_gpus == 1 else 100_000_000)
+    per = getattr(args, "reads_per_gpu", None) or total // n_gpus
+    name = "configs[1]" if n_gpus == 1 else "configs[2]"
+    return {"workload": "%s: profile k=%d canonical, %d synthetic %d bp reads%s, FASTA framing 162 B/record"
+                        % (name, args.k, total, READ_LEN, "" if n_gpus == 1 else " sharded over %d GPUs" % n_gpus),
+            "k": args.k, "reads_total": total, "reads_per_gpu": per, "read_len": READ_LEN, "canonical": True, "format": "fasta", "seed": SEED,
+            "l2": "input (%.2f GB per GPU) is larger than L2; no flush needed" % (per * 162 / 1e9),
+            "parallelism": ("reads sharded over %d GPUs (rank r = shard r); partial 4^k tables summed by kdb_reduce_nccl "
+                            "(reduce-scatter + per-slice finalize + slices to rank 0)" % n_gpus) if n_gpus > 1 else "1 GPU"}
 
 
 def run_b200(args):
@@ -222,12 +227,18 @@ def run_b200(args):
     if world > 1:
         dist.init_process_group("nccl", device_id=torch.device("cuda", local))
 
-    k, n_reads = args.k, args.reads
+    k = args.k
+    # N = 1: configs[1] (10 M reads).  N > 1: configs[2] as written — 100 M reads sharded N ways (rank r holds reads
+    # [r * R / N, (r + 1) * R / N) of the same stream), one reduce of the 4^12 tables per step.
+    total_reads = args.reads if args.reads else (10_000_000 if world == 1 else 100_000_000)
+    first_read = total_reads * rank // world
+    n_reads = total_reads * (rank + 1) // world - first_read
+    args.reads_total, args.reads_per_gpu = total_reads, n_reads
     rb = _native.synth_record_bytes(READ_LEN)
     nbytes = n_reads * rb
     n_bases = n_reads * READ_LEN
     dev_text = _native.DeviceBuffer(nbytes + 16, device=local)
-    _native.synth_device(dev_text, n_reads, READ_LEN, seed=SEED, first_read=rank * n_reads)
+    _native.synth_device(dev_text, n_reads, READ_LEN, seed=SEED, first_read=first_read)
     prof = _native.Profiler(k, canonical=True, skip_n=True, fastq=False, device=local)
 
     def barrier():
@@ -236,12 +247,12 @@ def run_b200(args):
         torch.cuda.synchronize()
 
     def reduce_to_rank0():
-        """NCCL sum-reduce of the 4^k uint64 partials and of the scalar pack to rank 0, then the non-additive
-        reductions (unique, nullomers) are recomputed there (kmerdb_b200/distributed.py)."""
+        """kdb_reduce_nccl (kmerdb_b200/csrc/kdb_multi.cuh): reduce-scatter of the 4^k uint64 partials, per-slice non-zero
+        count, one all-gather of the scalar packs folded on the device, slices sent to rank 0 — all queued on the context's
+        stream, nothing read back here."""
         if world == 1:
             return
         kd.reduce_profiler(prof, dist, torch.device("cuda", local), dst=0)
-        torch.cuda.synchronize()
 
     def step_device():
         prof.reset()
@@ -261,18 +272,19 @@ def run_b200(args):
     ev0, ev1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
     t0 = time.perf_counter()
     ev0.record()
-    job_ms = count_ms = scan_ms = fold_ms = final_ms = encode_ms = part_ms = 0.0
+    job_ms = count_ms = scan_ms = fold_ms = final_ms = encode_ms = part_ms = reduce_ms = 0.0
     count_launches = launches = 0
     for _ in range(args.steps):
         t = step_device()
-        job_ms += t["job_ms"]; count_ms += t["count_ms"]; part_ms += t["partition_ms"]; encode_ms += t["encode_ms"]; scan_ms += t["scan_ms"]; fold_ms += t["fold_ms"]; final_ms += t["final_ms"]
+        reduce_ms += t["reduce_ms"]; job_ms += t["job_ms"] + t["reduce_ms"]; count_ms += t["count_ms"]; part_ms += t["partition_ms"]; encode_ms += t["encode_ms"]; scan_ms += t["scan_ms"]; fold_ms += t["fold_ms"]; final_ms += t["final_ms"]
         count_launches += t["count_launches"]; launches += t["total_launches"]
     ev1.record()
     barrier()
     wall = time.perf_counter() - t0
     clocks = sampler.stop() if rank == 0 else None
-    # every call of the C-ABI is synchronous, so the wall clock between the two barriers is the device
-    # time of the K steps plus launch gaps; job_ms is the CUDA-event time on the context's own stream
+    # ONE clock for every N: CUDA events on the context's own stream — job (kdb_reset .. end of kdb_finish) plus, for
+    # N > 1, the reduce (first collective .. rank 0 holds the sum), max over ranks.  The wall clock between the two
+    # barriers (device time plus launch gaps) is reported beside it.
     tt = torch.tensor([wall, job_ms * 1e-3], dtype=torch.float64, device="cuda")
     if world > 1:
         dist.all_reduce(tt, op=dist.ReduceOp.MAX)
@@ -310,8 +322,33 @@ def run_b200(args):
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_wall = te.item()
 
+    # ---- parity gate T3, driver-visible: the N-GPU result equals a 1-GPU job over the same reads -----------------
+    t3 = None
+    if world > 1:
+        import hashlib
+        prof.reset()
+        prof.feed_device(dev_text.ptr, nbytes)
+        assert prof.finish() == 0
+        reduce_to_rank0()
+        multi_stats = prof.stats()
+        if rank == 0:
+            multi_sha = hashlib.sha256(prof.counts(out=counts_view).tobytes()).hexdigest()
+            chunk_reads = 12_500_000                                     # regenerate the whole stream on this GPU, piece by piece
+            one = _native.Profiler(k, canonical=True, skip_n=True, fastq=False, device=local)
+            buf = _native.DeviceBuffer(chunk_reads * rb + 16, device=local)
+            for r0 in range(0, total_reads, chunk_reads):
+                m = min(chunk_reads, total_reads - r0)
+                _native.synth_device(buf, m, READ_LEN, seed=SEED, first_read=r0)
+                one.feed_device(buf.ptr, m * rb)                         # (fragments at record boundaries)
+            assert one.finish() == 0
+            one_stats = one.stats()
+            one_sha = hashlib.sha256(one.counts(out=counts_view).tobytes()).hexdigest()
+            one.close()
+            t3 = {"t3_identical": bool(one_sha == multi_sha and one_stats == multi_stats), "counts_sha256_n_gpu": multi_sha,
+                  "counts_sha256_1_gpu": one_sha, "stats_equal": bool(one_stats == multi_stats)}
+            stats = multi_stats
     if rank == 0:
-        assert stats["total_kmers"] == world * n_reads * (READ_LEN - k + 1), stats
+        assert stats["total_kmers"] == total_reads * (READ_LEN - k + 1), stats
         assert st_host["total_kmers"] == stats["total_kmers"] and int(counts_view.sum()) == stats["total_kmers"]
         peak, peak_src = peaks()
         # dominant kernel of the step: k3p_partition (ids + tile-local bucket sort + stream write), one launch per pass
@@ -331,31 +368,37 @@ def run_b200(args):
             gbs = nbytes * args.steps / (ms * 1e-3) / 1e9 if ms > 0 else None
             per_kernel[name] = {"ms_per_step": ms / args.steps, "GBps_of_text": gbs, "frac_of_hbm_peak": gbs / peak if gbs else None}
         line = {
-            "metric": METRIC, "value": world * n_bases * args.steps / job_max if world == 1 else world * n_bases * args.steps / wall_max,
+            "metric": METRIC, "value": total_reads * READ_LEN * args.steps / job_max,
             "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
-            "ms_per_step": 1e3 * (job_max if world == 1 else wall_max) / args.steps, "higher_is_better": True, "scaling": "weak",
+            "ms_per_step": 1e3 * job_max / args.steps, "higher_is_better": True, "scaling": "weak" if world == 1 else "strong",
             "vs_baseline": None, "dtype": "u32", "data": "synthetic", "config": workload_config(args, world),
             "wall_ms_per_step": 1e3 * wall_max / args.steps,
-            "e2e": {"value": world * n_bases * e2e_steps / e2e_wall, "unit": UNIT, "h2d_bytes_per_step": nbytes,
+            "e2e": {"value": total_reads * READ_LEN * e2e_steps / e2e_wall, "unit": UNIT, "h2d_bytes_per_step": nbytes,
                     "d2h_bytes_per_step": 8 * 4 ** k + 112, "steps": e2e_steps},
             "gpu_launches": int(launches),
             "roofline": {"bound": "hbm", "kernel": "k3p_partition", "achieved": achieved, "peak": peak, "unit": "GB/s", "frac": achieved / peak,
                          "traffic": traffic, "peak_source": peak_src,
                          "algorithmic_bytes_per_base": rb / READ_LEN, "bytes_per_launch": per_launch_bytes,
                          "avg_launch_ms": 1e3 * avg_launch_s,
-                         "whole_job_frac": (nbytes * args.steps / (job_max if world == 1 else wall_max) / 1e9) / peak,
+                         "whole_job_frac": (nbytes * args.steps / job_max / 1e9) / peak,
                          "kernels": per_kernel,
                          "note": "the count path is bound by shared-memory bank wavefronts and instruction issue, not HBM: see DESIGN.md section 4 and profiles/"},
-            "kernel_ms_per_step": {"scan": scan_ms / args.steps, "partition": part_ms / args.steps, "count": count_ms / args.steps, "fold": fold_ms / args.steps, "final": final_ms / args.steps, "encode": encode_ms / args.steps},
+            "kernel_ms_per_step": {"scan": scan_ms / args.steps, "partition": part_ms / args.steps, "count": count_ms / args.steps, "fold": fold_ms / args.steps, "final": final_ms / args.steps, "encode": encode_ms / args.steps, "reduce": reduce_ms / args.steps},
             "clocks": clocks,
             "result_check": {"total_kmers": stats["total_kmers"], "unique_kmers": stats["unique_kmers"], "total_reads": stats["total_reads"]},
         }
+        if t3 is not None:
+            line["result_check"].update(t3)
         if not args.no_cpu_baseline:
             line.update(cpu_legs(k, args.ref_reads, args.cpu_reads))
         _emit(line)
     if world > 1:
+        ok = torch.tensor([0 if (t3 is not None and not t3["t3_identical"]) else 1], device="cuda")
+        dist.broadcast(ok, 0)
         dist.barrier()
         dist.destroy_process_group()
+        if not ok.item():
+            raise SystemExit("T3 failed: the %d-GPU count vector / statistics differ from the 1-GPU job" % world)
 
 
 _JSON_OUT = None
@@ -379,7 +422,7 @@ def main():
     ap.add_argument("--steps", type=int, default=20)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="b200", choices=["b200", "reference"])
-    ap.add_argument("--reads", type=int, default=10_000_000, help="reads per GPU (configs[1]: 10M x 150 bp)")
+    ap.add_argument("--reads", type=int, default=0, help="total reads of the job (default: 10 M at N = 1 = configs[1], 100 M sharded N ways at N > 1 = configs[2])")
     ap.add_argument("--k", type=int, default=12)
     ap.add_argument("--cpu-reads", type=int, default=2_000_000, help="bounded sample for the C-port CPU leg")
     ap.add_argument("--ref-reads", type=int, default=2_000, help="bounded sample (reads per step) for the Python reference")

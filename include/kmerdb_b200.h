@@ -63,7 +63,7 @@ typedef struct {
 
 /* Device timing of the passes run so far (CUDA events on the context's stream). */
 typedef struct {
-    float scan_ms;    /* K1: line/record boundary scan (tile summaries + carry scan)        */
+    float scan_ms;    /* pass set-up (zeroing the look-back status words); the old K1 scan when KDB_TWO_PASS is set */
     float encode_ms;  /* K2: tokenise + 2-bit encode into the packed letter stream           */
     float count_ms;   /* K3: rolling id + histogram (the dominant kernel)                    */
     float partition_ms; /* part of count_ms: first kernel of K3 (the whole of it when k is not partitioned) */
@@ -71,6 +71,8 @@ typedef struct {
     float final_ms;   /* record-length check, unique/nullomer reductions                     */
     float h2d_ms;     /* host -> device staging                                              */
     float job_ms;     /* kdb_reset/kdb_create (table zeroing) .. end of kdb_finish, one event pair    */
+    float reduce_ms;  /* kdb_reduce_nccl / kdb_reduce_peers: first collective .. root holds the sum   */
+    float pad_;
     uint64_t count_launches; /* number of count-kernel launches                              */
     uint64_t total_launches; /* all kernel launches issued by this context                   */
     uint64_t bytes_fed;
@@ -103,6 +105,19 @@ int kdb_nullomers(kdb_ctx* ctx, uint64_t* out_ids, size_t cap, size_t* n);
  * additive scalar pack, for the caller's collective (torch.distributed / NCCL sum-reduce), and
  * a call that recomputes the non-additive reductions (unique, nullomers) after the reduce. */
 int kdb_device_table(kdb_ctx* ctx, void** dev_counts_u64, size_t* n_bins);
+/* The reduce itself behind the C-ABI.  Reference: the cross-file sum of kmerdb/__init__.py:1888-1891 and the
+ * header statistics re-derived from the summed vector (:1901-1903).
+ * kdb_reduce_nccl: one process per GPU; rank r holds shard r of the input (file order) in a finished context.
+ *   kdb_nccl_unique_id fills `out` (cap >= 128 bytes) on one rank; the caller hands the bytes to every rank (any channel).
+ *   The call is a collective: ncclReduceScatter of the uint64[4^k] tables, non-zero count of the own slice, one
+ *   ncclAllGather of the 16-word scalar packs folded on the device (sums, min / max, first raise in FILE order), slices
+ *   sent to rank 0.  It queues everything on the context's stream and returns; afterwards rank 0 holds the summed table
+ *   (kdb_counts / kdb_nullomers there), every rank the combined kdb_stats.  4^k must be a multiple of nranks.
+ * kdb_reduce_peers: one process, one finished context per GPU with peer access, ctxs[0] the root: a single kernel per GPU
+ *   reads its slice of every table over NVLink, adds, counts and stores into the root's table. */
+int kdb_nccl_unique_id(void* out, size_t cap);
+int kdb_reduce_nccl(kdb_ctx* ctx, const void* unique_id, int rank, int nranks);
+int kdb_reduce_peers(kdb_ctx** ctxs, int n);
 int kdb_export_partials(kdb_ctx* ctx, uint64_t* out16); /* [reads,kmers,sum_len,mono0..3,nwin_n,min,max,err_key,...] */
 int kdb_import_partials(kdb_ctx* ctx, const uint64_t* in16);
 int kdb_refinalize(kdb_ctx* ctx);

@@ -18,7 +18,7 @@ EXPORTS = [
     "kdb_counts", "kdb_nullomers", "kdb_device_table", "kdb_export_partials", "kdb_import_partials", "kdb_refinalize",
     "kdb_reset", "kdb_timing", "kdb_kmer_to_id_batch", "kdb_synth_record_bytes", "kdb_synth_device",
     "kdb_synth_host", "kdb_microbench_atomics", "kdb_dev_alloc", "kdb_dev_free", "kdb_host_alloc_pinned",
-    "kdb_host_free_pinned", "kdb_memcpy_h2d", "kdb_memcpy_d2h",
+    "kdb_host_free_pinned", "kdb_memcpy_h2d", "kdb_memcpy_d2h", "kdb_nccl_unique_id", "kdb_reduce_nccl", "kdb_reduce_peers",
     "kdb_edge_rows", "kdb_edge_weights", "kdb_minimizers_compat", "kdb_minimizers", "kdb_attach", "kdb_format_rows", "kdb_minimizers_batch",
     "kdb_reader_create", "kdb_reader_feed", "kdb_reader_finish", "kdb_reader_destroy", "kdb_correlation_matrix",
 ]
@@ -33,7 +33,8 @@ class Stats(ctypes.Structure):
 
 class Timing(ctypes.Structure):
     _fields_ = [("scan_ms", ctypes.c_float), ("encode_ms", ctypes.c_float), ("count_ms", ctypes.c_float), ("partition_ms", ctypes.c_float), ("fold_ms", ctypes.c_float),
-                ("final_ms", ctypes.c_float), ("h2d_ms", ctypes.c_float), ("job_ms", ctypes.c_float), ("count_launches", ctypes.c_uint64),
+                ("final_ms", ctypes.c_float), ("h2d_ms", ctypes.c_float), ("job_ms", ctypes.c_float), ("reduce_ms", ctypes.c_float), ("pad_", ctypes.c_float),
+                ("count_launches", ctypes.c_uint64),
                 ("total_launches", ctypes.c_uint64), ("bytes_fed", ctypes.c_uint64)]
 
 
@@ -69,6 +70,7 @@ def lib():
         ("kdb_attach", [vp, vp]),
         ("kdb_format_rows", [ci, vp, u64, u64, vp, vp, vp, sz, vp, sz, ctypes.POINTER(sz)]), ("kdb_reset", [vp]), ("kdb_timing", [vp, ctypes.POINTER(Timing)]),
         ("kdb_kmer_to_id_batch", [ci, ctypes.c_char_p, sz, ci, ci, vp]),
+        ("kdb_nccl_unique_id", [vp, sz]), ("kdb_reduce_nccl", [vp, vp, ci, ci]), ("kdb_reduce_peers", [vp, ci]),
         ("kdb_synth_device", [ci, vp, u64, u64, ci, ci, u64]), ("kdb_synth_host", [vp, u64, u64, ci, ci, u64]),
         ("kdb_microbench_atomics", [ci, sz, u64, ci, ctypes.POINTER(ctypes.c_double)]),
         ("kdb_dev_alloc", [ci, sz, ctypes.POINTER(vp)]), ("kdb_dev_free", [ci, vp]),
@@ -190,6 +192,11 @@ class Profiler:
     def attach(self, follower):
         """Multi-k sweep: `follower` (a Profiler with a larger k) counts from this context's packed stream."""
         self._check(lib().kdb_attach(self._ctx, follower._ctx), "kdb_attach")
+
+    def reduce_nccl(self, unique_id, rank, nranks):
+        """Collective (kdb_reduce_nccl): sum of the shard profiles; rank 0 ends up with the whole table."""
+        buf = ctypes.create_string_buffer(bytes(unique_id), 128)
+        return self._check(lib().kdb_reduce_nccl(self._ctx, buf, rank, nranks), "kdb_reduce_nccl")
 
     def refinalize(self):
         return self._check(lib().kdb_refinalize(self._ctx), "kdb_refinalize")
@@ -441,3 +448,17 @@ def correlation_matrix(profiles, mode=0, device=0):
     if lib().kdb_correlation_matrix(int(device), x.ctypes.data, x.shape[0], x.shape[1], int(mode), out.ctypes.data):
         raise NativeError("kdb_correlation_matrix: " + _err())
     return out
+
+
+def nccl_unique_id():
+    """128 bytes for kdb_reduce_nccl; made on one rank, handed to the others by the caller."""
+    buf = ctypes.create_string_buffer(128)
+    if lib().kdb_nccl_unique_id(buf, 128):
+        raise NativeError("kdb_nccl_unique_id: " + _err())
+    return buf.raw
+
+
+def reduce_peers(profilers):
+    """One process, one finished Profiler per GPU (shard order): profilers[0] ends up with the whole table (kdb_reduce_peers)."""
+    arr = (ctypes.c_void_p * len(profilers))(*[p._ctx for p in profilers])
+    return profilers[0]._check(lib().kdb_reduce_peers(arr, len(profilers)), "kdb_reduce_peers")

@@ -44,7 +44,7 @@ def _profile(args, k, files, precomputed=None):
         else:
             # the per-file metadata arrives as a callable: md5 / sha256 of a large file finish seconds after its counts
             c, meta, _nullomers = parse.parsefile_deferred(f, k, replace_with_none=args.no_ambiguous, canonicalize=not args.do_not_canonicalize,
-                                                           device=args.device)
+                                                           device=getattr(args, "devices", None) or args.device)
         counts = counts + c                                        # __init__.py:1890
         file_metadata.append(meta)
     total = int(np.sum(counts))
@@ -157,6 +157,9 @@ def build_parser():
     p.add_argument("--no-ambiguous", action="store_true")
     p.add_argument("--do-not-canonicalize", action="store_true")
     p.add_argument("--sorted", action="store_true", default=False)
+    p.add_argument("--devices", type=str, default=None,
+                   help="several CUDA devices, e.g. 0-7 or 0,2,4 (kmerdb_b200 extension): the reads of each file are sharded over them, "
+                        "the partial tables are summed over NVLink into the first one; the .kdb is byte-identical to the one-GPU file")
     p.add_argument("input", nargs="+", type=str)
     p.set_defaults(func=profile)
 

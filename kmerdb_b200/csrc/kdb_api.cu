@@ -22,6 +22,7 @@
 #include "kdb_rows.cuh"
 #include "kdb_read.cuh"
 #include "kdb_corr.cuh"
+#include "kdb_multi.cuh"
 
 using namespace kdb;
 
@@ -72,6 +73,14 @@ struct kdb_ctx {
     PassCarry* pcarry = nullptr;                // two copies: a pass reads [pc_idx], writes [pc_idx ^ 1]
     int pc_idx = 0;
     uint8_t* zero_row = nullptr;                // 64 zero bytes: tensor map base for a pass shorter than one row
+    // multi-GPU (kdb_reduce_nccl / kdb_reduce_peers)
+    ncclComm_t comm = nullptr;
+    int comm_rank = -1, comm_n = 0;
+    unsigned long long* d_pack = nullptr;       // 16 words of this rank + 16 per rank gathered
+    cudaEvent_t ev_red0 = nullptr, ev_red1 = nullptr;
+    bool stats_dirty = false;                   // the device scalars changed after kdb_finish (a reduce): kdb_stats re-reads them
+    bool reduce_timed = false;
+    bool not_root = false;                      // after a reduce only the root holds the whole table
     void* null_scratch = nullptr;               // kdb_nullomers: per-block zero counts and offsets
     size_t null_cap = 0;
     // host mirrors
@@ -174,7 +183,10 @@ extern "C" void kdb_destroy(kdb_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaFree(ctx->tab32); cudaFree(ctx->tab64); cudaFree(ctx->acc); cudaFree(ctx->carry); cudaFree(ctx->carry_len);
     cudaFree(ctx->tile_sum); /* tile_state lives inside the tile_sum allocation */ cudaFree(ctx->rec_len); cudaFree(ctx->feed_buf); cudaFree(ctx->packed); cudaFree(ctx->stream); cudaFree(ctx->cursor);
-    cudaFree(ctx->look); /* trec lives inside the look allocation */ cudaFree(ctx->ticket); cudaFree(ctx->pcarry); cudaFree(ctx->zero_row); cudaFree(ctx->null_scratch);
+    cudaFree(ctx->look); /* trec lives inside the look allocation */ cudaFree(ctx->ticket); cudaFree(ctx->pcarry); cudaFree(ctx->zero_row); cudaFree(ctx->null_scratch); cudaFree(ctx->d_pack);
+    if (ctx->comm && nccl_api().ok) nccl_api().CommDestroy(ctx->comm);
+    if (ctx->ev_red0) cudaEventDestroy(ctx->ev_red0);
+    if (ctx->ev_red1) cudaEventDestroy(ctx->ev_red1);
     for (auto& e : ctx->ev) if (e) cudaEventDestroy(e);
     for (auto& e : ctx->ev_copy) cudaEventDestroy(e);
     if (ctx->ev_job0) cudaEventDestroy(ctx->ev_job0);
@@ -200,6 +212,7 @@ static int reset_state(kdb_ctx* ctx) {
     ctx->have_carry = false; ctx->carry_rec_id = 0; ctx->fq_rec_base = 0; ctx->bytes_since_fold = 0;
     ctx->job_started = true; ctx->finished = false; ctx->host_layout = false; ctx->tab64_valid = false;
     ctx->stats = kdb_stats_t{}; ctx->timing = kdb_timing_t{};
+    ctx->stats_dirty = false; ctx->reduce_timed = false; ctx->not_root = false;
     return KDB_OK;
 }
 
@@ -707,6 +720,11 @@ extern "C" int kdb_finish(kdb_ctx* ctx) {
 extern "C" int kdb_stats(kdb_ctx* ctx, kdb_stats_t* out) {
     if (!ctx || !out) return KDB_E_ARG;
     if (!ctx->finished) { ctx->err = "kdb_stats before kdb_finish"; return KDB_E_STATE; }
+    if (ctx->stats_dirty) {                      // a multi-GPU reduce rewrote the device scalars: read them once, here
+        if (int rc = set_device(ctx, ctx->device)) return rc;
+        if (int rc = fill_stats(ctx)) return rc;
+        ctx->stats_dirty = false;
+    }
     *out = ctx->stats;
     return KDB_OK;
 }
@@ -714,6 +732,7 @@ extern "C" int kdb_stats(kdb_ctx* ctx, kdb_stats_t* out) {
 extern "C" int kdb_counts(kdb_ctx* ctx, uint64_t* out) {
     if (!ctx || !out) return KDB_E_ARG;
     if (!ctx->finished) { ctx->err = "kdb_counts before kdb_finish"; return KDB_E_STATE; }
+    if (ctx->not_root) { ctx->err = "kdb_counts on a non-root rank after kdb_reduce_nccl: only the root holds the whole table"; return KDB_E_STATE; }
     if (int rc = set_device(ctx, ctx->device)) return rc;
     CK(cudaMemcpyAsync(out, ctx->tab64, ctx->nbins * sizeof(uint64_t), cudaMemcpyDeviceToHost, ctx->s_compute));
     CK(cudaStreamSynchronize(ctx->s_compute));
@@ -755,6 +774,13 @@ extern "C" int kdb_nullomers(kdb_ctx* ctx, uint64_t* out_ids, size_t cap, size_t
 
 extern "C" int kdb_timing(kdb_ctx* ctx, kdb_timing_t* out) {
     if (!ctx || !out) return KDB_E_ARG;
+    if (ctx->reduce_timed) {
+        float ms = 0;
+        CK(cudaEventSynchronize(ctx->ev_red1));
+        CK(cudaEventElapsedTime(&ms, ctx->ev_red0, ctx->ev_red1));
+        ctx->timing.reduce_ms += ms;
+        ctx->reduce_timed = false;
+    }
     *out = ctx->timing;
     return KDB_OK;
 }
@@ -819,6 +845,168 @@ extern "C" int kdb_refinalize(kdb_ctx* ctx) {
     if (int rc = set_device(ctx, ctx->device)) return rc;
     CK(cudaDeviceSynchronize());   // the caller's collective ran on another stream
     if (int rc = compute_unique(ctx)) return rc;
+    if (int rc = fill_stats(ctx)) return rc;
+    return ctx->stats.status;
+}
+
+// ---- multi-GPU behind the C-ABI (kdb_reduce_nccl) -----------------------------------------------------------
+#define NCK(call)                                                                                  \
+    do {                                                                                           \
+        ncclResult_t r_ = (call);                                                                  \
+        if (r_ != ncclSuccess) {                                                                   \
+            char b_[512];                                                                          \
+            snprintf(b_, sizeof b_, "%s failed at %s:%d: %s", #call, __FILE__, __LINE__, nccl_api().GetErrorString(r_)); \
+            if (ctx) ctx->err = b_;                                                                \
+            g_last_error = b_;                                                                     \
+            return KDB_E_CUDA;                                                                     \
+        }                                                                                          \
+    } while (0)
+
+extern "C" int kdb_nccl_unique_id(void* out, size_t cap) {
+    kdb_ctx* ctx = nullptr;
+    if (!out || cap < sizeof(ncclUniqueId)) return KDB_E_ARG;
+    if (!nccl_api().ok) { g_last_error = "NCCL is not available: " + nccl_api().why; return KDB_E_STATE; }
+    ncclUniqueId id;
+    NCK(nccl_api().GetUniqueId(&id));
+    memcpy(out, &id, sizeof id);
+    return KDB_OK;
+}
+
+// Collective over the `nranks` contexts that hold the shards of one input, in shard order (rank r = shard r).  After it
+// rank 0 holds the summed table and every rank the combined statistics.  Everything is queued on the context's stream:
+// the call returns without waiting for the device.
+extern "C" int kdb_reduce_nccl(kdb_ctx* ctx, const void* unique_id, int rank, int nranks) {
+    if (!ctx || !unique_id || nranks < 1 || rank < 0 || rank >= nranks) return KDB_E_ARG;
+    if (!ctx->finished) { ctx->err = "kdb_reduce_nccl before kdb_finish"; return KDB_E_STATE; }
+    if (ctx->leader && !ctx->leader->finished) { ctx->err = "kdb_reduce_nccl on a follower before its leader finished"; return KDB_E_STATE; }
+    if (int rc = set_device(ctx, ctx->device)) return rc;
+    if (nranks == 1) return KDB_OK;
+    NcclApi& N = nccl_api();
+    if (!N.ok) { ctx->err = "NCCL is not available: " + N.why; return KDB_E_STATE; }
+    if (ctx->nbins % (unsigned long long)nranks) { ctx->err = "kdb_reduce_nccl: 4^k must be a multiple of the number of ranks"; return KDB_E_ARG; }
+    if (ctx->comm && (ctx->comm_rank != rank || ctx->comm_n != nranks)) { N.CommDestroy(ctx->comm); ctx->comm = nullptr; }
+    if (!ctx->comm) {
+        ncclUniqueId id;
+        memcpy(&id, unique_id, sizeof id);
+        NCK(N.CommInitRank(&ctx->comm, nranks, id, rank));
+        ctx->comm_rank = rank; ctx->comm_n = nranks;
+    }
+    if (!ctx->d_pack) CK(cudaMalloc(&ctx->d_pack, 16 * (1 + kMaxPeers * 8) * sizeof(unsigned long long)));
+    if (nranks > kMaxPeers * 8) { ctx->err = "kdb_reduce_nccl: too many ranks"; return KDB_E_ARG; }
+    if (!ctx->ev_red0) { CK(cudaEventCreate(&ctx->ev_red0)); CK(cudaEventCreate(&ctx->ev_red1)); }
+    cudaStream_t st = ctx->s_compute;
+    // (a follower's per-record scalars are its leader's: take them from there)
+    kdb_ctx* rec = ctx->leader ? ctx->leader : ctx;
+    const unsigned long long slice = ctx->nbins / (unsigned long long)nranks;
+    unsigned long long* mine = ctx->tab64 + (unsigned long long)rank * slice;
+    CK(cudaEventRecord(ctx->ev_red0, st));
+    NCK(N.ReduceScatter(ctx->tab64, mine, (size_t)slice, ncclUint64, ncclSum, ctx->comm, st));
+    CK(cudaMemsetAsync(&ctx->acc->unique, 0, sizeof(unsigned long long), st));
+    {
+        const int grid = (int)std::min<unsigned long long>((slice + 255) / 256, 148ull * 8);
+        k_count_nonzero_range<<<grid, 256, 0, st>>>(ctx->tab64, (unsigned long long)rank * slice, (unsigned long long)(rank + 1) * slice, ctx->acc);
+        CK(cudaGetLastError());
+    }
+    if (rec != ctx) {
+        // follower: per-record words from the leader's device scalars, k-mer count and unique from its own
+        k_make_pack<<<1, 32, 0, st>>>(rec->acc, rec->pcarry + rec->pc_idx, ctx->fastq, rec->host_layout, ctx->d_pack);
+        CK(cudaGetLastError());
+        CK(cudaMemcpyAsync(ctx->d_pack + 1, &ctx->acc->total_kmers, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st));
+        CK(cudaMemcpyAsync(ctx->d_pack + 12, &ctx->acc->unique, sizeof(unsigned long long), cudaMemcpyDeviceToDevice, st));
+    } else {
+        k_make_pack<<<1, 32, 0, st>>>(ctx->acc, ctx->pcarry + ctx->pc_idx, ctx->fastq, ctx->host_layout, ctx->d_pack);
+        CK(cudaGetLastError());
+    }
+    NCK(N.AllGather(ctx->d_pack, ctx->d_pack + 16, 16, ncclUint64, ctx->comm, st));
+    k_fold_packs<<<1, 32, 0, st>>>(ctx->d_pack + 16, nranks, ctx->acc, ctx->pcarry + ctx->pc_idx, ctx->fastq);
+    CK(cudaGetLastError());
+    // the summed slices travel to the root
+    NCK(N.GroupStart());
+    if (rank == 0) { for (int r = 1; r < nranks; r++) NCK(N.Recv(ctx->tab64 + (unsigned long long)r * slice, (size_t)slice, ncclUint64, r, ctx->comm, st)); }
+    else NCK(N.Send(mine, (size_t)slice, ncclUint64, 0, ctx->comm, st));
+    NCK(N.GroupEnd());
+    CK(cudaEventRecord(ctx->ev_red1, st));
+    ctx->timing.total_launches += 3;
+    ctx->host_layout = false;                    // (folded into the device flag by k_make_pack / k_fold_packs)
+    ctx->stats_dirty = true; ctx->reduce_timed = true; ctx->not_root = rank != 0;
+    return KDB_OK;
+}
+
+// One process, one context per GPU (shard order), peer access: see kdb_multi.cuh.  ctxs[0] is the root.
+extern "C" int kdb_reduce_peers(kdb_ctx** ctxs, int n) {
+    kdb_ctx* ctx = (ctxs && n > 0) ? ctxs[0] : nullptr;
+    if (!ctx || n > kMaxPeers) return KDB_E_ARG;
+    for (int r = 0; r < n; r++) {
+        if (!ctxs[r] || !ctxs[r]->finished) { ctx->err = "kdb_reduce_peers before kdb_finish on every context"; return KDB_E_STATE; }
+        if (ctxs[r]->k != ctx->k || (ctxs[r]->flags & 7) != (ctx->flags & 7) || ctxs[r]->leader) { ctx->err = "kdb_reduce_peers: contexts must agree in k and flags"; return KDB_E_ARG; }
+        for (int q = 0; q < r; q++) if (ctxs[q]->device == ctxs[r]->device) { ctx->err = "kdb_reduce_peers: one context per device"; return KDB_E_ARG; }
+    }
+    if (n == 1) return KDB_OK;
+    if (ctx->nbins % (unsigned long long)(2 * n)) { ctx->err = "kdb_reduce_peers: 4^k must be a multiple of twice the number of GPUs"; return KDB_E_ARG; }
+    for (int r = 0; r < n; r++) {
+        CK(cudaSetDevice(ctxs[r]->device));
+        for (int q = 0; q < n; q++) {
+            if (q == r) continue;
+            int can = 0;
+            CK(cudaDeviceCanAccessPeer(&can, ctxs[r]->device, ctxs[q]->device));
+            if (!can) { ctx->err = "kdb_reduce_peers: no peer access between the devices"; return KDB_E_STATE; }
+            cudaError_t e = cudaDeviceEnablePeerAccess(ctxs[q]->device, 0);
+            if (e != cudaSuccess && e != cudaErrorPeerAccessAlreadyEnabled) CK(e);
+            cudaGetLastError();
+        }
+    }
+    // every GPU's table is complete once its stream reaches this point
+    for (int r = 0; r < n; r++) {
+        CK(cudaSetDevice(ctxs[r]->device));
+        if (!ctxs[r]->ev_red0) { CK(cudaEventCreate(&ctxs[r]->ev_red0)); CK(cudaEventCreate(&ctxs[r]->ev_red1)); }
+        CK(cudaEventRecord(ctxs[r]->ev_red0, ctxs[r]->s_compute));
+    }
+    PeerTables T{};
+    for (int r = 0; r < n; r++) T.tab[r] = ctxs[r]->tab64;
+    const unsigned long long slice = ctx->nbins / (unsigned long long)n;
+    for (int r = 0; r < n; r++) {
+        kdb_ctx* c = ctxs[r];
+        CK(cudaSetDevice(c->device));
+        for (int q = 0; q < n; q++) if (q != r) CK(cudaStreamWaitEvent(c->s_compute, ctxs[q]->ev_red0, 0));
+        CK(cudaMemsetAsync(&c->acc->unique, 0, sizeof(unsigned long long), c->s_compute));
+        const int grid = (int)std::min<unsigned long long>((slice / 2 + 255) / 256, 148ull * 8);
+        k_peer_reduce_slice<<<grid, 256, 0, c->s_compute>>>(T, n, ctx->tab64, (unsigned long long)r * slice, (unsigned long long)(r + 1) * slice, &c->acc->unique);
+        CK(cudaGetLastError());
+        CK(cudaEventRecord(c->ev_red1, c->s_compute));
+        c->timing.total_launches++;
+    }
+    // scalars: a few words per GPU, folded on the host exactly like k_fold_packs (this is the end of the job)
+    Accum a{};
+    a.min_len = ~0ull; a.err_key = ~0ull;
+    unsigned long long reads = 0;
+    for (int r = 0; r < n; r++) {
+        kdb_ctx* c = ctxs[r];
+        CK(cudaSetDevice(c->device));
+        CK(cudaStreamSynchronize(c->s_compute));
+        Accum p; PassCarry pc;
+        CK(cudaMemcpy(&p, c->acc, sizeof p, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(&pc, c->pcarry + c->pc_idx, sizeof pc, cudaMemcpyDeviceToHost));
+        const unsigned long long rd = c->fastq ? pc.fq_rec_base : pc.hdr_total;
+        unsigned long long ek = p.err_key;
+        if (ek != ~0ull) ek += reads * 4;
+        reads += rd;
+        a.total_kmers += p.total_kmers; a.sum_len += p.sum_len;
+        for (int i = 0; i < 4; i++) a.mono[i] += p.mono[i];
+        a.n_windows_with_n += p.n_windows_with_n;
+        a.min_len = std::min(a.min_len, p.min_len); a.max_len = std::max(a.max_len, p.max_len); a.err_key = std::min(a.err_key, ek);
+        a.layout_flag |= (p.layout_flag || c->host_layout) ? 1u : 0u;
+        a.unique += p.unique;
+        if (r) c->not_root = true;
+    }
+    CK(cudaSetDevice(ctx->device));
+    CK(cudaMemcpy(ctx->acc, &a, sizeof a, cudaMemcpyHostToDevice));
+    PassCarry pc{};
+    if (ctx->fastq) pc.fq_rec_base = reads; else pc.hdr_total = reads;
+    CK(cudaMemcpy(ctx->pcarry + ctx->pc_idx, &pc, sizeof pc, cudaMemcpyHostToDevice));
+    ctx->host_layout = false;
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, ctx->ev_red0, ctx->ev_red1));
+    ctx->timing.reduce_ms += ms;
     if (int rc = fill_stats(ctx)) return rc;
     return ctx->stats.status;
 }

@@ -467,6 +467,15 @@ __global__ void __launch_bounds__(kThreads, 4) k2s_encode(const EncodeParams2 P,
         if (tid == 0) s_seed = seed;
         TailAgg2 tile_total;
         TailAgg2 start = tail2_scan_exclusive<FASTQ>(tail, s_tail, &tile_total);      // (syncs: s_seed is visible after it)
+        // ---- stage: thread 0 takes the next ticket and starts its TMA load into the other buffer (the barrier of the tail
+        // scan is behind us: nobody reads text any more in this iteration).  The ticket is taken LATE — one copy-out before the tile is worked on, not a whole tile earlier: a
+        // ticket holder publishes its aggregate a few microseconds after taking the ticket, so a tile rarely finds a predecessor
+        // that has not published yet (with the ticket taken a tile ahead, 42 % of the kernel's samples sat in that wait). -----------
+        if (tid == 0) {
+            const unsigned int nxt = atomicAdd(P.ticket, 1u);
+            s_next[(it + 1) & 1] = nxt;
+            if (nxt < P.n_tiles) stage(nxt, buf ^ 1);
+        }
         const uint32_t off = start.letters, tile_letters = tile_total.letters;
         if (seen_b) {
             // my first record start closes the record that was open when my chunk began
@@ -500,15 +509,6 @@ __global__ void __launch_bounds__(kThreads, 4) k2s_encode(const EncodeParams2 P,
             or_bits<2>(s_out + kPackCodes + kPackBits, off, z, E.n);
         }
         __syncthreads();
-        // ---- stage: thread 0 takes the next ticket and starts its TMA load into the other buffer (nobody reads text any more in
-        // this iteration).  The ticket is taken LATE — one copy-out before the tile is worked on, not a whole tile earlier: a
-        // ticket holder publishes its aggregate a few microseconds after taking the ticket, so a tile rarely finds a predecessor
-        // that has not published yet (with the ticket taken a tile ahead, 42 % of the kernel's samples sat in that wait). -----------
-        if (tid == 0) {
-            const unsigned int nxt = atomicAdd(P.ticket, 1u);
-            s_next[(it + 1) & 1] = nxt;
-            if (nxt < P.n_tiles) stage(nxt, buf ^ 1);
-        }
         // ---- write the packed region: only the words the letters of this tile occupy ------------
         {
             uint32_t* dst = P.packed + (size_t)tile * kPackStride;
@@ -529,7 +529,6 @@ __global__ void __launch_bounds__(kThreads, 4) k2s_encode(const EncodeParams2 P,
                 dst[kPackHdr + kPackCodes + kPackBits + i] = s_out[kPackCodes + kPackBits + i]; s_out[kPackCodes + kPackBits + i] = 0;
             }
         }
-        __syncthreads();                                        // (s_next; also: s_out is clear before the next tile ORs into it)
         tile = s_next[(it + 1) & 1];
     }
 

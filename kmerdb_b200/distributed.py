@@ -105,25 +105,34 @@ class CudaArray:
         self.__cuda_array_interface__ = {"shape": (n,), "typestr": typestr, "data": (ptr, False), "version": 2}
 
 
-_TABLE_VIEWS = {}
-
-
-def _table_view(prof, device):
-    """torch view of the context's device table.  Keyed by what the view IS (pointer, bins, device), never by the
-    Python object: a closed Profiler's address can be reused by a new one whose table lives elsewhere."""
+def share_unique_id(dist, device):
+    """128 bytes of NCCL unique id made on rank 0 (kdb_nccl_unique_id) and broadcast over the caller's process group —
+    torch.distributed is only the messenger; the collective itself runs inside the library (kdb_reduce_nccl)."""
     import torch
-    ptr, nb = prof.device_table()
-    key = (int(ptr), int(nb), str(device))
-    if key not in _TABLE_VIEWS:
-        _TABLE_VIEWS.clear()
-        _TABLE_VIEWS[key] = torch.as_tensor(CudaArray(ptr, nb), device=device)
-    return _TABLE_VIEWS[key]
+    from . import _native
+    t = torch.zeros(128, dtype=torch.uint8, device=device)
+    if dist.get_rank() == 0:
+        t.copy_(torch.frombuffer(bytearray(_native.nccl_unique_id()), dtype=torch.uint8))
+    dist.broadcast(t, src=0)
+    return bytes(t.cpu().numpy().tobytes())
 
 
 def reduce_profiler(prof, dist, device, dst=0):
-    """After prof.finish() on every rank: NCCL sum-reduce of the partial tables and scalars to `dst`, then
-    the non-additive reductions (unique, nullomers) are recomputed there (kdb_refinalize)."""
-    reduce_table(_table_view(prof, device), dist, dst)
+    """After prof.finish() on every rank (rank r = shard r of the input): kdb_reduce_nccl — reduce-scatter of the partial
+    tables, per-slice non-zero count, one all-gather of the scalar packs folded on the device, slices sent to rank 0.
+    Nothing comes back to the host here; prof.stats() / prof.counts() (rank 0) read the result when asked."""
+    assert dst == 0, "kdb_reduce_nccl gathers on rank 0"
+    if getattr(prof, "_nccl_uid", None) is None:        # one communicator per context, kept by the library after the first call
+        prof._nccl_uid = share_unique_id(dist, device)
+    return prof.reduce_nccl(prof._nccl_uid, dist.get_rank(), dist.get_world_size())
+
+
+def reduce_profiler_torch(prof, dist, device, dst=0):
+    """The r01 path, kept for comparison: torch.distributed.reduce on the device table + host-folded scalar packs +
+    kdb_refinalize (a second pass over the whole table)."""
+    import torch
+    ptr, nb = prof.device_table()
+    reduce_table(torch.as_tensor(CudaArray(ptr, nb), device=device), dist, dst)
     out = combine_partials(prof.export_partials(), dist, device, dst)
     if out is not None:
         prof.import_partials(out)

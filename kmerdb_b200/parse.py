@@ -300,8 +300,61 @@ class Profile:
         }
 
 
+def _device_list(device):
+    """int | "0-3" | "0,2,5" | sequence of ints -> list of device indices."""
+    if isinstance(device, (list, tuple)):
+        return [int(d) for d in device]
+    if isinstance(device, str):
+        out = []
+        for part in device.split(","):
+            if "-" in part:
+                a, b = part.split("-")
+                out.extend(range(int(a), int(b) + 1))
+            elif part.strip():
+                out.append(int(part))
+        return out
+    return [int(device)]
+
+
+def _profile_bytes_multi(data, k, fmt, replace_with_none, canonicalize, devices, want_nullomers):
+    """One process, several GPUs (the reference's cross-file sum, kmerdb/__init__.py:1888-1891, applied to the shards of one
+    file): the text is cut at record boundaries (distributed.shard_bounds), shard r is profiled on devices[r] by its own
+    host thread (the ctypes calls release the GIL: the host->device copies and kernels of the GPUs overlap), then
+    kdb_reduce_peers sums the tables over NVLink into devices[0] in one kernel per GPU.  Returns None when the device
+    tokeniser wants the host layout (the caller then takes the single-GPU path)."""
+    from concurrent.futures import ThreadPoolExecutor
+    from . import distributed as kd
+    a = data if isinstance(data, np.ndarray) else np.frombuffer(data, dtype=np.uint8)
+    cuts = kd.shard_bounds(a, fmt, len(devices))
+    kw = dict(canonical=canonicalize, skip_n=replace_with_none, fastq=(fmt == "fastq"))
+    profs = [_native.Profiler(k, device=d, **kw) for d in devices]
+    try:
+        def work(r):
+            profs[r].feed(a[cuts[r]:cuts[r + 1]])
+            return profs[r].finish()
+        with ThreadPoolExecutor(max_workers=len(devices)) as ex:
+            statuses = list(ex.map(work, range(len(devices))))
+        if any(s == _native.KDB_E_LAYOUT for s in statuses):
+            return None
+        status = _native.reduce_peers(profs)
+        root = profs[0]
+        st = root.stats()
+        _raise_for_status(status, st)
+        return Profile(k, root.counts(), st, root.nullomers() if want_nullomers else None, root.timing())
+    finally:
+        for p in profs:
+            p.close()
+
+
 def profile_bytes(data, k, fmt="fasta", replace_with_none=True, canonicalize=True, device=0, want_nullomers=True):
-    """Profile uncompressed FASTA/FASTQ text held in host memory.  Raises the reference's exceptions."""
+    """Profile uncompressed FASTA/FASTQ text held in host memory.  Raises the reference's exceptions.
+    `device`: one device index, or several ("0-7", [0, 1, 2, 3]): the reads are sharded over them."""
+    devices = _device_list(device)
+    if len(devices) > 1:
+        prof = _profile_bytes_multi(data, k, fmt, replace_with_none, canonicalize, devices, want_nullomers)
+        if prof is not None:
+            return prof
+    device = devices[0]
     with _native.Profiler(k, canonical=canonicalize, skip_n=replace_with_none, fastq=(fmt == "fastq"), device=device) as p:
         p.feed(data)
         status = p.finish()
