@@ -72,7 +72,7 @@ typedef struct {
     float h2d_ms;     /* host -> device staging                                              */
     float job_ms;     /* kdb_reset/kdb_create (table zeroing) .. end of kdb_finish, one event pair    */
     float reduce_ms;  /* kdb_reduce_nccl / kdb_reduce_peers: first collective .. root holds the sum   */
-    float pad_;
+    float inflate_ms; /* kdb_feed_bgzf_host: DEFLATE of the BGZF members on the device                */
     uint64_t count_launches; /* number of count-kernel launches                              */
     uint64_t total_launches; /* all kernel launches issued by this context                   */
     uint64_t bytes_fed;
@@ -91,6 +91,20 @@ const char* kdb_last_error(const kdb_ctx* ctx);
  * already in this device's HBM (read-only, no copy is made). */
 int kdb_feed_host(kdb_ctx* ctx, const uint8_t* bytes, size_t n);
 int kdb_feed_device(kdb_ctx* ctx, const uint8_t* dev_bytes, size_t n);
+
+/* Compressed input (the reference opens every input through gzip.open, kmerdb/parse.py:63-68).  BGZF
+ * (bgzip / Bio.bgzf: independent gzip members of <= 64 KiB of text, size in the 'BC' extra subfield) is inflated ON THE
+ * DEVICE, one warp per member, so the compressed bytes are what crosses PCIe.
+ * kdb_bgzf_index: host walk of the member headers (RFC 1952 subfields); KDB_E_FORMAT when `raw` is not BGZF.
+ * kdb_inflate_bgzf: the text of a BGZF buffer (host -> device -> inflate -> host), for tests and tools; with host_out == NULL
+ *   it only reports the text size.  Every member is checked against its ISIZE and CRC-32.
+ * kdb_feed_bgzf_host: kdb_feed_host for a whole BGZF file: compressed H2D in pieces, inflate as they arrive, then the text
+ *   is tokenised and counted in place.  KDB_E_FORMAT: not BGZF / corrupt member (use the host's gzip, which raises what the
+ *   reference raises). */
+typedef struct { uint64_t in_off, out_off; uint32_t in_len, out_len, crc, pad_; } kdb_bgzf_member_t;
+int kdb_bgzf_index(const uint8_t* raw, size_t n, kdb_bgzf_member_t* members, size_t cap, size_t* n_members, uint64_t* text_bytes);
+int kdb_inflate_bgzf(int device, const uint8_t* raw, size_t n, uint8_t* host_out, size_t out_cap, size_t* out_len);
+int kdb_feed_bgzf_host(kdb_ctx* ctx, const uint8_t* raw, size_t n);
 
 /* Replaces kmerdb/parse.py:139-146: folds partial tables, computes the reductions.  After this
  * call kdb_stats/kdb_counts/kdb_nullomers are valid.  Returns stats.status. */

@@ -19,6 +19,7 @@ EXPORTS = [
     "kdb_reset", "kdb_timing", "kdb_kmer_to_id_batch", "kdb_synth_record_bytes", "kdb_synth_device",
     "kdb_synth_host", "kdb_microbench_atomics", "kdb_dev_alloc", "kdb_dev_free", "kdb_host_alloc_pinned",
     "kdb_host_free_pinned", "kdb_memcpy_h2d", "kdb_memcpy_d2h", "kdb_nccl_unique_id", "kdb_reduce_nccl", "kdb_reduce_peers",
+    "kdb_bgzf_index", "kdb_inflate_bgzf", "kdb_feed_bgzf_host",
     "kdb_edge_rows", "kdb_edge_weights", "kdb_minimizers_compat", "kdb_minimizers", "kdb_attach", "kdb_format_rows", "kdb_minimizers_batch",
     "kdb_reader_create", "kdb_reader_feed", "kdb_reader_finish", "kdb_reader_destroy", "kdb_correlation_matrix",
 ]
@@ -33,7 +34,7 @@ class Stats(ctypes.Structure):
 
 class Timing(ctypes.Structure):
     _fields_ = [("scan_ms", ctypes.c_float), ("encode_ms", ctypes.c_float), ("count_ms", ctypes.c_float), ("partition_ms", ctypes.c_float), ("fold_ms", ctypes.c_float),
-                ("final_ms", ctypes.c_float), ("h2d_ms", ctypes.c_float), ("job_ms", ctypes.c_float), ("reduce_ms", ctypes.c_float), ("pad_", ctypes.c_float),
+                ("final_ms", ctypes.c_float), ("h2d_ms", ctypes.c_float), ("job_ms", ctypes.c_float), ("reduce_ms", ctypes.c_float), ("inflate_ms", ctypes.c_float),
                 ("count_launches", ctypes.c_uint64),
                 ("total_launches", ctypes.c_uint64), ("bytes_fed", ctypes.c_uint64)]
 
@@ -70,6 +71,8 @@ def lib():
         ("kdb_attach", [vp, vp]),
         ("kdb_format_rows", [ci, vp, u64, u64, vp, vp, vp, sz, vp, sz, ctypes.POINTER(sz)]), ("kdb_reset", [vp]), ("kdb_timing", [vp, ctypes.POINTER(Timing)]),
         ("kdb_kmer_to_id_batch", [ci, ctypes.c_char_p, sz, ci, ci, vp]),
+        ("kdb_bgzf_index", [vp, sz, vp, sz, ctypes.POINTER(sz), ctypes.POINTER(u64)]), ("kdb_inflate_bgzf", [ci, vp, sz, vp, sz, ctypes.POINTER(sz)]),
+        ("kdb_feed_bgzf_host", [vp, vp, sz]),
         ("kdb_nccl_unique_id", [vp, sz]), ("kdb_reduce_nccl", [vp, vp, ci, ci]), ("kdb_reduce_peers", [vp, ci]),
         ("kdb_synth_device", [ci, vp, u64, u64, ci, ci, u64]), ("kdb_synth_host", [vp, u64, u64, ci, ci, u64]),
         ("kdb_microbench_atomics", [ci, sz, u64, ci, ctypes.POINTER(ctypes.c_double)]),
@@ -192,6 +195,13 @@ class Profiler:
     def attach(self, follower):
         """Multi-k sweep: `follower` (a Profiler with a larger k) counts from this context's packed stream."""
         self._check(lib().kdb_attach(self._ctx, follower._ctx), "kdb_attach")
+
+    def feed_bgzf(self, raw):
+        """raw: a whole BGZF file (bytes-like, host memory).  Returns KDB_OK, or KDB_E_FORMAT when it is not BGZF / a member
+        is corrupt (nothing was counted then)."""
+        a = raw if isinstance(raw, np.ndarray) else np.frombuffer(raw, dtype=np.uint8)
+        a = np.ascontiguousarray(a, dtype=np.uint8)
+        return self._check(lib().kdb_feed_bgzf_host(self._ctx, a.ctypes.data, a.size), "kdb_feed_bgzf_host")
 
     def reduce_nccl(self, unique_id, rank, nranks):
         """Collective (kdb_reduce_nccl): sum of the shard profiles; rank 0 ends up with the whole table."""
@@ -462,3 +472,28 @@ def reduce_peers(profilers):
     """One process, one finished Profiler per GPU (shard order): profilers[0] ends up with the whole table (kdb_reduce_peers)."""
     arr = (ctypes.c_void_p * len(profilers))(*[p._ctx for p in profilers])
     return profilers[0]._check(lib().kdb_reduce_peers(arr, len(profilers)), "kdb_reduce_peers")
+
+
+def bgzf_text_size(raw):
+    """Sum of ISIZE over the members of a BGZF buffer, or None when `raw` is not BGZF (host header walk only)."""
+    a = np.frombuffer(raw, dtype=np.uint8)
+    nm, text = ctypes.c_size_t(0), ctypes.c_uint64(0)
+    if lib().kdb_bgzf_index(a.ctypes.data, a.size, None, 0, ctypes.byref(nm), ctypes.byref(text)):
+        return None
+    return int(text.value)
+
+
+def inflate_bgzf(raw, device=0):
+    """The text of a BGZF buffer, inflated on the GPU (every member checked against ISIZE and CRC-32)."""
+    a = np.frombuffer(raw, dtype=np.uint8)
+    n = ctypes.c_size_t(0)
+    rc = lib().kdb_inflate_bgzf(device, a.ctypes.data, a.size, None, 0, ctypes.byref(n))
+    if rc:
+        raise ValueError("not a BGZF file")
+    out = np.empty(n.value, dtype=np.uint8)
+    rc = lib().kdb_inflate_bgzf(device, a.ctypes.data, a.size, out.ctypes.data, out.size, ctypes.byref(n))
+    if rc == KDB_E_FORMAT:
+        raise ValueError("BGZF: " + _err())
+    if rc:
+        raise NativeError("kdb_inflate_bgzf failed (%d): %s" % (rc, _err()))
+    return out

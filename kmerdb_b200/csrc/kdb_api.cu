@@ -23,6 +23,7 @@
 #include "kdb_read.cuh"
 #include "kdb_corr.cuh"
 #include "kdb_multi.cuh"
+#include "kdb_inflate.cuh"
 
 using namespace kdb;
 
@@ -81,6 +82,8 @@ struct kdb_ctx {
     bool stats_dirty = false;                   // the device scalars changed after kdb_finish (a reduce): kdb_stats re-reads them
     bool reduce_timed = false;
     bool not_root = false;                      // after a reduce only the root holds the whole table
+    uint8_t* comp_buf = nullptr;                // kdb_feed_bgzf_host: the compressed bytes, member table, status words
+    size_t comp_cap = 0;
     void* null_scratch = nullptr;               // kdb_nullomers: per-block zero counts and offsets
     size_t null_cap = 0;
     // host mirrors
@@ -183,7 +186,7 @@ extern "C" void kdb_destroy(kdb_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaFree(ctx->tab32); cudaFree(ctx->tab64); cudaFree(ctx->acc); cudaFree(ctx->carry); cudaFree(ctx->carry_len);
     cudaFree(ctx->tile_sum); /* tile_state lives inside the tile_sum allocation */ cudaFree(ctx->rec_len); cudaFree(ctx->feed_buf); cudaFree(ctx->packed); cudaFree(ctx->stream); cudaFree(ctx->cursor);
-    cudaFree(ctx->look); /* trec lives inside the look allocation */ cudaFree(ctx->ticket); cudaFree(ctx->pcarry); cudaFree(ctx->zero_row); cudaFree(ctx->null_scratch); cudaFree(ctx->d_pack);
+    cudaFree(ctx->look); /* trec lives inside the look allocation */ cudaFree(ctx->ticket); cudaFree(ctx->pcarry); cudaFree(ctx->zero_row); cudaFree(ctx->null_scratch); cudaFree(ctx->d_pack); cudaFree(ctx->comp_buf);
     if (ctx->comm && nccl_api().ok) nccl_api().CommDestroy(ctx->comm);
     if (ctx->ev_red0) cudaEventDestroy(ctx->ev_red0);
     if (ctx->ev_red1) cudaEventDestroy(ctx->ev_red1);
@@ -847,6 +850,157 @@ extern "C" int kdb_refinalize(kdb_ctx* ctx) {
     if (int rc = compute_unique(ctx)) return rc;
     if (int rc = fill_stats(ctx)) return rc;
     return ctx->stats.status;
+}
+
+// ---- BGZF input: compressed bytes over PCIe, inflate on the device (kdb_inflate.cuh) ------------------------------------
+static bool g_crc_table_loaded[64] = {false};
+static int load_crc_table(kdb_ctx* ctx, int device) {
+    if (device >= 0 && device < 64 && g_crc_table_loaded[device]) return KDB_OK;
+    unsigned int t[256];
+    for (unsigned int i = 0; i < 256; i++) {
+        unsigned int c = i;
+        for (int b = 0; b < 8; b++) c = (c & 1u) ? 0xEDB88320u ^ (c >> 1) : c >> 1;
+        t[i] = c;
+    }
+    CK(cudaMemcpyToSymbol(c_crc_table, t, sizeof t));
+    if (device >= 0 && device < 64) g_crc_table_loaded[device] = true;
+    return KDB_OK;
+}
+
+// Walk the gzip members of `raw` (RFC 1952): every member must carry the BGZF 'BC' extra subfield (its total size - 1),
+// found by walking the subfields of the extra field, not at a fixed offset.  Fills members[0..min(cap, n)); *n_members gets
+// the count, *text_bytes the sum of ISIZE.  KDB_E_FORMAT when `raw` is not a whole number of BGZF members.
+extern "C" int kdb_bgzf_index(const uint8_t* raw, size_t n, kdb_bgzf_member_t* members, size_t cap, size_t* n_members, uint64_t* text_bytes) {
+    if (!raw || !n_members || !text_bytes) return KDB_E_ARG;
+    size_t off = 0, cnt = 0;
+    uint64_t total = 0;
+    while (off < n) {
+        if (n - off < 18 + 8 || raw[off] != 0x1f || raw[off + 1] != 0x8b || raw[off + 2] != 8 || !(raw[off + 3] & 4)) return KDB_E_FORMAT;
+        const unsigned flg = raw[off + 3];
+        const size_t xlen = raw[off + 10] | (raw[off + 11] << 8);
+        size_t p = off + 12, xend = p + xlen;
+        if (xend > n) return KDB_E_FORMAT;
+        long bsize = -1;
+        while (p + 4 <= xend) {
+            const size_t slen = raw[p + 2] | (raw[p + 3] << 8);
+            if (raw[p] == 'B' && raw[p + 1] == 'C' && slen == 2 && p + 6 <= xend) bsize = (raw[p + 4] | (raw[p + 5] << 8)) + 1;
+            p += 4 + slen;
+        }
+        if (bsize < 0 || off + (size_t)bsize > n) return KDB_E_FORMAT;
+        size_t q = xend;
+        if (flg & 8) { while (q < off + bsize && raw[q]) q++; q++; }          // FNAME
+        if (flg & 16) { while (q < off + bsize && raw[q]) q++; q++; }         // FCOMMENT
+        if (flg & 2) q += 2;                                                  // FHCRC
+        if (q + 8 > off + (size_t)bsize) return KDB_E_FORMAT;
+        const uint8_t* tr = raw + off + bsize - 8;
+        const uint32_t crc = tr[0] | (tr[1] << 8) | (tr[2] << 16) | ((uint32_t)tr[3] << 24);
+        const uint32_t isize = tr[4] | (tr[5] << 8) | (tr[6] << 16) | ((uint32_t)tr[7] << 24);
+        if (isize > 65536) return KDB_E_FORMAT;
+        if (members && cnt < cap) members[cnt] = kdb_bgzf_member_t{(uint64_t)q, total, (uint32_t)(off + bsize - 8 - q), isize, crc, 0};
+        cnt++;
+        total += isize;
+        off += (size_t)bsize;
+    }
+    *n_members = cnt; *text_bytes = total;
+    return KDB_OK;
+}
+
+// comp / out: device buffers (comp readable 8 bytes past comp_len); members: host array.  Returns KDB_OK, or KDB_E_FORMAT
+// when a member does not inflate to its ISIZE / CRC-32 (first_bad receives its index).
+static int inflate_members(kdb_ctx* ctx, int device, const uint8_t* d_comp, const kdb_bgzf_member_t* members, size_t n_members, uint8_t* d_out,
+                           BgzfMember* d_members, unsigned int* d_status, cudaStream_t st, int check_crc) {
+    if (int rc = load_crc_table(ctx, device)) return rc;
+    static_assert(sizeof(kdb_bgzf_member_t) == sizeof(BgzfMember), "member layout");
+    CK(cudaMemcpyAsync(d_members, members, n_members * sizeof(BgzfMember), cudaMemcpyHostToDevice, st));
+    const int grid = (int)std::min<size_t>((n_members + kInfWarps - 1) / kInfWarps, (size_t)148 * 7);
+    k_inflate_bgzf<<<grid, kInfWarps * 32, 0, st>>>(d_comp, d_members, (unsigned int)n_members, d_out, d_status, check_crc);
+    CK(cudaGetLastError());
+    return KDB_OK;
+}
+
+extern "C" int kdb_inflate_bgzf(int device, const uint8_t* raw, size_t n, uint8_t* host_out, size_t out_cap, size_t* out_len) {
+    kdb_ctx* ctx = nullptr;
+    if (!raw || !out_len) return KDB_E_ARG;
+    size_t nm = 0; uint64_t text = 0;
+    if (int rc = kdb_bgzf_index(raw, n, nullptr, 0, &nm, &text)) return rc;
+    *out_len = (size_t)text;
+    if (!host_out) return KDB_OK;
+    if (out_cap < text) return KDB_E_ARG;
+    std::vector<kdb_bgzf_member_t> mem(nm);
+    kdb_bgzf_index(raw, n, mem.data(), nm, &nm, &text);
+    CK(cudaSetDevice(device));
+    DevBuf d_comp, d_out, d_mem, d_st;
+    CK(d_comp.alloc(n + 16)); CK(d_out.alloc(text + 16)); CK(d_mem.alloc(nm * sizeof(BgzfMember))); CK(d_st.alloc(nm * sizeof(unsigned int)));
+    CK(cudaMemcpy(d_comp.p, raw, n, cudaMemcpyHostToDevice));
+    if (int rc = inflate_members(ctx, device, d_comp.as<uint8_t>(), mem.data(), nm, d_out.as<uint8_t>(), d_mem.as<BgzfMember>(), d_st.as<unsigned int>(), nullptr, 1)) return rc;
+    std::vector<unsigned int> status(nm);
+    CK(cudaMemcpy(status.data(), d_st.p, nm * sizeof(unsigned int), cudaMemcpyDeviceToHost));
+    for (size_t i = 0; i < nm; i++) if (status[i]) { char b[128]; snprintf(b, sizeof b, "BGZF member %zu does not inflate (code %u)", i, status[i]); g_last_error = b; return KDB_E_FORMAT; }
+    CK(cudaMemcpy(host_out, d_out.p, text, cudaMemcpyDeviceToHost));
+    return KDB_OK;
+}
+
+// The profile path on compressed input: `raw` = a whole BGZF file in host memory.  The compressed bytes are copied to the device
+// in pieces; each piece is inflated as soon as it has arrived (the copy of piece i+1 overlaps the inflate of piece i), then the
+// text is tokenised and counted like a device feed.  KDB_E_FORMAT: not BGZF, or a member is corrupt (the caller falls back
+// to the host's gzip, which raises what the reference raises).
+extern "C" int kdb_feed_bgzf_host(kdb_ctx* ctx, const uint8_t* raw, size_t n) {
+    if (!ctx || !raw) return KDB_E_ARG;
+    if (int rc = set_device(ctx, ctx->device)) return rc;
+    if (!ctx->single_pass) { ctx->err = "kdb_feed_bgzf_host needs the single-pass tokeniser"; return KDB_E_STATE; }
+    size_t nm = 0; uint64_t text = 0;
+    if (int rc = kdb_bgzf_index(raw, n, nullptr, 0, &nm, &text)) return rc;
+    if (text == 0) return KDB_OK;
+    std::vector<kdb_bgzf_member_t> mem(nm);
+    kdb_bgzf_index(raw, n, mem.data(), nm, &nm, &text);
+    const size_t meta = nm * (sizeof(BgzfMember) + sizeof(unsigned int));
+    if (int rc = ensure(ctx, (void**)&ctx->comp_buf, &ctx->comp_cap, n + 64 + meta + 64, 1)) return rc;
+    if (int rc = ensure(ctx, (void**)&ctx->feed_buf, &ctx->feed_cap, text + 64, 1)) return rc;
+    uint8_t* d_comp = ctx->comp_buf;
+    BgzfMember* d_mem = reinterpret_cast<BgzfMember*>(ctx->comp_buf + ((n + 64 + 15) & ~(size_t)15));
+    unsigned int* d_st = reinterpret_cast<unsigned int*>(d_mem + nm);
+    if (int rc = begin_feed(ctx)) return rc;
+    // pieces of about 32 MiB of compressed bytes, cut at member borders
+    const size_t piece = 32u << 20;
+    std::vector<size_t> cut{0};                                   // member index where each piece starts
+    {
+        size_t start_off = 0;
+        for (size_t i = 0; i < nm; i++) {
+            const size_t member_end = (i + 1 < nm) ? (size_t)mem[i + 1].in_off : n;      // (a piece ends before the header of the next member's payload: close enough)
+            if (member_end - start_off >= piece && i + 1 < nm) { cut.push_back(i + 1); start_off = member_end; }
+        }
+        cut.push_back(nm);
+    }
+    const size_t n_piece = cut.size() - 1;
+    while (ctx->ev_copy.size() < n_piece + 1) { cudaEvent_t e; CK(cudaEventCreate(&e)); ctx->ev_copy.push_back(e); }
+    CK(cudaEventRecord(ctx->ev_copy[n_piece], ctx->s_copy));
+    size_t byte0 = 0;
+    for (size_t pi = 0; pi < n_piece; pi++) {
+        const size_t byte1 = cut[pi + 1] < nm ? (size_t)mem[cut[pi + 1]].in_off : n;
+        CK(cudaMemcpyAsync(d_comp + byte0, raw + byte0, byte1 - byte0, cudaMemcpyHostToDevice, ctx->s_copy));
+        CK(cudaEventRecord(ctx->ev_copy[pi], ctx->s_copy));
+        byte0 = byte1;
+    }
+    CK(cudaEventRecord(ctx->ev[0], ctx->s_compute));
+    for (size_t pi = 0; pi < n_piece; pi++) {
+        CK(cudaStreamWaitEvent(ctx->s_compute, ctx->ev_copy[pi], 0));
+        if (int rc = inflate_members(ctx, ctx->device, d_comp, mem.data() + cut[pi], cut[pi + 1] - cut[pi], ctx->feed_buf, d_mem + cut[pi], d_st + cut[pi],
+                                     ctx->s_compute, 1)) return rc;
+        ctx->timing.total_launches++;
+    }
+    CK(cudaEventRecord(ctx->ev[1], ctx->s_compute));
+    std::vector<unsigned int> status(nm);
+    CK(cudaMemcpyAsync(status.data(), d_st, nm * sizeof(unsigned int), cudaMemcpyDeviceToHost, ctx->s_compute));
+    CK(cudaStreamSynchronize(ctx->s_compute));
+    float ms = 0;
+    CK(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1])); ctx->timing.inflate_ms += ms;
+    CK(cudaEventElapsedTime(&ms, ctx->ev_copy[n_piece], ctx->ev_copy[n_piece - 1])); ctx->timing.h2d_ms += ms;
+    for (size_t i = 0; i < nm; i++)
+        if (status[i]) { char b[128]; snprintf(b, sizeof b, "BGZF member %zu does not inflate (code %u)", i, status[i]); ctx->err = b; return KDB_E_FORMAT; }
+    const unsigned long long pass = kPassBytes;
+    for (unsigned long long lo = 0; lo < text; lo += pass)
+        if (int rc = run_pass2(ctx, ctx->feed_buf, lo, std::min<unsigned long long>(lo + pass, text), text)) return rc;
+    return end_feed(ctx, (size_t)text);
 }
 
 // ---- multi-GPU behind the C-ABI (kdb_reduce_nccl) -----------------------------------------------------------

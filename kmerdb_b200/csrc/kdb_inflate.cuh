@@ -1,0 +1,308 @@
+// GPU inflate of BGZF members (reference: gzip.open at kmerdb/parse.py:63-68, sniffed by
+// kmerdb/util.py:80-88).  BGZF (bgzip, Bio.bgzf) is a series of independent gzip members of at most 64 KiB of text each,
+// so the COMPRESSED bytes cross PCIe and every member is inflated by one warp straight into the text buffer the
+// tokeniser reads.  RFC 1951 restated for a warp:
+//   * all 32 lanes run the bit-stream decoder redundantly (same addresses: broadcast loads, no shuffles, no divergence);
+//   * literal: lane 0 stores the byte; match (length, distance): the lanes copy the bytes of the match in parallel
+//     (out[pos + i] = out[pos - d + i mod d] covers overlapping matches), a __syncwarp orders them for the next symbol;
+//   * Huffman tables per warp in shared memory: a 10-bit (literal/length) and an 8-bit (distance) first-level table filled by
+//     the lanes together, longer codes by the canonical count/offset walk (RFC 1951 3.2.2);
+//   * stored and fixed-Huffman blocks included (bgzip's EOF marker is an empty fixed block).
+// Checks per member: the stream ends exactly at its last block, the output length equals ISIZE, and CRC-32 of the output
+// equals the trailer (32 lane-chunk CRCs by table, joined with the GF(2) shift operator of zlib's crc32_combine).
+#pragma once
+#include "kdb_common.cuh"
+
+namespace kdb {
+
+struct BgzfMember {
+    unsigned long long in_off;    // first byte of the deflate payload inside the compressed buffer
+    unsigned long long out_off;   // where its text goes
+    unsigned int in_len;          // payload bytes (member size - header - 8 trailer bytes)
+    unsigned int out_len;         // ISIZE
+    unsigned int crc;             // CRC-32 of the text (gzip trailer)
+    unsigned int pad;
+};
+
+constexpr int kInfWarps = 8;                 // warps (members in flight) per CTA
+constexpr int kLitBits = 10, kDistBits = 8;
+
+struct InfTables {
+    unsigned short lit[1 << kLitBits];       // first level: symbol | length << 9  (0: longer code / invalid)
+    unsigned short dist[1 << kDistBits];     // symbol | length << 5
+    unsigned short lit_sym[288], dist_sym[32];      // symbols in canonical order
+    unsigned short lit_cnt[16], dist_cnt[16];       // codes per length
+    unsigned char lens[352];                 // code lengths while a block header is read
+};
+
+__constant__ unsigned short c_len_base[29] = {3, 4, 5, 6, 7, 8, 9, 10, 11, 13, 15, 17, 19, 23, 27, 31, 35, 43, 51, 59, 67, 83, 99, 115, 131, 163, 195, 227, 258};
+__constant__ unsigned char c_len_extra[29] = {0, 0, 0, 0, 0, 0, 0, 0, 1, 1, 1, 1, 2, 2, 2, 2, 3, 3, 3, 3, 4, 4, 4, 4, 5, 5, 5, 5, 0};
+__constant__ unsigned short c_dist_base[30] = {1, 2, 3, 4, 5, 7, 9, 13, 17, 25, 33, 49, 65, 97, 129, 193, 257, 385, 513, 769, 1025, 1537, 2049, 3073, 4097, 6145, 8193, 12289, 16385, 24577};
+__constant__ unsigned char c_dist_extra[30] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 4, 5, 5, 6, 6, 7, 7, 8, 8, 9, 9, 10, 10, 11, 11, 12, 12, 13, 13};
+__constant__ unsigned char c_clen_order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
+__constant__ unsigned int c_crc_table[256];  // filled by the host (kdb_api.cu: build_crc_table)
+
+// LSB-first bit reader over global memory, identical in every lane (broadcast loads).  Whole aligned 32-bit words are
+// loaded (the payload may start at any byte: the first word is shifted into place); a word may reach up to 3 bytes past the
+// payload (the member's 8-byte trailer follows it): `used()` tells how many payload bits were really consumed.
+struct BitReader {
+    const uint32_t* w;                // aligned word holding the next unread byte ...
+    unsigned long long buf;
+    long long bits_in;                // payload bits loaded so far
+    int cnt;
+    __device__ __forceinline__ void init(const uint8_t* p) {
+        const unsigned int skip = (unsigned int)((uintptr_t)p & 3u);
+        w = reinterpret_cast<const uint32_t*>(p - skip);
+        buf = (unsigned long long)(__ldg(w++) >> (8 * skip));
+        cnt = 32 - 8 * (int)skip;
+        bits_in = cnt;
+    }
+    __device__ __forceinline__ void refill() {                      // at least 33 bits afterwards
+        if (cnt <= 32) { buf |= (unsigned long long)__ldg(w++) << cnt; cnt += 32; bits_in += 32; }
+    }
+    __device__ __forceinline__ unsigned int peek(int n) const { return (unsigned int)buf & ((1u << n) - 1u); }
+    __device__ __forceinline__ void drop(int n) { buf >>= n; cnt -= n; }
+    __device__ __forceinline__ unsigned int take(int n) { const unsigned int v = peek(n); drop(n); return v; }
+    __device__ __forceinline__ long long used() const { return bits_in - cnt; }
+};
+
+// Canonical decode, one bit at a time (codes longer than the first-level table; the code-length alphabet).
+__device__ __forceinline__ int slow_decode(BitReader& br, const unsigned short* cnt, const unsigned short* sym) {
+    int code = 0, first = 0, index = 0;
+    for (int len = 1; len <= 15; len++) {
+        code |= (int)br.take(1);
+        const int c = cnt[len];
+        if (code - c < first) return sym[index + (code - first)];
+        index += c; first += c; first <<= 1; code <<= 1;
+    }
+    return -1;
+}
+
+// Build the canonical order + first-level table of `n` code lengths (lens[0..n)).  All lanes call it; returns false on an
+// over-subscribed set.  tbl_bits = width of the first level, sym_shift = where the length sits in an entry.
+__device__ bool build_table(const unsigned char* lens, int n, unsigned short* cnt, unsigned short* sym, unsigned short* tbl, int tbl_bits, int sym_shift, int lane) {
+    if (lane < 16) cnt[lane] = 0;
+    __syncwarp();
+    if (lane == 0) {
+        for (int i = 0; i < n; i++) cnt[lens[i]]++;
+        cnt[0] = 0;
+    }
+    __syncwarp();
+    int left = 1;
+    unsigned short offs[16];
+    offs[1] = 0;
+    for (int len = 1; len <= 15; len++) {
+        left <<= 1;
+        left -= cnt[len];
+        if (left < 0) return false;
+        if (len < 15) offs[len + 1] = offs[len] + cnt[len];
+    }
+    for (int i = lane; i < (1 << tbl_bits); i += 32) tbl[i] = 0;
+    __syncwarp();
+    if (lane == 0) {
+        unsigned short o[16];
+        for (int len = 1; len <= 15; len++) o[len] = offs[len];
+        for (int i = 0; i < n; i++) if (lens[i]) sym[o[lens[i]]++] = (unsigned short)i;
+    }
+    __syncwarp();
+    // first level: symbol j of canonical order with length L and code c fills every index whose low L bits are c reversed
+    int code = 0, idx = 0;
+    for (int len = 1; len <= tbl_bits; len++) {
+        const int c = cnt[len];
+        for (int j = lane; j < c; j += 32) {
+            const unsigned int rev = __brev((unsigned int)(code + j)) >> (32 - len);
+            const unsigned short e = (unsigned short)(sym[idx + j] | (len << sym_shift));
+            for (unsigned int i = rev; i < (1u << tbl_bits); i += 1u << len) tbl[i] = e;
+        }
+        code = (code + c) << 1;
+        idx += c;
+    }
+    __syncwarp();
+    return true;
+}
+
+__device__ __forceinline__ int decode_sym(BitReader& br, const unsigned short* tbl, int tbl_bits, int sym_shift, const unsigned short* cnt, const unsigned short* sym) {
+    const unsigned short e = tbl[br.peek(tbl_bits)];
+    if (e) { br.drop(e >> sym_shift); return e & ((1 << sym_shift) - 1); }
+    return slow_decode(br, cnt, sym);
+}
+
+// CRC-32 (reflected, 0xEDB88320) helpers: byte table walk, and the GF(2) operator that appends n zero bytes
+__device__ __forceinline__ unsigned int gf2_times(const unsigned int* mat, unsigned int vec) {
+    unsigned int sum = 0;
+    for (int i = 0; vec; vec >>= 1, i++) if (vec & 1u) sum ^= mat[i];
+    return sum;
+}
+
+// status per member: 0 ok, 1 malformed stream, 2 length mismatch, 3 CRC mismatch
+__global__ void __launch_bounds__(kInfWarps * 32) k_inflate_bgzf(const uint8_t* __restrict__ comp, const BgzfMember* __restrict__ members, unsigned int n_members,
+                                                                 uint8_t* __restrict__ out, unsigned int* __restrict__ status, int check_crc) {
+    __shared__ InfTables s_tab[kInfWarps];
+    __shared__ unsigned int s_mat[kInfWarps][2][32];
+    __shared__ unsigned int s_crc[256];                              // (data-dependent index: a __constant__ table would serialise the lanes)
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) s_crc[i] = c_crc_table[i];
+    __syncthreads();
+    InfTables& T = s_tab[warp];
+    for (unsigned int mi = blockIdx.x * kInfWarps + warp; mi < n_members; mi += gridDim.x * kInfWarps) {
+        const BgzfMember M = members[mi];
+        uint8_t* const dst = out + M.out_off;
+        const uint8_t* const payload = comp + M.in_off;
+        BitReader br;
+        br.init(payload);
+        unsigned int pos = 0, err = 0;
+        bool last = false;
+        while (!last && !err) {
+            if (br.used() > 8ll * (long long)M.in_len) { err = 1; break; }      // (a run of empty blocks in garbage must not read on for ever)
+            br.refill();
+            last = br.take(1) != 0;
+            const unsigned int type = br.take(2);
+            if (type == 0) {                                    // stored
+                br.drop(br.cnt & 7);                            // (whole bytes are loaded, so the bit count says where the byte border is)
+                br.refill();
+                const unsigned int len = br.take(16);
+                br.refill();
+                const unsigned int nlen = br.take(16);
+                if ((len ^ 0xFFFFu) != nlen) { err = 1; break; }
+                const unsigned long long src = (unsigned long long)(br.used() >> 3);
+                if (src + len > M.in_len || pos + len > M.out_len) { err = 1; break; }
+                for (unsigned int i = lane; i < len; i += 32) dst[pos + i] = payload[src + i];
+                pos += len;
+                br.init(payload + src + len);
+                br.bits_in += 8ll * (long long)(src + len);
+                __syncwarp();
+                continue;
+            }
+            if (type == 3) { err = 1; break; }
+            if (type == 1) {                                    // fixed codes (RFC 1951 3.2.6)
+                for (int i = lane; i < 288; i += 32) T.lens[i] = i < 144 ? 8 : (i < 256 ? 9 : (i < 280 ? 7 : 8));
+                __syncwarp();
+                build_table(T.lens, 288, T.lit_cnt, T.lit_sym, T.lit, kLitBits, 9, lane);
+                for (int i = lane; i < 30; i += 32) T.lens[i] = 5;
+                __syncwarp();
+                build_table(T.lens, 30, T.dist_cnt, T.dist_sym, T.dist, kDistBits, 5, lane);
+            } else {                                            // dynamic codes (3.2.7)
+                const int nlen = (int)br.take(5) + 257, ndist = (int)br.take(5) + 1, ncode = (int)br.take(4) + 4;
+                if (nlen > 286 || ndist > 30) { err = 1; break; }
+                if (lane < 19) T.lens[lane] = 0;
+                __syncwarp();
+                for (int i = 0; i < ncode; i++) {
+                    br.refill();
+                    const unsigned int v = br.take(3);
+                    if (lane == 0) T.lens[c_clen_order[i]] = (unsigned char)v;
+                }
+                __syncwarp();
+                // the code-length alphabet (19 symbols, at most 7 bits): canonical walk only; its tables sit where the distance
+                // tables go later
+                if (!build_table(T.lens, 19, T.dist_cnt, T.dist_sym, T.dist, 7, 5, lane)) { err = 1; break; }
+                __syncwarp();
+                int idx = 0;
+                while (idx < nlen + ndist) {
+                    br.refill();
+                    const int sym = decode_sym(br, T.dist, 7, 5, T.dist_cnt, T.dist_sym);
+                    if (sym < 0) { err = 1; break; }
+                    if (sym < 16) { if (lane == 0) T.lens[32 + idx] = (unsigned char)sym; idx++; }
+                    else {
+                        int rep, val = 0;
+                        if (sym == 16) {
+                            if (idx == 0) { err = 1; break; }
+                            __syncwarp();
+                            val = T.lens[32 + idx - 1];
+                            rep = 3 + (int)br.take(2);
+                        } else if (sym == 17) rep = 3 + (int)br.take(3);
+                        else rep = 11 + (int)br.take(7);
+                        if (idx + rep > nlen + ndist) { err = 1; break; }
+                        __syncwarp();
+                        for (int i = lane; i < rep; i += 32) T.lens[32 + idx + i] = (unsigned char)val;
+                        idx += rep;
+                        __syncwarp();
+                    }
+                }
+                if (err) break;
+                __syncwarp();
+                if (T.lens[32 + 256] == 0) { err = 1; break; }          // no end-of-block code
+                if (!build_table(T.lens + 32, nlen, T.lit_cnt, T.lit_sym, T.lit, kLitBits, 9, lane)) { err = 1; break; }
+                if (!build_table(T.lens + 32 + nlen, ndist, T.dist_cnt, T.dist_sym, T.dist, kDistBits, 5, lane)) { err = 1; break; }
+            }
+            // ---- the symbols of the block ---------------------------------------------------------------------
+            while (true) {
+                br.refill();
+                int sym = decode_sym(br, T.lit, kLitBits, 9, T.lit_cnt, T.lit_sym);
+                if (sym < 0) { err = 1; break; }
+                if (sym < 256) {
+                    if (pos >= M.out_len) { err = 2; break; }
+                    if (lane == 0) dst[pos] = (uint8_t)sym;
+                    pos++;
+                    continue;
+                }
+                if (sym == 256) break;
+                sym -= 257;
+                if (sym >= 29) { err = 1; break; }
+                const unsigned int len = c_len_base[sym] + br.take(c_len_extra[sym]);
+                br.refill();
+                const int ds = decode_sym(br, T.dist, kDistBits, 5, T.dist_cnt, T.dist_sym);
+                if (ds < 0 || ds >= 30) { err = 1; break; }
+                const unsigned int d = c_dist_base[ds] + br.take(c_dist_extra[ds]);
+                if (d > pos) { err = 1; break; }
+                if (pos + len > M.out_len) { err = 2; break; }
+                __syncwarp();                                       // the literals before the match are in place
+                const uint8_t* from = dst + pos - d;
+                if (d >= len) { for (unsigned int i = lane; i < len; i += 32) dst[pos + i] = from[i]; }
+                else { for (unsigned int i = lane; i < len; i += 32) dst[pos + i] = from[i % d]; }
+                pos += len;
+                __syncwarp();
+            }
+        }
+        if (!err && br.used() > 8ll * (long long)M.in_len) err = 1;   // ran past the end of the payload
+        if (!err && pos != M.out_len) err = 2;
+        __syncwarp();
+        if (!err && check_crc) {
+            // every lane takes one chunk of `per` bytes, then the partial values are joined front to back:
+            // crc(A || B) = shift(crc(A), |B|) ^ crc(B) on the raw register values (zlib crc32_combine)
+            const unsigned int per = (M.out_len + 31) / 32;
+            const unsigned int b0 = min(M.out_len, lane * per), b1 = min(M.out_len, b0 + per);
+            unsigned int c = 0xFFFFFFFFu;
+            for (unsigned int i = b0; i < b1; i++) c = s_crc[(c ^ dst[i]) & 0xFFu] ^ (c >> 8);
+            c ^= 0xFFFFFFFFu;
+            // operator for `per` zero bytes: start from the one-bit operator, square to one byte, then square-and-multiply
+            unsigned int* even = s_mat[warp][0];
+            unsigned int* odd = s_mat[warp][1];
+            odd[lane] = lane == 0 ? 0xEDB88320u : (1u << (lane - 1));                       // 1 zero bit
+            __syncwarp();
+            even[lane] = gf2_times(odd, odd[lane]); __syncwarp();                           // 2 bits
+            odd[lane] = gf2_times(even, even[lane]); __syncwarp();                          // 4 bits
+            unsigned int total = 0;
+            // join: total = crc of lanes [0, L]; every lane's chunk but the last has `per` bytes
+            for (int L = 0; L < 32; L++) {
+                const unsigned int cl = __shfl_sync(0xffffffffu, c, L);
+                const unsigned int lb0 = min(M.out_len, L * per), lb1 = min(M.out_len, lb0 + per);
+                unsigned int len2 = lb1 - lb0;
+                if (len2 == 0) continue;
+                if (L == 0) { total = cl; continue; }
+                // shift `total` by len2 bytes: square-and-multiply, every lane owns one row of the operator.  B starts as the
+                // 4-bit operator; each round squares it (first round: one byte) and applies it when the bit of len2 is set.
+                unsigned int v = total, nb = len2;
+                const unsigned int four_bits = odd[lane];
+                unsigned int* A = even;
+                unsigned int* B = odd;
+                __syncwarp();
+                do {
+                    A[lane] = gf2_times(B, B[lane]);
+                    __syncwarp();
+                    if (nb & 1u) v = gf2_times(A, v);
+                    nb >>= 1;
+                    unsigned int* t = A; A = B; B = t;
+                    __syncwarp();
+                } while (nb);
+                total = v ^ cl;
+                odd[lane] = four_bits;                               // back to the 4-bit operator for the next chunk
+                __syncwarp();
+            }
+            if (total != M.crc) err = 3;
+        }
+        if (lane == 0) status[mi] = err;
+        __syncwarp();
+    }
+}
+
+}  // namespace kdb

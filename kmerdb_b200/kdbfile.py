@@ -144,7 +144,7 @@ _ROW_ERRORS = {33: (AssertionError, "kmerdb.fileutil.KDBReader requires .kdb fil
 
 def _inflate_groups(raw, threads=None, group=2048):
     """The inflated text of a BGZF file, yielded in pieces of `group` blocks (inflate on a thread pool)."""
-    from .parse import _bgzf_blocks
+    from .parse import _bgzf_blocks, _inflate_member
     blocks = _bgzf_blocks(raw)
     if blocks is None:                                       # ordinary gzip: one piece
         yield gzip.decompress(raw)
@@ -152,7 +152,7 @@ def _inflate_groups(raw, threads=None, group=2048):
     mv = memoryview(raw)
     with ThreadPoolExecutor(max_workers=threads or _host_threads()) as ex:
         for g in range(0, len(blocks), group):
-            yield b"".join(ex.map(lambda b: zlib.decompress(mv[b[0] + 18:b[0] + b[1] - 8], -15), blocks[g:g + group]))
+            yield b"".join(ex.map(lambda b: _inflate_member(mv, b), blocks[g:g + group]))
 
 
 class KDBReader:

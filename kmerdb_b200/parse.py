@@ -58,29 +58,60 @@ def checksum(filepath):
 
 
 def _bgzf_blocks(raw):
-    """Offsets of the members of a BGZF file (gzip members whose extra field carries their size, e.g. written by
-    bgzip), or None when `raw` is ordinary gzip."""
+    """(offset, size, payload offset) of the members of a BGZF file (gzip members whose extra field carries their size in a
+    'BC' subfield, e.g. written by bgzip), or None when `raw` is ordinary gzip.  The extra field is walked subfield by
+    subfield (RFC 1952 2.3.1.1): XLEN is read, not assumed to be 6."""
     out, off, n = [], 0, len(raw)
     while off < n:
-        if n - off < 18 or raw[off:off + 4] != b"\x1f\x8b\x08\x04" or raw[off + 12:off + 16] != b"BC\x02\x00":
+        if n - off < 26 or raw[off:off + 3] != b"\x1f\x8b\x08" or not raw[off + 3] & 4:
             return None
-        size = int.from_bytes(raw[off + 16:off + 18], "little") + 1
-        out.append((off, size))
+        flg = raw[off + 3]
+        xlen = int.from_bytes(raw[off + 10:off + 12], "little")
+        p, xend, size = off + 12, off + 12 + xlen, None
+        while p + 4 <= xend:
+            slen = int.from_bytes(raw[p + 2:p + 4], "little")
+            if raw[p:p + 2] == b"BC" and slen == 2:
+                size = int.from_bytes(raw[p + 4:p + 6], "little") + 1
+            p += 4 + slen
+        if size is None or off + size > n:
+            return None
+        q = xend
+        for bit in (8, 16):                       # FNAME, FCOMMENT: zero-terminated
+            if flg & bit:
+                q = raw.index(b"\x00", q) + 1 if isinstance(raw, (bytes, bytearray)) else bytes(raw[q:off + size]).index(b"\x00") + q + 1
+        if flg & 2:
+            q += 2
+        out.append((off, size, q))
         off += size
     return out if off == n else None
 
 
+def _inflate_member(mv, b):
+    """One BGZF member on the host, checked against its trailer like gzip.open checks it (CRC-32 and ISIZE)."""
+    import zlib
+    off, size, q = b
+    text = zlib.decompress(mv[q:off + size - 8], -15)
+    crc, isize = int.from_bytes(mv[off + size - 8:off + size - 4], "little"), int.from_bytes(mv[off + size - 4:off + size], "little")
+    if zlib.crc32(text) & 0xFFFFFFFF != crc or len(text) & 0xFFFFFFFF != isize:
+        raise gzip.BadGzipFile("CRC check failed" if len(text) & 0xFFFFFFFF == isize else "Incorrect length of data produced")
+    return text
+
+
 def _gunzip(raw, threads=8):
     """Host gzip decode (kmerdb/parse.py:63-68 uses gzip.open).  Block-compressed input (BGZF) is inflated on a
-    thread pool, one member per task; plain gzip goes through zlib in one piece.  Same bytes either way."""
-    import zlib
+    thread pool, one member per task, each checked against its CRC-32 / ISIZE; plain gzip goes through zlib in one piece.
+    Same bytes either way; anything odd about the BGZF framing falls back to gzip.decompress, which raises what
+    gzip.open raises."""
     blocks = _bgzf_blocks(raw) if len(raw) > (1 << 20) else None
     if not blocks:
         return gzip.decompress(raw)
     from concurrent.futures import ThreadPoolExecutor
     mv = memoryview(raw)
-    with ThreadPoolExecutor(max_workers=threads) as ex:
-        parts = list(ex.map(lambda b: zlib.decompress(mv[b[0] + 18:b[0] + b[1] - 8], -15), blocks))
+    try:
+        with ThreadPoolExecutor(max_workers=threads) as ex:
+            parts = list(ex.map(lambda b: _inflate_member(mv, b), blocks))
+    except Exception:
+        return gzip.decompress(raw)
     return b"".join(parts)
 
 
@@ -375,6 +406,24 @@ def profile_bytes(data, k, fmt="fasta", replace_with_none=True, canonicalize=Tru
         return Profile(k, p.counts(), st, p.nullomers() if want_nullomers else None, p.timing())
 
 
+def profile_bgzf(raw, k, fmt="fasta", replace_with_none=True, canonicalize=True, device=0, want_nullomers=True):
+    """BGZF input: the COMPRESSED bytes go to the device and are inflated there, one warp per member
+    (kdb_feed_bgzf_host), then tokenised and counted in place.  Returns None when `raw` is not BGZF, a member fails its
+    CRC-32 / ISIZE, or the text needs the host tokeniser: the caller then takes the host gzip path, which raises what the
+    reference's gzip.open raises."""
+    if _native.bgzf_text_size(raw) is None:
+        return None
+    with _native.Profiler(k, canonical=canonicalize, skip_n=replace_with_none, fastq=(fmt == "fastq"), device=device) as p:
+        if p.feed_bgzf(raw) != 0:
+            return None
+        status = p.finish()
+        if status == _native.KDB_E_LAYOUT:
+            return None
+        st = p.stats()
+        _raise_for_status(status, st)
+        return Profile(k, p.counts(), st, p.nullomers() if want_nullomers else None, p.timing())
+
+
 def iter_profile_multik(data, min_k, max_k, fmt="fasta", replace_with_none=True, canonicalize=True, device=0, want_nullomers=False):
     """`--minK/--maxK` sweep (kmerdb/__init__.py:1846-1855) over text held in host memory, yielding (k, Profile)
     for k = min_k .. max_k.  The reference re-parses the file for every k; here the text crosses PCIe once, is
@@ -438,9 +487,14 @@ def parsefile_deferred(filepath, k, replace_with_none=True, canonicalize=True, d
         raise TypeError("kmerdb.parse.parsefile expects the keyword argument 'replace_with_none' to be a bool")
     raw, sums = _read_and_hash(filepath)                       # hashes of the raw bytes, computed beside the read and the GPU work
     try:
-        data = _read_text_bytes(filepath, raw)
         fmt = _file_format(filepath)
-        prof = profile_bytes(data, k, fmt, replace_with_none, bool(canonicalize), device)
+        prof = None
+        devices = _device_list(device)
+        if len(devices) == 1 and len(raw) >= 28 and bytes(raw[:2]) == b"\x1f\x8b" and is_gz_file(filepath):
+            prof = profile_bgzf(raw, k, fmt, replace_with_none, bool(canonicalize), devices[0])       # BGZF: inflate on the GPU
+        if prof is None:
+            data = _read_text_bytes(filepath, raw)
+            prof = profile_bytes(data, k, fmt, replace_with_none, bool(canonicalize), device)
     except BaseException:
         sums()                                                 # (join the hashing threads before the raise leaves)
         raise

@@ -44,3 +44,42 @@ def test_read_and_hash_streams_the_file(tmp_path):
         assert bytes(raw) == data
         assert sums() == (hashlib.md5(data).hexdigest(), hashlib.sha256(data).hexdigest())
         assert sums() == parse.checksum(str(p))
+
+
+def _bgzf_with_extra_subfield(data):
+    """A BGZF member whose extra field holds another subfield BEFORE 'BC' (legal RFC 1952; XLEN = 12, not 6)."""
+    import struct
+    import zlib
+    c = zlib.compressobj(6, zlib.DEFLATED, -15)
+    comp = c.compress(data) + c.flush()
+    bsize = len(comp) + 12 + 12 + 8
+    head = b"\x1f\x8b\x08\x04\x00\x00\x00\x00\x00\xff" + struct.pack("<H", 12) + b"XY\x02\x00\xaa\xbb" + b"BC\x02\x00" + struct.pack("<H", bsize - 1)
+    return head + comp + struct.pack("<II", zlib.crc32(data) & 0xFFFFFFFF, len(data))
+
+
+def test_bgzf_walker_reads_xlen_and_checks_the_trailer():
+    """members with extra subfields must inflate from the right offset; a corrupt member must raise like
+    gzip.open does (BadGzipFile), not be counted silently."""
+    import ctypes
+    import numpy as np
+    import pytest
+    from kmerdb_b200 import _native
+    raw = b">r\n" + b"ACGTTGCAAC" * 20000 + b"\n"
+    pieces = [raw[o:o + 60000] for o in range(0, len(raw), 60000)]
+    blob = b"".join(_bgzf_with_extra_subfield(x) for x in pieces) * 6 + kdbfile._BGZF_EOF          # > 1 MiB of members
+    blocks = parse._bgzf_blocks(blob)
+    assert blocks is not None and all(q - off == 24 for off, _size, q in blocks[:-1])
+    assert parse._gunzip(blob) == raw * 6
+    # the C-ABI walker (kdb_bgzf_index, host code) agrees
+    assert _native.bgzf_text_size(blob) == 6 * len(raw)
+    assert _native.bgzf_text_size(gzip.compress(raw)) is None
+    a = np.frombuffer(blob, dtype=np.uint8)
+    mem = np.zeros((len(blocks), 4), dtype=np.uint64)                 # 32 bytes per member
+    nm, text = ctypes.c_size_t(0), ctypes.c_uint64(0)
+    assert _native.lib().kdb_bgzf_index(a.ctypes.data, a.size, mem.ctypes.data, len(blocks), ctypes.byref(nm), ctypes.byref(text)) == 0
+    assert nm.value == len(blocks) and [int(x) for x in mem[:, 0]] == [q for _o, _s, q in blocks]
+    # flip one payload byte of the second member: CRC / stream check must fire
+    bad = bytearray(blob)
+    bad[blocks[1][2] + 40] ^= 0x55
+    with pytest.raises((gzip.BadGzipFile, OSError, EOFError, Exception)):
+        parse._gunzip(bytes(bad))
