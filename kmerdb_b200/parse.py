@@ -424,6 +424,159 @@ def profile_bgzf(raw, k, fmt="fasta", replace_with_none=True, canonicalize=True,
         return Profile(k, p.counts(), st, p.nullomers() if want_nullomers else None, p.timing())
 
 
+# ---- streaming input: bounded host memory ---------------------------------------------------------------
+# The reference consumes its input as a stream (kmerdb/parse.py:63-72: gzip.open + SeqIO.parse).  Here the raw file is read in
+# pieces (hashed for md5 / sha256 as they pass, kmerdb/util.py:35-50), gzip is inflated piece by piece on a host thread, the
+# text is cut into fragments at record borders, and every fragment is one kdb_feed_host: the next piece is being read /
+# inflated while the GPU works on the current fragment.  Host memory: a few pieces, whatever the file size.
+STREAM_PIECE = 64 << 20
+
+
+def _iter_raw_hashed(filepath, piece, hashes):
+    with open(filepath, "rb", buffering=0) as fh:
+        while True:
+            b = fh.read(piece)
+            if not b:
+                return
+            for h in hashes:
+                h.update(b)
+            yield b
+
+
+def _iter_text_pieces(filepath, piece, hashes):
+    """Uncompressed text of the file in pieces of about `piece` bytes.  gzip (any number of members, as gzip.open reads
+    them) is inflated with zlib on this thread; errors are what gzip.open raises (BadGzipFile / EOFError / zlib.error)."""
+    import zlib
+    raw = _iter_raw_hashed(filepath, piece // 4, hashes)
+    first = next(raw, b"")
+    if not (first[:2] == b"\x1f\x8b" and is_gz_file(filepath)):
+        if first:
+            yield first
+        yield from raw
+        return
+    d = zlib.decompressobj(31)
+    pending = first
+    while True:
+        while pending:
+            out = d.decompress(pending, piece)
+            if out:
+                yield out
+            if d.eof:                                            # next member (concatenated gzip), or trailing garbage
+                pending = d.unused_data
+                if pending[:2] == b"\x1f\x8b":
+                    d = zlib.decompressobj(31)
+                    continue
+                pending = pending.lstrip(b"\x00")
+                if pending and pending[:2] != b"\x1f\x8b":
+                    raise gzip.BadGzipFile("Not a gzipped file (%r)" % pending[:2])
+                if pending:
+                    d = zlib.decompressobj(31)
+                    continue
+                break
+            pending = d.unconsumed_tail
+        nxt = next(raw, None)
+        if nxt is None:
+            if not d.eof:
+                raise EOFError("Compressed file ended before the end-of-stream marker was reached")
+            return
+        if d.eof:
+            d = zlib.decompressobj(31)
+        pending = nxt
+
+
+def _iter_fragments(pieces, fmt):
+    """Cut the text at record borders: a FASTA fragment ends before a line that starts with '>', a FASTQ fragment after a line
+    whose index is a multiple of 4 (the only layout the device tokeniser takes natively).  What follows the last border of a
+    piece is carried into the next fragment; the end of the file flushes it."""
+    carry, carry_lines = [], 0
+    for piece in pieces:
+        if fmt == "fasta":
+            cut = piece.rfind(b"\n>") + 1                       # 0 when there is no border in this piece
+        else:
+            total = carry_lines + piece.count(b"\n")
+            m = total - total % 4
+            cut = 0
+            if m > carry_lines:
+                pos = len(piece)
+                for _ in range(total - m + 1):
+                    pos = piece.rfind(b"\n", 0, pos)
+                cut = pos + 1
+                carry_lines = total - m
+            else:
+                carry_lines = total
+        if cut:
+            yield b"".join(carry + [piece[:cut]]) if carry else piece[:cut]
+            carry = [piece[cut:]] if cut < len(piece) else []
+        else:
+            carry.append(piece)
+    if carry:
+        yield b"".join(carry)
+
+
+def profile_stream(filepath, k, fmt, replace_with_none=True, canonicalize=True, device=0, want_nullomers=True, piece=None):
+    """Profile a file of any size with bounded host memory.  Returns (Profile or None, sums) — None when the text needs the
+    host tokeniser (the caller re-reads the file the slow way); sums() gives (md5, sha256) of the raw bytes."""
+    import queue
+    import threading
+    piece = piece or STREAM_PIECE
+    hashes = (hashlib.md5(), hashlib.sha256())
+    q = queue.Queue(maxsize=2)
+    stop = threading.Event()
+
+    def produce():
+        try:
+            for frag in _iter_fragments(_iter_text_pieces(filepath, piece, hashes), fmt):
+                while not stop.is_set():
+                    try:
+                        q.put(frag, timeout=0.1)
+                        break
+                    except queue.Full:
+                        continue
+                if stop.is_set():
+                    return
+            q.put(None)
+        except BaseException as e:                               # surfaces on the consumer side, after the fragments before it
+            q.put(e)
+
+    t = threading.Thread(target=produce, daemon=True)
+    t.start()
+
+    def sums():
+        t.join()
+        return hashes[0].hexdigest(), hashes[1].hexdigest()
+    try:
+        with _native.Profiler(k, canonical=canonicalize, skip_n=replace_with_none, fastq=(fmt == "fastq"), device=device) as p:
+            pending = None
+            while True:
+                item = q.get()
+                if item is None:
+                    break
+                if isinstance(item, BaseException):
+                    pending = item
+                    break
+                p.feed(item)
+            if pending is not None and not isinstance(pending, ValueError):
+                raise pending                                     # BadGzipFile / EOFError / zlib.error: what gzip.open raises
+            status = p.finish()
+            if status == _native.KDB_E_LAYOUT:
+                return None, sums
+            st = p.stats()
+            if status not in (0, _native.KDB_E_EMPTY) or pending is None:
+                _raise_for_status(status, st)
+            if pending is not None:
+                raise pending
+            return Profile(k, p.counts(), st, p.nullomers() if want_nullomers else None, p.timing()), sums
+    except BaseException:
+        stop.set()
+        raise
+
+
+def _is_bgzf_file(filepath):
+    with open(filepath, "rb") as fh:
+        head = fh.read(18)
+    return len(head) == 18 and head[:4] == b"\x1f\x8b\x08\x04" and b"BC\x02\x00" in head[12:18]
+
+
 def iter_profile_multik(data, min_k, max_k, fmt="fasta", replace_with_none=True, canonicalize=True, device=0, want_nullomers=False):
     """`--minK/--maxK` sweep (kmerdb/__init__.py:1846-1855) over text held in host memory, yielding (k, Profile)
     for k = min_k .. max_k.  The reference re-parses the file for every k; here the text crosses PCIe once, is
@@ -485,19 +638,25 @@ def parsefile_deferred(filepath, k, replace_with_none=True, canonicalize=True, d
         raise TypeError("kmerdb.parse.parsefile expects an int as its second positional argument")
     elif type(replace_with_none) is not bool:
         raise TypeError("kmerdb.parse.parsefile expects the keyword argument 'replace_with_none' to be a bool")
-    raw, sums = _read_and_hash(filepath)                       # hashes of the raw bytes, computed beside the read and the GPU work
-    try:
-        fmt = _file_format(filepath)
-        prof = None
-        devices = _device_list(device)
-        if len(devices) == 1 and len(raw) >= 28 and bytes(raw[:2]) == b"\x1f\x8b" and is_gz_file(filepath):
-            prof = profile_bgzf(raw, k, fmt, replace_with_none, bool(canonicalize), devices[0])       # BGZF: inflate on the GPU
+    fmt = _file_format(filepath)
+    devices = _device_list(device)
+    prof, sums = None, None
+    if len(devices) == 1 and not _is_bgzf_file(filepath):
+        # one GPU, plain or ordinary-gzip input: streamed with bounded host memory (pieces are read / inflated while the GPU works)
+        prof, sums = profile_stream(filepath, k, fmt, replace_with_none, bool(canonicalize), devices[0])
         if prof is None:
-            data = _read_text_bytes(filepath, raw)
-            prof = profile_bytes(data, k, fmt, replace_with_none, bool(canonicalize), device)
-    except BaseException:
-        sums()                                                 # (join the hashing threads before the raise leaves)
-        raise
+            sums()
+    if prof is None:
+        raw, sums = _read_and_hash(filepath)                   # hashes of the raw bytes, computed beside the read and the GPU work
+        try:
+            if len(devices) == 1 and len(raw) >= 28 and bytes(raw[:2]) == b"\x1f\x8b" and is_gz_file(filepath):
+                prof = profile_bgzf(raw, k, fmt, replace_with_none, bool(canonicalize), devices[0])       # BGZF: inflate on the GPU
+            if prof is None:
+                data = _read_text_bytes(filepath, raw)
+                prof = profile_bytes(data, k, fmt, replace_with_none, bool(canonicalize), device)
+        except BaseException:
+            sums()                                             # (join the hashing threads before the raise leaves)
+            raise
     assert prof.nullomers == len(prof.nullomer_array), "Internal Error: kmerdb.parse.parsefile() found inconsistencies between two ways of counting nullomers. Internal error."
 
     def file_metadata():

@@ -254,3 +254,32 @@ def test_packed_16bit_counters_wrap_exactly(k, canonical):
         rec[which == j, 2:k + 2] = pat[j]
     counts = _cmp_oracle(rec.reshape(-1).tobytes(), k, canonical=canonical)
     assert counts[0] > 4_000_000 and counts[1] > 3_000_000
+
+
+@pytest.mark.parametrize("fmt", ["fasta", "fastq"])
+@pytest.mark.parametrize("gz", [False, True])
+def test_streamed_parsefile_equals_whole_file(fmt, gz, tmp_path, monkeypatch):
+    """f2 streaming: the file is read / inflated in small pieces and fed fragment by fragment (record-aligned cuts);
+    counts, statistics and checksums equal the whole-text profile.  Records cross many piece borders (80-column genome
+    lines, 150 bp reads)."""
+    rng = np.random.default_rng(21)
+    if fmt == "fasta":
+        recs = []
+        for i in range(40):
+            L = int(rng.integers(30, 60000))
+            seq = "".join(np.array(list("ACGT"))[rng.integers(0, 4, size=L)])
+            recs.append(">chr%d\n" % i + "\n".join(seq[j:j + 80] for j in range(0, L, 80)) + "\n")
+        text = "".join(recs).encode()
+    else:
+        text = bytes(_native.synth_host(9000, fastq=True))
+    path = str(tmp_path / ("x." + ("fa" if fmt == "fasta" else "fq") + (".gz" if gz else "")))
+    with (gzip.open(path, "wb") if gz else open(path, "wb")) as fh:
+        fh.write(text)
+    monkeypatch.setattr(parse, "STREAM_PIECE", 1 << 16)
+    counts, meta, nullomers = parse.parsefile(path, 9, replace_with_none=True, canonicalize=True)
+    whole = parse.profile_bytes(text, 9, fmt, True, True)
+    assert np.array_equal(counts, whole.counts) and np.array_equal(nullomers, whole.nullomer_array)
+    blob = open(path, "rb").read()
+    assert meta == whole.file_metadata(path, hashlib.md5(blob).hexdigest(), hashlib.sha256(blob).hexdigest())
+    rc, ocounts, _ost = oracle.profile(text, 9, fastq=(fmt == "fastq"))
+    assert rc == 0 and np.array_equal(counts, ocounts)

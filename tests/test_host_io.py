@@ -83,3 +83,44 @@ def test_bgzf_walker_reads_xlen_and_checks_the_trailer():
     bad[blocks[1][2] + 40] ^= 0x55
     with pytest.raises((gzip.BadGzipFile, OSError, EOFError, Exception)):
         parse._gunzip(bytes(bad))
+
+
+def test_streamed_text_pieces_and_record_aligned_fragments(tmp_path):
+    """parse._iter_text_pieces / _iter_fragments (bounded-memory input): same bytes as gzip.open for plain, gzip and
+    multi-member gzip files; fragments join back to the text and start at record borders; raw bytes are hashed on the way."""
+    import numpy as np
+    import pytest
+    rng = np.random.default_rng(7)
+    recs = []
+    for i in range(300):
+        L = int(rng.integers(1, 400))
+        seq = "".join(np.array(list("ACGT"))[rng.integers(0, 4, size=L)])
+        recs.append(">r%d with > inside\n" % i + "\n".join(seq[j:j + 70] for j in range(0, L, 70)) + "\n")
+    fasta = "".join(recs).encode()
+    fastq = "".join("@q%d\n%s\n+\n%s\n" % (i, "ACGT" * int(rng.integers(1, 30)), "@>+I" * 3) for i in range(500)).encode()
+    for name, text, fmt in (("a.fa", fasta, "fasta"), ("b.fq", fastq, "fastq"), ("c.fq", fastq[:-1], "fastq")):
+        for variant in ("plain", "gz", "gz2"):
+            p = str(tmp_path / (name + ("" if variant == "plain" else ".gz")))
+            blob = text if variant == "plain" else (gzip.compress(text) if variant == "gz" else gzip.compress(text[:5000]) + gzip.compress(text[5000:]))
+            open(p, "wb").write(blob)
+            for piece in (257, 4096, 1 << 20):
+                hs = (hashlib.md5(), hashlib.sha256())
+                pieces = list(parse._iter_text_pieces(p, piece, hs))
+                assert b"".join(pieces) == text and max(len(x) for x in pieces) <= max(piece, 64)
+                assert hs[0].hexdigest() == hashlib.md5(blob).hexdigest() and hs[1].hexdigest() == hashlib.sha256(blob).hexdigest()
+                frags = list(parse._iter_fragments(iter(pieces), fmt))
+                assert b"".join(frags) == text
+                off = 0
+                for f in frags[:-1]:
+                    off += len(f)
+                    if fmt == "fasta":
+                        assert text[off:off + 1] == b">" and text[off - 1:off] == b"\n"
+                    else:
+                        assert text[:off].count(b"\n") % 4 == 0 and text[off - 1:off] == b"\n"
+    # a truncated gzip stream raises like gzip.open does
+    p = str(tmp_path / "t.fa.gz")
+    open(p, "wb").write(gzip.compress(fasta)[:-20])
+    with pytest.raises(EOFError):
+        list(parse._iter_text_pieces(p, 4096, ()))
+    with pytest.raises(EOFError):
+        gzip.open(p, "rb").read()
