@@ -189,8 +189,9 @@ def test_kmer_to_id_batch(golden):
 
 
 def test_full_size_100M_reads_properties():
-    """BASELINE.json configs[2] size on one GPU (100 M x 150 bp, 16.2 GB of FASTA text, 16 passes): the
-    size-independent properties of the result, and identity of two different feed chunkings."""
+    """BASELINE.json configs[2] size on one GPU (100 M x 150 bp, 16.2 GB of FASTA text, 31 passes): the
+    size-independent properties of the result, identity of two different feed chunkings, and gate T2 — the full
+    vector's sha256 against the C oracle over the same text (about 2 minutes of host time)."""
     n, k = 100_000_000, 12
     rb = _native.synth_record_bytes()
     buf = _native.DeviceBuffer(n * rb + 16)
@@ -212,12 +213,26 @@ def test_full_size_100M_reads_properties():
         p.feed_device(buf.ptr + cut, n * rb - cut)
         assert p.finish() == 0
         assert np.array_equal(p.counts(), counts) and p.stats() == st
-    # the first 200 000 reads of the same stream against the oracle
-    host = _native.synth_host(200000)
-    rc, ocounts, ost = oracle.profile(host, k, threads=8)
-    with _native.Profiler(k) as q:
-        q.feed_device(buf.ptr, 200000 * rb)
-        assert q.finish() == 0 and np.array_equal(q.counts(), ocounts)
+    # Parity gate T2 at full R: sha256 of the whole little-endian uint64 vector + the scalars against the C
+    # oracle run over the SAME 16.2 GB of text (copied back from the device in 8 pieces; the oracle's vectors add up)
+    threads = max(4, len(os.sched_getaffinity(0)))
+    osum = np.zeros(4 ** k, dtype=np.uint64)
+    ost = {"total_reads": 0, "total_kmers": 0, "sum_len": 0, "mono": [0, 0, 0, 0]}
+    piece = n // 8
+    host = np.empty(piece * rb, dtype=np.uint8)
+    for i in range(8):
+        assert _native.lib().kdb_memcpy_d2h(0, host.ctypes.data, buf.ptr + i * piece * rb, piece * rb) == 0
+        rc, oc, o = oracle.profile(host, k, threads=threads)
+        assert rc == 0
+        osum += oc
+        for f in ("total_reads", "total_kmers", "sum_len"):
+            ost[f] += o[f]
+        ost["mono"] = [a + b for a, b in zip(ost["mono"], o["mono"])]
+        assert o["min_len"] == o["max_len"] == 150
+    assert hashlib.sha256(counts.tobytes()).hexdigest() == hashlib.sha256(osum.tobytes()).hexdigest()
+    for f in ("total_reads", "total_kmers", "sum_len", "mono"):
+        assert st[f] == ost[f], f
+    assert st["unique_kmers"] == int(np.count_nonzero(osum))
 
 
 def test_configs1_full_vector_vs_oracle():
