@@ -1519,10 +1519,37 @@ extern "C" int kdb_minimizers_batch(int device, const uint8_t* letters, size_t n
     if (int rc = upload_lut(ctx)) return rc;
     const unsigned long long n_win = n_letters - k + 1, n_out = n_win - w + 1;
     DevBuf d_let, d_off, d_ids, d_best, d_bad, d_cnt, d_boff, d_out;
-    CK(d_let.alloc(n_letters)); CK(d_off.alloc((n_recs + 1) * 8)); CK(d_ids.alloc(n_win * 8)); CK(d_best.alloc(n_out * 8)); CK(d_bad.alloc(4));
+    CK(d_let.alloc(n_letters)); CK(d_off.alloc((n_recs + 1) * 8)); CK(d_bad.alloc(4));
     CK(cudaMemcpy(d_let.p, letters, n_letters, cudaMemcpyHostToDevice));
     CK(cudaMemcpy(d_off.p, rec_off, (n_recs + 1) * 8, cudaMemcpyHostToDevice));
     CK(cudaMemset(d_bad.p, 0, 4));
+    if (k <= 16 && w <= kFusedMaxW && !getenv("KDB_MIN_UNFUSED")) {
+        // fused path: letters -> rows, nothing staged in HBM (k8_minb_fused); first launch counts (and checks the letters), second writes
+        const unsigned int blocks = (unsigned int)((n_out + kEdgeBlock - 1) / kEdgeBlock);
+        CK(d_cnt.alloc(blocks * sizeof(unsigned int)));
+        k8_minb_fused<false><<<blocks, 256>>>(d_let.as<uint8_t>(), n_letters, n_out, d_off.as<unsigned long long>(), n_recs, k, w, d_cnt.as<unsigned int>(),
+                                              nullptr, nullptr, nullptr, nullptr, 0, d_bad.as<unsigned int>());
+        CK(cudaGetLastError());
+        unsigned int bad = 0;
+        CK(cudaMemcpy(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost));
+        if (bad & 1u) return KDB_E_ALPHABET;
+        if (bad & 2u) return KDB_E_IUPAC;
+        unsigned long long total = 0;
+        if (int rc = scan_blocks(ctx, d_cnt.as<unsigned int>(), blocks, d_boff, &total)) return rc;
+        *n_rows = (size_t)total;
+        const size_t m = std::min<size_t>(cap, (size_t)total);
+        if (!m || !rec || !pos || !ids) return KDB_OK;
+        CK(d_out.alloc(3 * m * 8));
+        unsigned long long* o = d_out.as<unsigned long long>();
+        k8_minb_fused<true><<<blocks, 256>>>(d_let.as<uint8_t>(), n_letters, n_out, d_off.as<unsigned long long>(), n_recs, k, w, nullptr,
+                                             d_boff.as<unsigned long long>(), o, o + m, o + 2 * m, m, d_bad.as<unsigned int>());
+        CK(cudaGetLastError());
+        CK(cudaMemcpy(rec, o, m * 8, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(pos, o + m, m * 8, cudaMemcpyDeviceToHost));
+        CK(cudaMemcpy(ids, o + 2 * m, m * 8, cudaMemcpyDeviceToHost));
+        return KDB_OK;
+    }
+    CK(d_ids.alloc(n_win * 8)); CK(d_best.alloc(n_out * 8));
     k8_window_ids<<<(unsigned int)((n_win + 255) / 256), 256>>>(d_let.as<uint8_t>(), n_win, k, d_ids.as<unsigned long long>(), d_bad.as<unsigned int>());
     CK(cudaGetLastError());
     unsigned int bad = 0;

@@ -127,7 +127,9 @@ __device__ __forceinline__ void or_bits(uint32_t* dst, uint32_t bitoff, const ui
 }
 
 // 4-bit gather of the 0x80 byte flags of m (byte j -> bit j)
-__device__ __forceinline__ uint32_t nib(uint32_t m) { return (((m >> 7) * 0x00204081u) >> 21) & 0xFu; }
+// (flags at bits 7, 15, 23, 31: the product puts flag j at bit 28 + j and every other partial product below bit 28 or beyond
+// bit 31, each on a bit of its own, so nothing carries: one IMAD + one shift)
+__device__ __forceinline__ uint32_t nib(uint32_t m) { return (m * 0x00204081u) >> 28; }
 __device__ __forceinline__ unsigned long long ones64(uint32_t n) { return n >= 64 ? ~0ull : ((1ull << n) - 1ull); }
 // x | x>>1 | ... | x>>(n-1)   (n >= 1)
 __device__ __forceinline__ unsigned long long smear_down(unsigned long long x, uint32_t n) {

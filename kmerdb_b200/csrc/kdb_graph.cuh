@@ -367,4 +367,139 @@ __global__ void __launch_bounds__(256) k8_minb_rows(const unsigned long long* __
     }
 }
 
+// ---- batched minimizers, fused (r02): letters -> rows in one kernel, nothing staged in HBM ---------------------------------
+// One CTA owns kEdgeBlock window-group starts.  Its letters (with the k + w - 1 halo) are classified through a shared-memory
+// copy of the class table (the __constant__ table indexed by a data-dependent byte serialises the warp), every thread builds
+// the canonical 32-bit ids of a run of consecutive windows by rolling (k <= 16), the window minimum is a doubling pass over
+// (id << 32 | position) keys in shared memory — the 64-bit minimum IS the leftmost minimum — and the rows leave compacted.
+// Replaces k8_window_ids + k8_min_window + k8_minb_rows and their two uint64 arrays (16 B of HBM per window before any row).
+constexpr int kFusedMaxW = 64;
+constexpr int kFusedIds = kEdgeBlock + 1 + kFusedMaxW;             // ids a CTA may need (one group before the block, w - 1 after)
+template <bool WRITE>
+__global__ void __launch_bounds__(256) k8_minb_fused(const uint8_t* __restrict__ letters, unsigned long long n_letters, unsigned long long n_out,
+                                                     const unsigned long long* __restrict__ rec_off, unsigned long long n_recs, int k, int w,
+                                                     unsigned int* __restrict__ block_n, const unsigned long long* __restrict__ block_off,
+                                                     unsigned long long* __restrict__ out_rec, unsigned long long* __restrict__ out_pos,
+                                                     unsigned long long* __restrict__ out_id, unsigned long long cap, unsigned int* bad_flag) {
+    __shared__ unsigned long long s_key[2][kFusedIds];
+    __shared__ uint8_t s_cls[kFusedIds + 16];
+    __shared__ uint8_t s_lut[256];
+    __shared__ unsigned int s_off[kMinbSlice];                      // record offsets of the block's slice, relative to its first record
+    __shared__ RecSlice s_hdr;
+    __shared__ unsigned long long s_off0;
+    __shared__ unsigned int s_warp[8];
+    __shared__ unsigned int s_total;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const unsigned long long base = (unsigned long long)blockIdx.x * kEdgeBlock;
+    const unsigned long long last = base + kEdgeBlock - 1 < n_out ? base + kEdgeBlock - 1 : n_out - 1;
+    s_lut[tid] = c_class_lut[tid];
+    if (tid == 0) {
+        const unsigned long long r0 = upper_rec(rec_off, n_recs, base), r1 = upper_rec(rec_off, n_recs, last);
+        s_hdr.first = r0;
+        s_hdr.n = (r1 - r0 + 2 <= (unsigned long long)kMinbSlice && rec_off[r1 + 1] - rec_off[r0] < 0xFFFFFFFFull) ? (unsigned int)(r1 - r0 + 2) : 0u;
+        s_off0 = rec_off[r0];
+    }
+    __syncthreads();
+    const RecSlice h = s_hdr;
+    const unsigned long long off0 = s_off0;
+    for (unsigned int i = tid; i < h.n; i += 256) s_off[i] = (unsigned int)(rec_off[h.first + i] - off0);
+    __syncthreads();
+    auto rec_of32 = [&](unsigned long long pq, unsigned long long* start, unsigned long long* end) -> unsigned long long {
+        if (h.n) {
+            const unsigned int x = (unsigned int)(pq - off0);
+            unsigned int lo = 0, hi = h.n - 1;          // s_off[lo] <= x < s_off[hi]
+            while (hi - lo > 1) { const unsigned int mid = (lo + hi) >> 1; if (s_off[mid] <= x) lo = mid; else hi = mid; }
+            *start = off0 + s_off[lo]; *end = off0 + s_off[lo + 1];
+            return h.first + lo;
+        }
+        const unsigned long long r = upper_rec(rec_off, n_recs, pq);
+        *start = rec_off[r]; *end = rec_off[r + 1];
+        return r;
+    };
+    // local index q <-> global position g0 + q; q = 0 is the group before the block (its minimum decides whether base opens a new row)
+    const long long g0 = (long long)base - 1;
+    const int n_ids = kEdgeBlock + w;                               // ids [0, n_ids): groups 0 .. kEdgeBlock, each spanning w ids
+    const int n_let = n_ids + k - 1;
+    unsigned int bad = 0;
+    for (int i = tid; i < n_let; i += 256) {
+        const long long g = g0 + i;
+        uint8_t cl = C_A;
+        if (g >= 0 && (unsigned long long)g < n_letters) {
+            cl = s_lut[letters[g]];
+            if (cl == C_N || cl == C_IUPAC) bad |= 2u; else if (cl > C_T) bad |= 1u;
+        }
+        s_cls[i] = cl & 3u;
+    }
+    __syncthreads();
+    {   // ids: a run of consecutive windows per thread, rolled
+        const int per = (n_ids + 255) / 256, i0 = tid * per, i1 = min(n_ids, i0 + per);
+        if (i0 < i1) {
+            const uint32_t mask = k == 16 ? 0xFFFFFFFFu : ((1u << (2 * k)) - 1u);
+            uint32_t fwd = 0, rc = 0;
+            for (int j = 0; j < k; j++) { const uint32_t c = s_cls[i0 + j]; fwd = (fwd << 2) | c; rc |= (3u - c) << (2 * j); }
+            for (int i = i0; ; ) {
+                const uint32_t id = rc < fwd ? rc : fwd;
+                s_key[0][i] = ((unsigned long long)id << 32) | (unsigned int)i;
+                if (++i >= i1) break;
+                const uint32_t c = s_cls[i + k - 1];
+                fwd = ((fwd << 2) | c) & mask;
+                rc = (rc >> 2) | ((3u - c) << (2 * (k - 1)));
+            }
+        }
+    }
+    __syncthreads();
+    // window minimum by doubling: after the pass with span p, key[i] = min of ids [i, i + p)
+    int cur = 0, p = 1;
+    while (2 * p <= w) {
+        for (int i = tid; i < n_ids; i += 256) {
+            const unsigned long long a = s_key[cur][i], b = i + p < n_ids ? s_key[cur][i + p] : ~0ull;
+            s_key[cur ^ 1][i] = b < a ? b : a;
+        }
+        __syncthreads();
+        cur ^= 1; p *= 2;
+    }
+    if (w > p) {
+        for (int i = tid; i <= kEdgeBlock; i += 256) {
+            const unsigned long long a = s_key[cur][i], b = s_key[cur][i + w - p];
+            s_key[cur ^ 1][i] = b < a ? b : a;
+        }
+        __syncthreads();
+        cur ^= 1;
+    }
+    const unsigned long long* best = s_key[cur];                    // best[q]: (id, local position) of the minimum of group q
+    unsigned long long off = WRITE ? block_off[blockIdx.x] : 0ull;
+    unsigned int mine = 0;
+    for (int j0 = 0; j0 < kEdgeBlock; j0 += 256) {
+        const int q = 1 + j0 + tid;
+        const unsigned long long pg = base + j0 + tid;
+        bool keep = false;
+        unsigned long long r = 0, start = 0, end = 0;
+        if (pg < n_out) {
+            r = rec_of32(pg, &start, &end);
+            keep = pg + (unsigned long long)(k + w - 1) <= end && (pg == start || (unsigned int)best[q] != (unsigned int)best[q - 1]);
+        }
+        if (!WRITE) { mine += keep; continue; }
+        const unsigned int bal = __ballot_sync(0xffffffffu, keep);
+        if (lane == 0) s_warp[warp] = __popc(bal);
+        __syncthreads();
+        unsigned int before = 0, total = 0;
+        for (int x = 0; x < 8; x++) { const unsigned int v = s_warp[x]; if (x < warp) before += v; total += v; }
+        if (keep) {
+            const unsigned long long o = off + before + __popc(bal & ((1u << lane) - 1u));
+            if (o < cap) { out_rec[o] = r; out_pos[o] = (unsigned long long)(g0 + (long long)(unsigned int)best[q]) - start; out_id[o] = best[q] >> 32; }
+        }
+        off += total;
+        __syncthreads();
+    }
+    if (!WRITE) {
+        if (tid == 0) s_total = 0;
+        __syncthreads();
+        for (int d = 16; d; d >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, d);
+        if (lane == 0 && mine) atomicAdd(&s_total, mine);
+        __syncthreads();
+        if (tid == 0) block_n[blockIdx.x] = s_total;
+        if (bad) atomicOr(bad_flag, bad);
+    }
+}
+
 }  // namespace kdb
