@@ -1247,6 +1247,33 @@ extern "C" int kdb_microbench_atomics(int device, size_t table_bytes, uint64_t n
         CK(cudaEventSynchronize(e1));
         CK(cudaEventElapsedTime(&ms, e0, e1));
         cudaFree(tab);
+    } else if (mode == 2 || mode == 3) {
+        // distributed shared memory: clusters of 8 (portable) / 16 (opt-in) CTAs, random red.shared::cluster over the cluster's tables
+        DevBuf sink;
+        CK(sink.alloc(4));
+        const int cs = mode == 2 ? 8 : 16;
+        const void* fn = mode == 2 ? (const void*)k_micro_atoms_cluster<8> : (const void*)k_micro_atoms_cluster<16>;
+        CK(cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, 65536));
+        if (cs == 16) CK(cudaFuncSetAttribute(fn, cudaFuncAttributeNonPortableClusterSizeAllowed, 1));
+        cudaLaunchConfig_t cfg{};
+        cudaLaunchAttribute at[1];
+        at[0].id = cudaLaunchAttributeClusterDimension;
+        at[0].val.clusterDim.x = cs; at[0].val.clusterDim.y = 1; at[0].val.clusterDim.z = 1;
+        cfg.gridDim = dim3((grid / cs) * cs); cfg.blockDim = dim3(threads); cfg.dynamicSmemBytes = 65536; cfg.attrs = at; cfg.numAttrs = 1;
+        unsigned int* sp = sink.as<unsigned int>();
+        uint32_t warm = per_thread / 8 + 1;
+        void* a0[2] = {&sp, &warm};
+        CK(cudaLaunchKernelExC(&cfg, fn, a0));
+        CK(cudaEventRecord(e0));
+        void* a1[2] = {&sp, (void*)&per_thread};
+        CK(cudaLaunchKernelExC(&cfg, fn, a1));
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        CK(cudaGetLastError());
+        *updates_per_s = (double)per_thread * cfg.gridDim.x * threads / (ms * 1e-3);
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
+        return KDB_OK;
     } else {
         unsigned int* sink = nullptr;
         CK(cudaMalloc(&sink, 4));

@@ -110,4 +110,27 @@ __global__ void __launch_bounds__(256) k_micro_atoms_shared(unsigned int* sink, 
     if (s == 0xffffffffu) sink[0] = s;
 }
 
+// mode 2 / 3: the same random shared-memory atomicAdd, but the table is spread over the shared memories of a thread-block
+// cluster (8 / 16 CTAs x 64 KiB): red.shared::cluster on distributed shared memory.  Decides whether a cluster-wide count
+// table (an 8- or 16-way partition instead of a 512-way one) could beat partition + count.
+template <int CSIZE>
+__global__ void __launch_bounds__(256) k_micro_atoms_cluster(unsigned int* sink, uint32_t per_thread) {
+    extern __shared__ unsigned int s_tab[];
+    for (int i = threadIdx.x; i < 16384; i += blockDim.x) s_tab[i] = 0;
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    uint32_t x = mix32(blockIdx.x * blockDim.x + threadIdx.x + 1u);
+    const uint32_t base = (uint32_t)__cvta_generic_to_shared(s_tab);
+    for (uint32_t i = 0; i < per_thread; i++) {
+        x = x * 1664525u + 1013904223u;
+        const uint32_t h = mix32(x);
+        uint32_t remote;
+        asm volatile("mapa.shared::cluster.u32 %0, %1, %2;" : "=r"(remote) : "r"(base + 4u * (h & 16383u)), "r"((h >> 14) & (uint32_t)(CSIZE - 1)));
+        asm volatile("red.relaxed.cluster.shared::cluster.add.u32 [%0], %1;" ::"r"(remote), "r"(1u) : "memory");
+    }
+    asm volatile("barrier.cluster.arrive.release.aligned;\nbarrier.cluster.wait.acquire.aligned;" ::: "memory");
+    unsigned int s = 0;
+    for (int i = threadIdx.x; i < 16384; i += blockDim.x) s += s_tab[i];
+    if (s == 0xffffffffu) sink[0] = s;
+}
+
 }  // namespace kdb
