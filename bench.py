@@ -322,6 +322,44 @@ def run_b200(args):
         dist.all_reduce(te, op=dist.ReduceOp.MAX)
     e2e_wall = te.item()
 
+    # ---- e2e on COMPRESSED input (f2): the same reads as a BGZF file in host memory -> kdb_feed_bgzf_host (compressed bytes
+    # over PCIe, inflate on the GPU) -> counts + stats on the host; beside it the host-inflate path on the same blob ---------
+    bgzf = None
+    if world == 1 and not args.no_bgzf:
+        import zlib
+        from concurrent.futures import ThreadPoolExecutor
+        from kmerdb_b200 import kdbfile, parse as kparse
+        n_bz = min(n_reads, args.bgzf_reads)
+        text_mv = memoryview(pin_text.array)[: n_bz * rb]
+        with ThreadPoolExecutor(max_workers=host_threads()) as ex:
+            blocks = list(ex.map(lambda o: kdbfile.bgzf_block(bytes(text_mv[o:o + 65280]), 1), range(0, n_bz * rb, 65280)))
+        blob = np.frombuffer(b"".join(blocks) + kdbfile._BGZF_EOF, dtype=np.uint8)
+        pin_blob = _native.PinnedBuffer(blob.size)
+        pin_blob.array[:] = blob
+
+        def step_bgzf():
+            prof.reset()
+            assert prof.feed_bgzf(pin_blob.array) == 0
+            assert prof.finish() == 0
+            prof.counts(out=counts_view)
+            return prof.stats(), prof.timing()
+        step_bgzf()
+        t0 = time.perf_counter()
+        for _ in range(3):
+            st_bz, tm_bz = step_bgzf()
+        dt_gpu = (time.perf_counter() - t0) / 3
+        assert st_bz["total_kmers"] == n_bz * (READ_LEN - k + 1)
+        t0 = time.perf_counter()
+        text_host = kparse._gunzip(blob.tobytes(), threads=host_threads())
+        prof.reset(); prof.feed(np.frombuffer(text_host, dtype=np.uint8)); assert prof.finish() == 0
+        prof.counts(out=counts_view)
+        dt_host = time.perf_counter() - t0
+        bgzf = {"value": n_bz * READ_LEN / dt_gpu, "unit": UNIT, "reads": n_bz, "h2d_bytes_per_step": int(blob.size), "text_bytes": n_bz * rb,
+                "compression_ratio": n_bz * rb / blob.size, "inflate_ms_per_step": tm_bz["inflate_ms"], "inflate_GBps_of_text": n_bz * rb / (tm_bz["inflate_ms"] * 1e-3) / 1e9,
+                "host_inflate_path": {"value": n_bz * READ_LEN / dt_host, "unit": UNIT, "threads": host_threads(),
+                                      "note": "the same BGZF blob inflated by zlib on the host threads, then fed uncompressed"}}
+        del pin_blob
+
     # ---- parity gate T3, driver-visible: the N-GPU result equals a 1-GPU job over the same reads -----------------
     t3 = None
     if world > 1:
@@ -389,6 +427,8 @@ def run_b200(args):
         }
         if t3 is not None:
             line["result_check"].update(t3)
+        if bgzf is not None:
+            line["e2e_bgzf"] = bgzf
         if not args.no_cpu_baseline:
             line.update(cpu_legs(k, args.ref_reads, args.cpu_reads))
         _emit(line)
@@ -427,6 +467,8 @@ def main():
     ap.add_argument("--cpu-reads", type=int, default=2_000_000, help="bounded sample for the C-port CPU leg")
     ap.add_argument("--ref-reads", type=int, default=2_000, help="bounded sample (reads per step) for the Python reference")
     ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-bgzf", action="store_true", help="skip the compressed-input leg (e2e_bgzf)")
+    ap.add_argument("--bgzf-reads", type=int, default=10_000_000, help="reads of the compressed-input leg")
     args = ap.parse_args()
     if args.warmup < 3 and args.impl == "b200":
         args.warmup = 3
