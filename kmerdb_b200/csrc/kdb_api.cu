@@ -853,6 +853,9 @@ extern "C" int kdb_refinalize(kdb_ctx* ctx) {
 }
 
 // ---- BGZF input: compressed bytes over PCIe, inflate on the device (kdb_inflate.cuh) ------------------------------------
+// a corrupt member can make the decoder read on past its payload before a check fires (at most 15 bits per output byte of a
+// 64 KiB member): the compressed buffer carries that much slack behind the last member
+constexpr size_t kInflateSlack = 160u << 10;
 static bool g_crc_table_loaded[64] = {false};
 static int load_crc_table(kdb_ctx* ctx, int device) {
     if (device >= 0 && device < 64 && g_crc_table_loaded[device]) return KDB_OK;
@@ -930,7 +933,7 @@ extern "C" int kdb_inflate_bgzf(int device, const uint8_t* raw, size_t n, uint8_
     kdb_bgzf_index(raw, n, mem.data(), nm, &nm, &text);
     CK(cudaSetDevice(device));
     DevBuf d_comp, d_out, d_mem, d_st;
-    CK(d_comp.alloc(n + 16)); CK(d_out.alloc(text + 16)); CK(d_mem.alloc(nm * sizeof(BgzfMember))); CK(d_st.alloc(nm * sizeof(unsigned int)));
+    CK(d_comp.alloc(n + kInflateSlack)); CK(d_out.alloc(text + 16)); CK(d_mem.alloc(nm * sizeof(BgzfMember))); CK(d_st.alloc(nm * sizeof(unsigned int)));
     CK(cudaMemcpy(d_comp.p, raw, n, cudaMemcpyHostToDevice));
     if (int rc = inflate_members(ctx, device, d_comp.as<uint8_t>(), mem.data(), nm, d_out.as<uint8_t>(), d_mem.as<BgzfMember>(), d_st.as<unsigned int>(), nullptr, 1)) return rc;
     std::vector<unsigned int> status(nm);
@@ -954,10 +957,10 @@ extern "C" int kdb_feed_bgzf_host(kdb_ctx* ctx, const uint8_t* raw, size_t n) {
     std::vector<kdb_bgzf_member_t> mem(nm);
     kdb_bgzf_index(raw, n, mem.data(), nm, &nm, &text);
     const size_t meta = nm * (sizeof(BgzfMember) + sizeof(unsigned int));
-    if (int rc = ensure(ctx, (void**)&ctx->comp_buf, &ctx->comp_cap, n + 64 + meta + 64, 1)) return rc;
+    if (int rc = ensure(ctx, (void**)&ctx->comp_buf, &ctx->comp_cap, n + kInflateSlack + meta + 64, 1)) return rc;
     if (int rc = ensure(ctx, (void**)&ctx->feed_buf, &ctx->feed_cap, text + 64, 1)) return rc;
     uint8_t* d_comp = ctx->comp_buf;
-    BgzfMember* d_mem = reinterpret_cast<BgzfMember*>(ctx->comp_buf + ((n + 64 + 15) & ~(size_t)15));
+    BgzfMember* d_mem = reinterpret_cast<BgzfMember*>(ctx->comp_buf + ((n + kInflateSlack + 15) & ~(size_t)15));
     unsigned int* d_st = reinterpret_cast<unsigned int*>(d_mem + nm);
     if (int rc = begin_feed(ctx)) return rc;
     // pieces of about 32 MiB of compressed bytes, cut at member borders
