@@ -126,8 +126,9 @@ __global__ void __launch_bounds__(kThreads, 4) k2s_encode(const EncodeParams2 P,
     __shared__ unsigned long long s_red[kThreads / 32][10];
     __shared__ __align__(8) unsigned long long s_bar[2];
     __shared__ unsigned int s_next[2];
-    __shared__ unsigned long long s_pre_ls, s_pre_hdr, s_head_rec;
-    __shared__ unsigned int s_pre_last, s_head[3];
+    __shared__ unsigned long long s_pre_ls, s_pre_hdr, s_head_rec, s_carry_ls, s_carry_hdr;
+    __shared__ unsigned int s_pre_last, s_head[3], s_carry_last;
+    __shared__ unsigned int s_prev[6];                               // the tile whose packed words still wait in s_out: index, letters, olen, oqlen, meta, valid
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int k = P.k, skip_n = P.skip_n;
@@ -153,21 +154,53 @@ __global__ void __launch_bounds__(kThreads, 4) k2s_encode(const EncodeParams2 P,
         tma_load_2d(smem_u32(&s_text2[b][0]), &tmap, 0, (int)(tile * (unsigned int)kThreads), bar);
     };
 
-    unsigned int tile = 0;
+    // The next tile's index travels with its text: thread 0 writes s_next[slot] BEFORE it arrives on the slot's mbarrier
+    // (release), every thread reads it AFTER the wait on that mbarrier (acquire) — no CTA barrier is spent on the hand-over.
+    // Past the last tile nothing is loaded: a plain arrive completes the phase so that the waiters see the end.
+    auto take_ticket = [&](unsigned int slot, int b) {
+        const unsigned int nxt = atomicAdd(P.ticket, 1u);
+        s_next[slot] = nxt;
+        if (nxt < P.n_tiles) stage(nxt, b);
+        else asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar0 + 8u * (uint32_t)b) : "memory");
+    };
     if (tid == 0) {
         mbar_init(bar0, 1); mbar_init(bar0 + 8, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
-        tile = atomicAdd(P.ticket, 1u);
-        s_next[0] = tile;
-        if (tile < P.n_tiles) stage(tile, 0);
+        s_carry_ls = P.carry_in->ls_total; s_carry_hdr = P.carry_in->hdr_total; s_carry_last = P.carry_in->last;
+        s_prev[5] = 0;
     }
     for (int i = tid; i < kPackCodes + 2 * kPackBits; i += kThreads) s_out[i] = 0;
     __syncthreads();
-    tile = s_next[0];
+    if (tid == 0) take_ticket(0, 0);
+    // The packed words of a tile leave shared memory one iteration later, while warp 0 looks back for the next tile
+    // (see below); after the loop the last tile is flushed by everybody.
+    auto copy_out = [&](int first_thread, int n_threads) {
+        const uint32_t letters = s_prev[1];
+        uint32_t* dst = P.packed + (size_t)s_prev[0] * kPackStride;
+        const int t = tid - first_thread;
+        if (t == 0) {
+            dst[0] = letters;
+            TileRec tr;
+            const bool has_b = (s_prev[4] & 0x200u) != 0;
+            tr.head_len = has_b ? s_head[0] : s_prev[2]; tr.head_qlen = has_b ? s_head[1] : s_prev[3];
+            tr.tail_len = s_prev[2]; tr.tail_qlen = s_prev[3];
+            tr.flags = has_b ? s_head[2] : 0u; tr.pad = 0; tr.head_rec = has_b ? s_head_rec : 0ull;
+            P.trec[s_prev[0]] = tr;
+        }
+        const uint32_t cw = (letters + 15) >> 4, bw = (letters + 31) >> 5;
+        // (the words are cleared as they leave: the tile in work ORs into them after two more barriers)
+        for (uint32_t i = t; i < cw; i += n_threads) { dst[kPackHdr + i] = s_out[i]; s_out[i] = 0; }
+        for (uint32_t i = t; i < bw; i += n_threads) {
+            dst[kPackHdr + kPackCodes + i] = s_out[kPackCodes + i]; s_out[kPackCodes + i] = 0;
+            dst[kPackHdr + kPackCodes + kPackBits + i] = s_out[kPackCodes + kPackBits + i]; s_out[kPackCodes + kPackBits + i] = 0;
+        }
+    };
     int buf = 0;
-    for (unsigned int it = 0; tile < P.n_tiles; it++, buf ^= 1) {
-        const unsigned long long tile0 = P.lo + (unsigned long long)tile * kTile;
+    for (unsigned int it = 0;; it++, buf ^= 1) {
         mbar_wait(bar0 + 8u * (uint32_t)buf, (it >> 1) & 1u);
+        const unsigned int tile = s_next[it & 1];
+        if (tile >= P.n_tiles) break;
+        const unsigned long long tile0 = P.lo + (unsigned long long)tile * kTile;
         s_text = s_text2[buf];
 
         const unsigned long long a = tile0 + (unsigned long long)tid * kChunk;
@@ -258,15 +291,15 @@ __global__ void __launch_bounds__(kThreads, 4) k2s_encode(const EncodeParams2 P,
                 const unsigned long long in = ex + (((unsigned long long)tot.ls << 30) | (unsigned long long)tot.hdr);
                 const unsigned int in_last = tot.last ? tot.last : ex_last;
                 *reinterpret_cast<volatile unsigned long long*>(&P.look[tile].w0) = (2ull << 62) | ((unsigned long long)in_last << 60) | in;
-                const unsigned long long c_ls = P.carry_in->ls_total, c_hdr = P.carry_in->hdr_total;
-                const unsigned int c_last = P.carry_in->last;
+                const unsigned long long c_ls = s_carry_ls, c_hdr = s_carry_hdr;
+                const unsigned int c_last = s_carry_last;
                 if (tile == P.n_tiles - 1) {
                     P.carry_out->ls_total = c_ls + (in >> 30); P.carry_out->hdr_total = c_hdr + (in & 0x3FFFFFFFull);
                     P.carry_out->last = in_last ? in_last : c_last; P.carry_out->fq_rec_base = fq_base;
                 }
                 s_pre_ls = c_ls + (ex >> 30); s_pre_hdr = c_hdr + (ex & 0x3FFFFFFFull); s_pre_last = ex_last ? ex_last : c_last;
             }
-        }
+        } else if (s_prev[5]) copy_out(32, kThreads - 32);              // warps 1..7 meanwhile: the packed words of the tile before leave
         __syncthreads();
         const unsigned long long ls_before = s_pre_ls + (inc.ls - g.ls);
         unsigned long long hdr_before = s_pre_hdr + (inc.hdr - g.hdr);
@@ -472,11 +505,10 @@ __global__ void __launch_bounds__(kThreads, 4) k2s_encode(const EncodeParams2 P,
         // ticket holder publishes its aggregate a few microseconds after taking the ticket, so a tile rarely finds a predecessor
         // that has not published yet (with the ticket taken a tile ahead, 42 % of the kernel's samples sat in that wait). -----------
         if (tid == 0) {
-            const unsigned int nxt = atomicAdd(P.ticket, 1u);
-            s_next[(it + 1) & 1] = nxt;
-            if (nxt < P.n_tiles) stage(nxt, buf ^ 1);
+            take_ticket((it + 1) & 1, buf ^ 1);
+            s_prev[0] = tile; s_prev[1] = tile_total.letters; s_prev[2] = tile_total.olen; s_prev[3] = tile_total.oqlen; s_prev[4] = tile_total.meta; s_prev[5] = 1;
         }
-        const uint32_t off = start.letters, tile_letters = tile_total.letters;
+        const uint32_t off = start.letters;
         if (seen_b) {
             // my first record start closes the record that was open when my chunk began
             const uint32_t cl = start.olen + first_len, cq = start.oqlen + first_qlen;
@@ -508,29 +540,9 @@ __global__ void __launch_bounds__(kThreads, 4) k2s_encode(const EncodeParams2 P,
             or_bits<2>(s_out + kPackCodes, off, y, E.n);
             or_bits<2>(s_out + kPackCodes + kPackBits, off, z, E.n);
         }
-        __syncthreads();
-        // ---- write the packed region: only the words the letters of this tile occupy ------------
-        {
-            uint32_t* dst = P.packed + (size_t)tile * kPackStride;
-            if (tid == 0) {
-                dst[0] = tile_letters;
-                TileRec tr;
-                const bool has_b = (tile_total.meta & 0x200u) != 0;
-                tr.head_len = has_b ? s_head[0] : tile_total.olen; tr.head_qlen = has_b ? s_head[1] : tile_total.oqlen;
-                tr.tail_len = tile_total.olen; tr.tail_qlen = tile_total.oqlen;
-                tr.flags = has_b ? s_head[2] : 0u; tr.pad = 0; tr.head_rec = has_b ? s_head_rec : 0ull;
-                P.trec[tile] = tr;
-            }
-            const uint32_t cw = (tile_letters + 15) >> 4, bw = (tile_letters + 31) >> 5;
-            // (the words are cleared as they leave: the next tile ORs into them after its own scans' barriers)
-            for (uint32_t i = tid; i < cw; i += kThreads) { dst[kPackHdr + i] = s_out[i]; s_out[i] = 0; }
-            for (uint32_t i = tid; i < bw; i += kThreads) {
-                dst[kPackHdr + kPackCodes + i] = s_out[kPackCodes + i]; s_out[kPackCodes + i] = 0;
-                dst[kPackHdr + kPackCodes + kPackBits + i] = s_out[kPackCodes + kPackBits + i]; s_out[kPackCodes + kPackBits + i] = 0;
-            }
-        }
-        tile = s_next[(it + 1) & 1];
     }
+    __syncthreads();
+    if (s_prev[5]) copy_out(0, kThreads);
 
     // ---- CTA reduction of the fused scalars --------------------------------------------------------
     unsigned long long v[8] = {0, letters_total, Y.mono[0], Y.mono[1], Y.mono[2], Y.mono[3], Y.nwin, 0};

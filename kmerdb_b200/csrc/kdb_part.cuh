@@ -466,9 +466,9 @@ __global__ void __launch_bounds__(kPartThreads, 3) k3s_partition(const PartParam
 
         // ---- the slots leave as payload runs, four entries per thread, and are reset to 0xFFFF ------------------------------
 #pragma unroll 4
-        for (int i = 0; i < NB * Q / kPartThreads; i++) {
-            const uint32_t j = (uint32_t)tid + (uint32_t)i * kPartThreads, b = j / (uint32_t)Q, r = 4u * (j % (uint32_t)Q);
-            const uint32_t c = s_cnt[b];
+        for (int i = 0; i < (NB * Q + kPartThreads - 1) / kPartThreads; i++) {
+            const uint32_t j = (uint32_t)tid + (uint32_t)i * kPartThreads, b = min(j / (uint32_t)Q, (uint32_t)(NB - 1)), r = 4u * (j % (uint32_t)Q);
+            const uint32_t c = j < (uint32_t)(NB * Q) ? s_cnt[b] : 0u;
             if (r < c) {
                 const unsigned long long v = slot64[j];
                 slot64[j] = ~0ull;

@@ -3,7 +3,7 @@
 # usage: gpurun --timeout 1200 -- 'bash scripts/gpu_ab.sh TAG "" "KDB_TWO_SWEEP=1"'
 TAG=$1; shift
 O=gpurun_out; mkdir -p $O
-timeout 1500 python -m pytest tests -m gpu -x -q --timeout 900 > $O/pytest_$TAG.log 2>&1; echo "pytest exit $?" >> $O/pytest_$TAG.log
+timeout 1500 python -m pytest tests -m gpu -x -q --timeout 900 ${PYTEST_K:+-k "$PYTEST_K"} > $O/pytest_$TAG.log 2>&1; echo "pytest exit $?" >> $O/pytest_$TAG.log
 tail -4 $O/pytest_$TAG.log
 i=0
 for V in "$@"; do
