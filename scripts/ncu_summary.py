@@ -42,11 +42,14 @@ root = os.path.join(os.path.dirname(os.path.abspath(__file__)), "..")
 json.dump(out, open(os.path.join(root, "profiles", "ncu_full_%s.json" % tag), "w"), indent=1)
 for name, e in out.items():
     print(name, json.dumps(e))
+traffic = {}
 for name, e in out.items():
-    if name.startswith("k3p_partition<12") and "--no-traffic" not in sys.argv:
-        rd, wr = e["dram__bytes_read.sum"] * 1e6, e["dram__bytes_write.sum"] * 1e6
-        t = {"kernel": name.replace(" ", ""), "source": "ncu --set full --clock-control none, profiles/ncu_full_%s.json (%d bytes of text per launch)" % (tag, text_bytes),
-             "text_bytes_per_launch": text_bytes, "dram_bytes_read": rd, "dram_bytes_write": wr, "dram_bytes_per_launch": rd + wr,
-             "dram_bytes_per_text_byte": (rd + wr) / text_bytes}
-        json.dump(t, open(os.path.join(root, "profiles", "traffic_k3p_partition.json"), "w"), indent=1)
-        print("traffic", t["dram_bytes_per_text_byte"])
+    if "--no-traffic" in sys.argv or "dram__bytes_read.sum" not in e:
+        continue
+    rd, wr = e["dram__bytes_read.sum"] * 1e6, e["dram__bytes_write.sum"] * 1e6
+    traffic[name.split("<")[0]] = {"kernel": name.replace(" ", ""), "text_bytes_per_launch": text_bytes, "dram_bytes_read": rd, "dram_bytes_write": wr,
+                                   "dram_bytes_per_launch": rd + wr, "dram_bytes_per_text_byte": (rd + wr) / text_bytes}
+if traffic:
+    traffic["source"] = "ncu --set full --clock-control none, profiles/ncu_full_%s.json (%d bytes of text per launch)" % (tag, text_bytes)
+    json.dump(traffic, open(os.path.join(root, "profiles", "traffic_%s.json" % tag), "w"), indent=1)
+    print("traffic", {k: round(v["dram_bytes_per_text_byte"], 3) for k, v in traffic.items() if isinstance(v, dict)})
