@@ -302,7 +302,7 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
         if (!rc) rc = occupancy_grid(ctx->part_kernel, kPartThreads, dyn, &ctx->part_grid);
         if ((e = cudaMalloc(&ctx->cursor, 2 * ctx->n_buckets * sizeof(unsigned int))) != cudaSuccess) return fail("cudaMalloc cursor", e);
     }
-    if (!rc && ctx->single_pass) rc = ctx->fastq ? occupancy_grid(k2s_encode<true>, kEncThreads, 0, &ctx->encode_grid) : occupancy_grid(k2s_encode<false>, kEncThreads, 0, &ctx->encode_grid);
+    if (!rc && ctx->single_pass) rc = ctx->fastq ? occupancy_grid(k2s_encode<true>, kThreads, 0, &ctx->encode_grid) : occupancy_grid(k2s_encode<false>, kThreads, 0, &ctx->encode_grid);
     else if (!rc) rc = ctx->fastq ? occupancy_grid(k2_encode<true>, kThreads, 0, &ctx->encode_grid) : occupancy_grid(k2_encode<false>, kThreads, 0, &ctx->encode_grid);
     if (rc) { kdb_destroy(ctx); return nullptr; }
     if (reset_state(ctx)) { g_last_error = ctx->err; kdb_destroy(ctx); return nullptr; }
@@ -525,8 +525,8 @@ static int run_pass2(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, u
     CK(cudaEventRecord(ctx->ev[2], ctx->s_compute));
     {
         const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->encode_grid);
-        if (ctx->fastq) k2s_encode<true><<<grid, kEncThreads, 0, ctx->s_compute>>>(P, tmap);
-        else k2s_encode<false><<<grid, kEncThreads, 0, ctx->s_compute>>>(P, tmap);
+        if (ctx->fastq) k2s_encode<true><<<grid, kThreads, 0, ctx->s_compute>>>(P, tmap);
+        else k2s_encode<false><<<grid, kThreads, 0, ctx->s_compute>>>(P, tmap);
         CK(cudaGetLastError());
     }
     CK(cudaEventRecord(ctx->ev[6], ctx->s_compute));

@@ -10,11 +10,14 @@
 //   * record lengths (min / max read length, the short-record raise of kmer.py:461-463, FASTQ sequence/quality agreement)
 //     ride on the CTA scan of the chunk tails: a record that closes inside the tile is checked on the spot, the two records
 //     that cross the tile borders are left in a TileRec for k4_stitch_records — no per-record array, no global atomics;
-//   * the CTA is warp-specialised: a producer warp takes the tickets, issues the TMA loads, computes each tile's line aggregate and
-//     does the look-back one tile ahead of the eight consumer warps, which find text and prefix ready behind one mbarrier;
-//   * the text tile is staged by TMA: the producer issues cp.async.bulk.tensor.2d into the double buffer, completion
+//   * the text tile is staged by TMA: one elected thread issues cp.async.bulk.tensor.2d into the double buffer, completion
 //     on an mbarrier; the tensor map views the text as [n / 64][64 B] with CU_TENSOR_MAP_SWIZZLE_64B, which is exactly the
 //     conflict-free LDS.128 layout (16-byte group q of chunk t at q ^ ((t >> 1) & 3)).
+// Tried and rejected (r02g / r02h, measured on the same workload, encode ms per 10 M reads; this kernel: 3.38): a warp-
+// specialised CTA — a ninth warp owning tickets, TMA, the tile's line aggregate and the look-back one tile ahead, eight
+// consumer warps on a named barrier with two barriers per tile.  Correct (all parity tests), but the producer's chain
+// (ticket atomic -> TMA -> 16 KiB aggregate by ONE warp -> look-back) is longer than a tile: 4.51 ms with two text buffers
+// (consumers 18 % of their samples in the ready-wait), 7.46 ms with three (tickets two tiles ahead: the early-ticket wait is back).
 #pragma once
 #include <cuda.h>
 
@@ -60,12 +63,6 @@ __device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map
                  ::"r"(dst), "l"(reinterpret_cast<uint64_t>(map)), "r"(c0), "r"(c1), "r"(bar) : "memory");
 }
 
-// The tokeniser CTA = 8 consumer warps (one 64-byte chunk per thread) + 1 producer warp (tickets, TMA, look-back).  The
-// consumers synchronise among themselves on named barrier 1; the producer never joins it.
-constexpr int kEncThreads = kThreads + 32;
-__device__ __forceinline__ void cons_sync() { asm volatile("bar.sync 1, %0;" ::"n"(kThreads) : "memory"); }
-__device__ __forceinline__ void mbar_arrive(uint32_t bar) { asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory"); }
-
 // ---- chunk tails with the open-record lengths -------------------------------------------------------------------
 struct TailAgg2 {
     uint32_t codes;    // 2-bit codes of the last (up to 15) letters, most recent letter in the low bits
@@ -109,7 +106,7 @@ __device__ __forceinline__ TailAgg2 tail2_scan_exclusive(TailAgg2 v, TailAgg2* s
 #pragma unroll
     for (int d = 1; d < 32; d <<= 1) { const TailAgg2 o = tail2_shfl_up<FASTQ>(v, d); if (lane >= d) v = tail2_combine<FASTQ>(o, v); }
     if (lane == 31) sm[warp] = v;
-    cons_sync();
+    __syncthreads();
     TailAgg2 pre = ident, tot = ident;
 #pragma unroll
     for (int w = 0; w < kThreads / 32; w++) {
@@ -124,7 +121,7 @@ __device__ __forceinline__ TailAgg2 tail2_scan_exclusive(TailAgg2 v, TailAgg2* s
 }
 
 template <bool FASTQ>
-__global__ void __launch_bounds__(kEncThreads, 3) k2s_encode(const EncodeParams2 P, const __grid_constant__ CUtensorMap tmap) {
+__global__ void __launch_bounds__(kThreads, 4) k2s_encode(const EncodeParams2 P, const __grid_constant__ CUtensorMap tmap) {
     __shared__ __align__(1024) uint32_t s_text2[2][kTile / 4];     // TMA destinations (64-byte swizzle: 512-byte pattern)
     __shared__ uint32_t s_out[kPackCodes + 2 * kPackBits];
     __shared__ uint8_t s_lut[256];
@@ -132,14 +129,16 @@ __global__ void __launch_bounds__(kEncThreads, 3) k2s_encode(const EncodeParams2
     __shared__ TailAgg2 s_tail[kThreads / 32];
     __shared__ TailAgg2 s_seed;
     __shared__ unsigned long long s_red[kThreads / 32][10];
-    __shared__ __align__(8) unsigned long long s_bar[6];             // mbarriers per text buffer: full (TMA landed), ready (prefix known), empty (text consumed)
-    __shared__ unsigned long long s_slot_ls[2], s_slot_hdr[2], s_head_rec;
-    __shared__ unsigned int s_slot_tile[2], s_slot_last[2], s_head[3];
+    __shared__ __align__(8) unsigned long long s_bar[2];
+    __shared__ unsigned int s_next[2];
+    __shared__ unsigned long long s_pre_ls, s_pre_hdr, s_head_rec, s_carry_ls, s_carry_hdr;
+    __shared__ unsigned int s_pre_last, s_head[3], s_carry_last;
     __shared__ unsigned int s_prev[6];                               // the tile whose packed words still wait in s_out: index, letters, olen, oqlen, meta, valid
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int k = P.k, skip_n = P.skip_n;
     const uint32_t kmask = (1u << k) - 1u;
+    s_lut[tid] = c_class_lut[tid];
 
     Tally Y;
     Y.mono[0] = Y.mono[1] = Y.mono[2] = Y.mono[3] = 0; Y.nwin = 0; Y.err = 0;
@@ -152,99 +151,112 @@ __global__ void __launch_bounds__(kEncThreads, 3) k2s_encode(const EncodeParams2
     auto byte_at = [&](uint32_t p) -> uint8_t { return (uint8_t)(s_text[16 * tid + 4 * ((p >> 4) ^ swz) + ((p >> 2) & 3)] >> (8 * (p & 3))); };
     const unsigned long long fq_base = P.carry_in->fq_rec_base;
     const uint32_t bar0 = smem_u32(&s_bar[0]);
-    auto bar_full = [&](int b) -> uint32_t { return bar0 + 8u * (uint32_t)b; };
-    auto bar_ready = [&](int b) -> uint32_t { return bar0 + 16u + 8u * (uint32_t)b; };
-    auto bar_empty = [&](int b) -> uint32_t { return bar0 + 32u + 8u * (uint32_t)b; };
+    // the whole tile in one TMA request; rows past the end of the pass arrive as zeros
+    auto stage = [&](unsigned int tile, int b) {
+        const uint32_t bar = bar0 + 8u * (uint32_t)b;
+        asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
+        mbar_expect_tx(bar, kTile);
+        tma_load_2d(smem_u32(&s_text2[b][0]), &tmap, 0, (int)(tile * (unsigned int)kThreads), bar);
+    };
+
+    // The next tile's index travels with its text: thread 0 writes s_next[slot] BEFORE it arrives on the slot's mbarrier
+    // (release), every thread reads it AFTER the wait on that mbarrier (acquire) — no CTA barrier is spent on the hand-over.
+    // Past the last tile nothing is loaded: a plain arrive completes the phase so that the waiters see the end.
+    auto take_ticket = [&](unsigned int slot, int b) {
+        const unsigned int nxt = atomicAdd(P.ticket, 1u);
+        s_next[slot] = nxt;
+        if (nxt < P.n_tiles) stage(nxt, b);
+        else asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar0 + 8u * (uint32_t)b) : "memory");
+    };
     if (tid == 0) {
-        for (int i = 0; i < 6; i++) mbar_init(bar0 + 8u * (uint32_t)i, 1);
+        mbar_init(bar0, 1); mbar_init(bar0 + 8, 1);
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
+        s_carry_ls = P.carry_in->ls_total; s_carry_hdr = P.carry_in->hdr_total; s_carry_last = P.carry_in->last;
         s_prev[5] = 0;
     }
-    for (int i = tid; i < kPackCodes + 2 * kPackBits; i += kEncThreads) s_out[i] = 0;
-    if (tid < 256) s_lut[tid] = c_class_lut[tid];
+    for (int i = tid; i < kPackCodes + 2 * kPackBits; i += kThreads) s_out[i] = 0;
     __syncthreads();
+    if (tid == 0) take_ticket(0, 0);
+    // The packed words of a tile leave shared memory one iteration later, while warp 0 looks back for the next tile
+    // (see below); after the loop the last tile is flushed by everybody.
+    auto copy_out = [&](int first_thread, int n_threads) {
+        const uint32_t letters = s_prev[1];
+        uint32_t* dst = P.packed + (size_t)s_prev[0] * kPackStride;
+        const int t = tid - first_thread;
+        if (t == 0) {
+            dst[0] = letters;
+            TileRec tr;
+            const bool has_b = (s_prev[4] & 0x200u) != 0;
+            tr.head_len = has_b ? s_head[0] : s_prev[2]; tr.head_qlen = has_b ? s_head[1] : s_prev[3];
+            tr.tail_len = s_prev[2]; tr.tail_qlen = s_prev[3];
+            tr.flags = has_b ? s_head[2] : 0u; tr.pad = 0; tr.head_rec = has_b ? s_head_rec : 0ull;
+            P.trec[s_prev[0]] = tr;
+        }
+        const uint32_t cw = (letters + 15) >> 4, bw = (letters + 31) >> 5;
+        // (the words are cleared as they leave: the tile in work ORs into them after two more barriers)
+        for (uint32_t i = t; i < cw; i += n_threads) { dst[kPackHdr + i] = s_out[i]; s_out[i] = 0; }
+        for (uint32_t i = t; i < bw; i += n_threads) {
+            dst[kPackHdr + kPackCodes + i] = s_out[kPackCodes + i]; s_out[kPackCodes + i] = 0;
+            dst[kPackHdr + kPackCodes + kPackBits + i] = s_out[kPackCodes + kPackBits + i]; s_out[kPackCodes + kPackBits + i] = 0;
+        }
+    };
+    int buf = 0;
+    for (unsigned int it = 0;; it++, buf ^= 1) {
+        mbar_wait(bar0 + 8u * (uint32_t)buf, (it >> 1) & 1u);
+        const unsigned int tile = s_next[it & 1];
+        if (tile >= P.n_tiles) break;
+        const unsigned long long tile0 = P.lo + (unsigned long long)tile * kTile;
+        s_text = s_text2[buf];
 
-    if (warp == kThreads / 32) {
-        // ================= producer warp: ticket -> TMA -> tile aggregate -> look-back -> prefix in the slot =================
-        // It runs one tile ahead of the consumers, so a tile's aggregate and inclusive prefix are published about a tile time
-        // before any successor asks for them: the look-back almost never finds a predecessor that has not published, and the
-        // consumers never wait for it (with the look-back inside the consumers' path 20 % of their samples sat in that wait).
-        const unsigned long long c_ls = P.carry_in->ls_total, c_hdr = P.carry_in->hdr_total;
-        const unsigned int c_last = P.carry_in->last;
-        int b = 0;
-        for (unsigned int it = 0;; it++, b ^= 1) {
-            if (it >= 2) mbar_wait(bar_empty(b), ((it >> 1) - 1u) & 1u);            // the consumers are done with the text in this buffer
-            unsigned int tile = 0;
-            if (lane == 0) tile = atomicAdd(P.ticket, 1u);
-            tile = __shfl_sync(0xffffffffu, tile, 0);
-            if (tile >= P.n_tiles) {
-                if (lane == 0) { s_slot_tile[b] = tile; mbar_arrive(bar_ready(b)); }
-                break;
+        const unsigned long long a = tile0 + (unsigned long long)tid * kChunk;
+        const int lim = a >= P.hi ? 0 : (P.hi - a >= (unsigned long long)kChunk ? kChunk : (int)(P.hi - a));
+        if (lim > 0 && lim < kChunk) {
+            // the ragged last row of the feed is not part of the tensor (zeros arrived): its owner copies it by hand
+            uint32_t* mine = s_text2[buf] + 16 * tid;
+            for (int j = 0; j < lim; j++) {
+                uint32_t* w = mine + 4 * (((uint32_t)j >> 4) ^ swz) + ((j >> 2) & 3);
+                *w |= (uint32_t)P.feed[a + j] << (8 * (j & 3));
             }
-            if (lane == 0) {
-                asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
-                mbar_expect_tx(bar_full(b), kTile);
-                tma_load_2d(smem_u32(&s_text2[b][0]), &tmap, 0, (int)(tile * (unsigned int)kThreads), bar_full(b));   // rows past the end of the pass arrive as zeros
-            }
-            mbar_wait(bar_full(b), (it >> 1) & 1u);
-            uint32_t* const txt = s_text2[b];
-            const unsigned long long tile0 = P.lo + (unsigned long long)tile * kTile;
-            // line aggregate of the tile: lane l scans chunks l, l + 32, ..., l + 224 (the consumers' chunk layout: conflict-free LDS.128)
-            unsigned int ls = 0, hdr = 0, last_chunk = 0, last_cls = 0;
-#pragma unroll 2
-            for (int j = 0; j < kThreads / 32; j++) {
-                const int c = lane + 32 * j;
-                const uint32_t sz = ((uint32_t)c >> 1) & 3u;
-                const unsigned long long a = tile0 + (unsigned long long)c * kChunk;
-                const int lim = a >= P.hi ? 0 : (P.hi - a >= (unsigned long long)kChunk ? kChunk : (int)(P.hi - a));
-                if (lim > 0 && lim < kChunk) {
-                    // the ragged last row of the feed is not part of the tensor (zeros arrived): copied by hand
-                    for (int q = 0; q < lim; q++) txt[16 * c + 4 * (((uint32_t)q >> 4) ^ sz) + ((q >> 2) & 3)] |= (uint32_t)P.feed[a + q] << (8 * (q & 3));
-                }
-                if (lim == 0) continue;
-                uint8_t prev = '\n';
-                if (a > 0) {
-                    if (c > 0) { const uint32_t pz = ((uint32_t)(c - 1) >> 1) & 3u; prev = (uint8_t)(txt[16 * (c - 1) + 4 * (3u ^ pz) + 3] >> 24); }
-                    else prev = P.feed[a - 1];
-                }
-                unsigned long long lf = 0;
+        }
+        uint8_t prev = '\n';
+        if (lim > 0 && a > 0) {
+            // last byte of the chunk before mine: my neighbour's chunk in shared memory, or the text before the tile
+            if (tid > 0) { const uint32_t sz = ((uint32_t)(tid - 1) >> 1) & 3u; prev = (uint8_t)(s_text[16 * (tid - 1) + 4 * (3u ^ sz) + 3] >> 24); }
+            else prev = P.feed[a - 1];
+        }
+
+        // ---- phase A: bit masks of my chunk; phase B: line starts -> CTA scan ---------------------
+        const ChunkMasks M = chunk_masks(quad);      // zero fill beyond lim is neither LF nor a letter
+        LineAgg g{0, 0, 0};
+        if (lim > 0) {
+            unsigned long long lsm = ((M.lf << 1) | (prev == '\n' ? 1ull : 0ull)) & ones64((uint32_t)lim);
+            g.ls = __popcll(lsm);
+            if (!FASTQ && lsm) {
+                const uint32_t top = 63 - __clzll(lsm);
+                g.last = byte_at(top) == '>' ? 2u : 1u;
+                while (lsm) { const uint32_t p = __ffsll(lsm) - 1; lsm &= lsm - 1; g.hdr += byte_at(p) == '>' ? 1u : 0u; }
+            } else if (lsm) g.last = 1u;
+        }
+        LineAgg inc = g, warp_pre{0, 0, 0}, tot{0, 0, 0};
 #pragma unroll
-                for (int q = 0; q < 4; q++) {
-                    const uint4 v4 = *reinterpret_cast<const uint4*>(txt + 16 * c + 4 * ((uint32_t)q ^ sz));
-                    const uint32_t m16 = nib(eqmask(v4.x, 0x0A0A0A0Au)) | (nib(eqmask(v4.y, 0x0A0A0A0Au)) << 4) | (nib(eqmask(v4.z, 0x0A0A0A0Au)) << 8) |
-                                         (nib(eqmask(v4.w, 0x0A0A0A0Au)) << 12);
-                    lf |= (unsigned long long)m16 << (16 * q);
-                }
-                unsigned long long lsm = ((lf << 1) | (prev == '\n' ? 1ull : 0ull)) & ones64((uint32_t)lim);
-                if (!lsm) continue;
-                ls += __popcll(lsm);
-                unsigned int cls = 1;
-                if (!FASTQ) {
-                    const uint32_t top = 63 - __clzll(lsm);
-                    auto byte_c = [&](uint32_t pp) -> uint8_t { return (uint8_t)(txt[16 * c + 4 * ((pp >> 4) ^ sz) + ((pp >> 2) & 3)] >> (8 * (pp & 3))); };
-                    cls = byte_c(top) == '>' ? 2u : 1u;
-                    while (lsm) { const uint32_t pp = __ffsll(lsm) - 1; lsm &= lsm - 1; hdr += byte_c(pp) == '>' ? 1u : 0u; }
-                }
-                last_chunk = (unsigned int)c + 1; last_cls = cls;                 // (j ascends: the last assignment is this lane's right-most)
-            }
-            __syncwarp();
-            // warp totals; `last` = class of the right-most line start of the tile
-            unsigned int key = (last_chunk << 2) | last_cls;
+        for (int d = 1; d < 32; d <<= 1) { const LineAgg o = shfl_up_agg(inc, d); if (lane >= d) inc = combine(o, inc); }
+        if (lane == 31) s_scan[warp] = inc;
+        __syncthreads();
 #pragma unroll
-            for (int d = 16; d; d >>= 1) {
-                ls += __shfl_xor_sync(0xffffffffu, ls, d); hdr += __shfl_xor_sync(0xffffffffu, hdr, d);
-                const unsigned int o = __shfl_xor_sync(0xffffffffu, key, d); key = o > key ? o : key;
-            }
-            const unsigned int tot_last = key & 3u;
-            const unsigned long long tot_pack = ((unsigned long long)ls << 30) | (unsigned long long)hdr;
-            // ---- decoupled look-back: what came before this tile -------------------------------------------------------
-            // Every lane polls four predecessors (128 tiles per round, nearest first).  The sum runs back to the nearest tile that
-            // already holds an inclusive prefix; everything nearer contributes its aggregate.  All of them hold earlier tickets,
-            // so they are running or done: the spin cannot starve.
+        for (int w = 0; w < kThreads / 32; w++) { const LineAgg t = s_scan[w]; if (w < warp) warp_pre = combine(warp_pre, t); tot = combine(tot, t); }
+        inc = combine(warp_pre, inc);
+
+        // ---- decoupled look-back (warp 0): what came before this tile ---------------------------------------------
+        // Every lane polls four predecessors (128 tiles per round, nearest first).  The sum runs back to the nearest tile that
+        // already holds an inclusive prefix; everything nearer contributes its aggregate.  All of them hold earlier tickets,
+        // so they are running or done: the spin cannot starve.
+        if (warp == 0) {
             unsigned long long ex = 0;                                  // [59:30] line starts, [29:0] title lines before this tile, in this pass
             unsigned int ex_last = 0;
             if (tile != 0) {
-                if (lane == 0) *reinterpret_cast<volatile unsigned long long*>(&P.look[tile].w0) = (1ull << 62) | ((unsigned long long)tot_last << 60) | tot_pack;
+                if (lane == 0)
+                    *reinterpret_cast<volatile unsigned long long*>(&P.look[tile].w0) =
+                        (1ull << 62) | ((unsigned long long)tot.last << 60) | ((unsigned long long)tot.ls << 30) | (unsigned long long)tot.hdr;
                 long long j = (long long)tile - 1;
                 bool done = false;
                 while (!done) {
@@ -281,84 +293,19 @@ __global__ void __launch_bounds__(kEncThreads, 3) k2s_encode(const EncodeParams2
                 }
             }
             if (lane == 0) {
-                const unsigned long long in = ex + tot_pack;
-                const unsigned int in_last = tot_last ? tot_last : ex_last;
+                const unsigned long long in = ex + (((unsigned long long)tot.ls << 30) | (unsigned long long)tot.hdr);
+                const unsigned int in_last = tot.last ? tot.last : ex_last;
                 *reinterpret_cast<volatile unsigned long long*>(&P.look[tile].w0) = (2ull << 62) | ((unsigned long long)in_last << 60) | in;
+                const unsigned long long c_ls = s_carry_ls, c_hdr = s_carry_hdr;
+                const unsigned int c_last = s_carry_last;
                 if (tile == P.n_tiles - 1) {
                     P.carry_out->ls_total = c_ls + (in >> 30); P.carry_out->hdr_total = c_hdr + (in & 0x3FFFFFFFull);
-                    P.carry_out->last = in_last ? in_last : c_last; P.carry_out->fq_rec_base = P.carry_in->fq_rec_base;
+                    P.carry_out->last = in_last ? in_last : c_last; P.carry_out->fq_rec_base = fq_base;
                 }
-                s_slot_ls[b] = c_ls + (ex >> 30); s_slot_hdr[b] = c_hdr + (ex & 0x3FFFFFFFull); s_slot_last[b] = ex_last ? ex_last : c_last;
-                s_slot_tile[b] = tile;
-                mbar_arrive(bar_ready(b));                                           // (release: the slot and the hand-copied ragged row are visible to the waiters)
+                s_pre_ls = c_ls + (ex >> 30); s_pre_hdr = c_hdr + (ex & 0x3FFFFFFFull); s_pre_last = ex_last ? ex_last : c_last;
             }
-            __syncwarp();
-        }
-        return;
-    }
-
-    // ================= consumer warps =====================================================================================
-    // The packed words of a tile leave shared memory one iteration later (after the line-scan barrier of the next tile: the
-    // OR-ing of the tile before is complete, the OR-ing of the new tile is two barriers away); after the loop the last tile is flushed.
-    auto copy_out = [&]() {
-        const uint32_t letters = s_prev[1];
-        uint32_t* dst = P.packed + (size_t)s_prev[0] * kPackStride;
-        if (tid == 0) {
-            dst[0] = letters;
-            TileRec tr;
-            const bool has_b = (s_prev[4] & 0x200u) != 0;
-            tr.head_len = has_b ? s_head[0] : s_prev[2]; tr.head_qlen = has_b ? s_head[1] : s_prev[3];
-            tr.tail_len = s_prev[2]; tr.tail_qlen = s_prev[3];
-            tr.flags = has_b ? s_head[2] : 0u; tr.pad = 0; tr.head_rec = has_b ? s_head_rec : 0ull;
-            P.trec[s_prev[0]] = tr;
-        }
-        const uint32_t cw = (letters + 15) >> 4, bw = (letters + 31) >> 5;
-        for (uint32_t i = tid; i < cw; i += kThreads) { dst[kPackHdr + i] = s_out[i]; s_out[i] = 0; }
-        for (uint32_t i = tid; i < bw; i += kThreads) {
-            dst[kPackHdr + kPackCodes + i] = s_out[kPackCodes + i]; s_out[kPackCodes + i] = 0;
-            dst[kPackHdr + kPackCodes + kPackBits + i] = s_out[kPackCodes + kPackBits + i]; s_out[kPackCodes + kPackBits + i] = 0;
-        }
-    };
-    int buf = 0;
-    for (unsigned int it = 0;; it++, buf ^= 1) {
-        mbar_wait(bar_ready(buf), (it >> 1) & 1u);
-        const unsigned int tile = s_slot_tile[buf];
-        if (tile >= P.n_tiles) break;
-        const unsigned long long tile0 = P.lo + (unsigned long long)tile * kTile;
-        s_text = s_text2[buf];
-
-        const unsigned long long a = tile0 + (unsigned long long)tid * kChunk;
-        const int lim = a >= P.hi ? 0 : (P.hi - a >= (unsigned long long)kChunk ? kChunk : (int)(P.hi - a));
-        uint8_t prev = '\n';
-        if (lim > 0 && a > 0) {
-            // last byte of the chunk before mine: my neighbour's chunk in shared memory, or the text before the tile
-            if (tid > 0) { const uint32_t sz = ((uint32_t)(tid - 1) >> 1) & 3u; prev = (uint8_t)(s_text[16 * (tid - 1) + 4 * (3u ^ sz) + 3] >> 24); }
-            else prev = P.feed[a - 1];
-        }
-
-        // ---- phase A: bit masks of my chunk; phase B: line starts -> CTA scan ---------------------
-        const ChunkMasks M = chunk_masks(quad);      // zero fill beyond lim is neither LF nor a letter
-        LineAgg g{0, 0, 0};
-        if (lim > 0) {
-            unsigned long long lsm = ((M.lf << 1) | (prev == '\n' ? 1ull : 0ull)) & ones64((uint32_t)lim);
-            g.ls = __popcll(lsm);
-            if (!FASTQ && lsm) {
-                const uint32_t top = 63 - __clzll(lsm);
-                g.last = byte_at(top) == '>' ? 2u : 1u;
-                while (lsm) { const uint32_t p = __ffsll(lsm) - 1; lsm &= lsm - 1; g.hdr += byte_at(p) == '>' ? 1u : 0u; }
-            } else if (lsm) g.last = 1u;
-        }
-        LineAgg inc = g, warp_pre{0, 0, 0};
-#pragma unroll
-        for (int d = 1; d < 32; d <<= 1) { const LineAgg o = shfl_up_agg(inc, d); if (lane >= d) inc = combine(o, inc); }
-        if (lane == 31) s_scan[warp] = inc;
-        cons_sync();
-#pragma unroll
-        for (int w = 0; w < kThreads / 32; w++) { const LineAgg t = s_scan[w]; if (w < warp) warp_pre = combine(warp_pre, t); }
-        inc = combine(warp_pre, inc);
-        if (s_prev[5]) copy_out();                                   // the packed words of the tile before leave
-        const unsigned long long s_pre_ls = s_slot_ls[buf], s_pre_hdr = s_slot_hdr[buf];
-        const unsigned int s_pre_last = s_slot_last[buf];
+        } else if (s_prev[5]) copy_out(32, kThreads - 32);              // warps 1..7 meanwhile: the packed words of the tile before leave
+        __syncthreads();
         const unsigned long long ls_before = s_pre_ls + (inc.ls - g.ls);
         unsigned long long hdr_before = s_pre_hdr + (inc.hdr - g.hdr);
         unsigned int last_before;
@@ -558,9 +505,12 @@ __global__ void __launch_bounds__(kEncThreads, 3) k2s_encode(const EncodeParams2
         if (tid == 0) s_seed = seed;
         TailAgg2 tile_total;
         TailAgg2 start = tail2_scan_exclusive<FASTQ>(tail, s_tail, &tile_total);      // (syncs: s_seed is visible after it)
-        // ---- hand the text buffer back to the producer; remember what the deferred copy-out needs ------------------------
+        // ---- stage: thread 0 takes the next ticket and starts its TMA load into the other buffer (the barrier of the tail
+        // scan is behind us: nobody reads text any more in this iteration).  The ticket is taken LATE — one copy-out before the tile is worked on, not a whole tile earlier: a
+        // ticket holder publishes its aggregate a few microseconds after taking the ticket, so a tile rarely finds a predecessor
+        // that has not published yet (with the ticket taken a tile ahead, 42 % of the kernel's samples sat in that wait). -----------
         if (tid == 0) {
-            mbar_arrive(bar_empty(buf));                                 // (the tail scan's barrier is behind us: nobody reads this text any more)
+            take_ticket((it + 1) & 1, buf ^ 1);
             s_prev[0] = tile; s_prev[1] = tile_total.letters; s_prev[2] = tile_total.olen; s_prev[3] = tile_total.oqlen; s_prev[4] = tile_total.meta; s_prev[5] = 1;
         }
         const uint32_t off = start.letters;
@@ -596,8 +546,8 @@ __global__ void __launch_bounds__(kEncThreads, 3) k2s_encode(const EncodeParams2
             or_bits<2>(s_out + kPackCodes + kPackBits, off, z, E.n);
         }
     }
-    cons_sync();
-    if (s_prev[5]) copy_out();
+    __syncthreads();
+    if (s_prev[5]) copy_out(0, kThreads);
 
     // ---- CTA reduction of the fused scalars --------------------------------------------------------
     unsigned long long v[8] = {0, letters_total, Y.mono[0], Y.mono[1], Y.mono[2], Y.mono[3], Y.nwin, 0};
@@ -612,12 +562,12 @@ __global__ void __launch_bounds__(kEncThreads, 3) k2s_encode(const EncodeParams2
         const unsigned int o2 = __shfl_xor_sync(0xffffffffu, mx_len, d); mx_len = o2 > mx_len ? o2 : mx_len;
         any_rec |= __shfl_xor_sync(0xffffffffu, any_rec, d);
     }
-    cons_sync();
+    __syncthreads();
     if (lane == 0) {
         for (int i = 1; i < 7; i++) s_red[warp][i] = v[i];
         s_red[warp][7] = err_key; s_red[warp][8] = any_rec ? mn_len : ~0ull; s_red[warp][9] = mx_len;
     }
-    cons_sync();
+    __syncthreads();
     if (tid >= 1 && tid < 7) {
         unsigned long long s = 0;
         for (int wp = 0; wp < kThreads / 32; wp++) s += s_red[wp][tid];
