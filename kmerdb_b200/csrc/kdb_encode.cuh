@@ -178,6 +178,50 @@ __device__ __forceinline__ ChunkMasks chunk_masks(Quad quad) {
     return M;
 }
 
+// The two halves of chunk_masks for the single-pass tokeniser: the line-feed mask first (all the line scan needs), the letter
+// masks and codes later — in k2s_encode they fill the time between publishing a tile's aggregate and looking back for its
+// predecessors' (kdb_encode2.cuh).
+template <typename Quad>
+__device__ __forceinline__ unsigned long long chunk_lf(Quad quad) {
+    unsigned long long lf = 0;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        const uint4 v4 = quad(q);
+        const uint32_t m16 = nib(eqmask(v4.x, 0x0A0A0A0Au)) | (nib(eqmask(v4.y, 0x0A0A0A0Au)) << 4) | (nib(eqmask(v4.z, 0x0A0A0A0Au)) << 8) |
+                             (nib(eqmask(v4.w, 0x0A0A0A0Au)) << 12);
+        lf |= (unsigned long long)m16 << (16 * q);
+    }
+    return lf;
+}
+template <typename Quad>
+__device__ __forceinline__ ChunkMasks chunk_masks_rest(Quad quad, unsigned long long lf) {
+    ChunkMasks M;
+    M.lf = lf; M.acgt = 0; M.any_cr = 0; M.any_hi = 0;
+#pragma unroll
+    for (int q = 0; q < 4; q++) {
+        uint32_t xc = 0, ok16 = 0;
+        const uint4 v4 = quad(q);
+        const uint32_t w4[4] = {v4.x, v4.y, v4.z, v4.w};
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const uint32_t wv = w4[r];
+            const uint32_t t = ((wv >> 1) ^ (wv >> 2)) & 0x03030303u;              // A0 C1 G2 T3 (N -> 0)
+            const uint32_t s = t | (t >> 4);
+            const uint32_t sel = (s & 0xFFu) | ((s >> 8) & 0xFF00u);
+            const uint32_t d = __byte_perm(0x54474341u, 0u, sel) ^ wv;            // zero byte <=> ACGT
+            const uint32_t z = ~(((d & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | d | 0x7F7F7F7Fu);
+            ok16 |= nib(z) << (4 * r);
+            xc = (xc << 8) | ((t * 0x40100401u) >> 24);
+            M.any_cr |= eqmask(wv, 0x0D0D0D0Du);
+            M.any_hi |= wv;
+        }
+        M.x[q] = xc;
+        M.acgt |= (unsigned long long)ok16 << (16 * q);
+    }
+    M.any_hi &= 0x80808080u;
+    return M;
+}
+
 // 64-bit byte-equality mask, computed only when needed (N letters, CR).
 template <typename ByteWord>
 __device__ __noinline__ unsigned long long lazy_eq_mask(ByteWord word, uint32_t pat4) {

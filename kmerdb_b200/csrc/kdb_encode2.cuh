@@ -226,10 +226,10 @@ __global__ void __launch_bounds__(kThreads, 4) k2s_encode(const EncodeParams2 P,
         }
 
         // ---- phase A: bit masks of my chunk; phase B: line starts -> CTA scan ---------------------
-        const ChunkMasks M = chunk_masks(quad);      // zero fill beyond lim is neither LF nor a letter
+        const unsigned long long lfm = chunk_lf(quad);             // (zero fill beyond lim is neither LF nor a letter)
         LineAgg g{0, 0, 0};
         if (lim > 0) {
-            unsigned long long lsm = ((M.lf << 1) | (prev == '\n' ? 1ull : 0ull)) & ones64((uint32_t)lim);
+            unsigned long long lsm = ((lfm << 1) | (prev == '\n' ? 1ull : 0ull)) & ones64((uint32_t)lim);
             g.ls = __popcll(lsm);
             if (!FASTQ && lsm) {
                 const uint32_t top = 63 - __clzll(lsm);
@@ -245,6 +245,13 @@ __global__ void __launch_bounds__(kThreads, 4) k2s_encode(const EncodeParams2 P,
 #pragma unroll
         for (int w = 0; w < kThreads / 32; w++) { const LineAgg t = s_scan[w]; if (w < warp) warp_pre = combine(warp_pre, t); tot = combine(tot, t); }
         inc = combine(warp_pre, inc);
+        // The tile's aggregate goes out NOW; the letter masks and codes of my chunk (the larger half of phase A) are built before
+        // anybody looks back, so that the predecessors — which took their tickets moments before this tile and are at the same
+        // point of their own iteration — have published by the time their status words are polled.
+        if (tid == 0 && tile != 0)
+            *reinterpret_cast<volatile unsigned long long*>(&P.look[tile].w0) =
+                (1ull << 62) | ((unsigned long long)tot.last << 60) | ((unsigned long long)tot.ls << 30) | (unsigned long long)tot.hdr;
+        const ChunkMasks M = chunk_masks_rest(quad, lfm);
 
         // ---- decoupled look-back (warp 0): what came before this tile ---------------------------------------------
         // Every lane polls four predecessors (128 tiles per round, nearest first).  The sum runs back to the nearest tile that
@@ -254,9 +261,6 @@ __global__ void __launch_bounds__(kThreads, 4) k2s_encode(const EncodeParams2 P,
             unsigned long long ex = 0;                                  // [59:30] line starts, [29:0] title lines before this tile, in this pass
             unsigned int ex_last = 0;
             if (tile != 0) {
-                if (lane == 0)
-                    *reinterpret_cast<volatile unsigned long long*>(&P.look[tile].w0) =
-                        (1ull << 62) | ((unsigned long long)tot.last << 60) | ((unsigned long long)tot.ls << 30) | (unsigned long long)tot.hdr;
                 long long j = (long long)tile - 1;
                 bool done = false;
                 while (!done) {
