@@ -131,8 +131,8 @@ __global__ void __launch_bounds__(kThreads, 4) k2s_encode(const EncodeParams2 P,
     __shared__ unsigned long long s_red[kThreads / 32][10];
     __shared__ __align__(8) unsigned long long s_bar[2];
     __shared__ unsigned int s_next[2];
-    __shared__ unsigned long long s_pre_ls, s_pre_hdr, s_head_rec, s_carry_ls, s_carry_hdr;
-    __shared__ unsigned int s_pre_last, s_head[3], s_carry_last;
+    __shared__ unsigned long long s_head_rec, s_carry_ls, s_carry_hdr, s_grp_sum[kThreads / 32];
+    __shared__ unsigned int s_head[3], s_carry_last, s_grp_flag[kThreads / 32];
     __shared__ unsigned int s_prev[6];                               // the tile whose packed words still wait in s_out: index, letters, olen, oqlen, meta, valid
 
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -245,71 +245,71 @@ __global__ void __launch_bounds__(kThreads, 4) k2s_encode(const EncodeParams2 P,
 #pragma unroll
         for (int w = 0; w < kThreads / 32; w++) { const LineAgg t = s_scan[w]; if (w < warp) warp_pre = combine(warp_pre, t); tot = combine(tot, t); }
         inc = combine(warp_pre, inc);
-        // The tile's aggregate goes out NOW; the letter masks and codes of my chunk (the larger half of phase A) are built before
-        // anybody looks back, so that the predecessors — which took their tickets moments before this tile and are at the same
-        // point of their own iteration — have published by the time their status words are polled.
-        if (tid == 0 && tile != 0)
+        // The tile's aggregate goes out NOW, and every thread asks for the status word of ONE predecessor (thread t: tile - 1 - t:
+        // a window of 256 tiles per round, the load issued here and looked at later).  The letter masks and codes of my chunk
+        // (the larger half of phase A) and the copy-out of the tile before fill the time until the answers are in; the
+        // predecessors — which took their tickets moments before this tile and are at the same point of their own iteration —
+        // have published by then.
+        if (tid == 0)
             *reinterpret_cast<volatile unsigned long long*>(&P.look[tile].w0) =
                 (1ull << 62) | ((unsigned long long)tot.last << 60) | ((unsigned long long)tot.ls << 30) | (unsigned long long)tot.hdr;
+        long long pidx = (long long)tile - 1 - tid;
+        unsigned long long pw = 2ull << 62;                                  // before tile 0 of the pass: an empty prefix
+        if (pidx >= 0) pw = *reinterpret_cast<const volatile unsigned long long*>(&P.look[pidx].w0);
         const ChunkMasks M = chunk_masks_rest(quad, lfm);
+        if (s_prev[5]) copy_out(0, kThreads);                                // the packed words of the tile before leave
 
-        // ---- decoupled look-back (warp 0): what came before this tile ---------------------------------------------
-        // Every lane polls four predecessors (128 tiles per round, nearest first).  The sum runs back to the nearest tile that
-        // already holds an inclusive prefix; everything nearer contributes its aggregate.  All of them hold earlier tickets,
-        // so they are running or done: the spin cannot starve.
-        if (warp == 0) {
-            unsigned long long ex = 0;                                  // [59:30] line starts, [29:0] title lines before this tile, in this pass
-            unsigned int ex_last = 0;
-            if (tile != 0) {
-                long long j = (long long)tile - 1;
-                bool done = false;
-                while (!done) {
-                    unsigned long long w[4];
-#pragma unroll
-                    for (int q = 0; q < 4; q++) {
-                        const long long idx = j - lane - 32 * q;
-                        w[q] = 2ull << 62;                                           // before tile 0 of the pass: an empty prefix
-                        if (idx >= 0) {
-                            const volatile unsigned long long* src = reinterpret_cast<const volatile unsigned long long*>(&P.look[idx].w0);
-                            unsigned long long x;
-                            do { x = *src; } while ((x >> 62) == 0);
-                            w[q] = x;
-                        }
-                    }
-                    __syncwarp();
-                    unsigned long long mine = 0;
-#pragma unroll
-                    for (int q = 0; q < 4; q++) {
-                        if (done) break;
-                        const unsigned int m2 = __ballot_sync(0xffffffffu, (w[q] >> 62) == 2);
-                        const int first = m2 ? __ffs(m2) - 1 : 32;                   // nearest tile of this group that already holds an inclusive prefix
-                        const bool use = lane <= first;
-                        const unsigned int last = use ? (unsigned int)(w[q] >> 60) & 3u : 0u;
-                        const unsigned int ml = __ballot_sync(0xffffffffu, last != 0);
-                        if (ex_last == 0 && ml) ex_last = __shfl_sync(0xffffffffu, last, __ffs(ml) - 1);
-                        if (use) mine += w[q] & ((1ull << 60) - 1ull);
-                        done = m2 != 0;
-                    }
-#pragma unroll
-                    for (int d = 16; d; d >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, d);
-                    ex += mine;
-                    j -= 128;
-                }
+        // ---- decoupled look-back, all eight warps: what came before this tile ------------------------------------------
+        // Warp w holds predecessors [32 w, 32 w + 32) of the window.  The sum runs back to the nearest tile that already holds an
+        // inclusive prefix; everything nearer contributes its aggregate.  All of them hold earlier tickets, so they are running
+        // or done: the spin cannot starve.  One round (256 tiles) is nearly always enough.
+        unsigned long long ex = 0;                                           // [59:30] line starts, [29:0] title lines before this tile, in this pass
+        unsigned int ex_last = 0;
+        while (true) {
+            if (pidx >= 0) {
+                const volatile unsigned long long* src = reinterpret_cast<const volatile unsigned long long*>(&P.look[pidx].w0);
+                while ((pw >> 62) == 0) pw = *src;                           // that predecessor has not published yet
             }
-            if (lane == 0) {
-                const unsigned long long in = ex + (((unsigned long long)tot.ls << 30) | (unsigned long long)tot.hdr);
-                const unsigned int in_last = tot.last ? tot.last : ex_last;
-                *reinterpret_cast<volatile unsigned long long*>(&P.look[tile].w0) = (2ull << 62) | ((unsigned long long)in_last << 60) | in;
-                const unsigned long long c_ls = s_carry_ls, c_hdr = s_carry_hdr;
-                const unsigned int c_last = s_carry_last;
-                if (tile == P.n_tiles - 1) {
-                    P.carry_out->ls_total = c_ls + (in >> 30); P.carry_out->hdr_total = c_hdr + (in & 0x3FFFFFFFull);
-                    P.carry_out->last = in_last ? in_last : c_last; P.carry_out->fq_rec_base = fq_base;
-                }
-                s_pre_ls = c_ls + (ex >> 30); s_pre_hdr = c_hdr + (ex & 0x3FFFFFFFull); s_pre_last = ex_last ? ex_last : c_last;
+            __syncwarp();
+            const unsigned int m2 = __ballot_sync(0xffffffffu, (pw >> 62) == 2);
+            const int first = m2 ? __ffs(m2) - 1 : 32;                       // nearest tile of my group that already holds an inclusive prefix
+            const bool use = lane <= first;
+            const unsigned int last = use ? (unsigned int)(pw >> 60) & 3u : 0u;
+            const unsigned int ml = __ballot_sync(0xffffffffu, last != 0);
+            const unsigned int glast = ml ? __shfl_sync(0xffffffffu, last, __ffs(ml) - 1) : 0u;
+            unsigned long long mine = use ? pw & ((1ull << 60) - 1ull) : 0ull;
+#pragma unroll
+            for (int d = 16; d; d >>= 1) mine += __shfl_xor_sync(0xffffffffu, mine, d);
+            if (lane == 0) { s_grp_sum[warp] = mine; s_grp_flag[warp] = glast | (m2 ? 4u : 0u); }
+            __syncthreads();
+            bool found = false;
+#pragma unroll
+            for (int w = 0; w < kThreads / 32; w++) {
+                if (found) break;
+                const unsigned int f = s_grp_flag[w];
+                ex += s_grp_sum[w];
+                if (ex_last == 0) ex_last = f & 3u;
+                found = (f & 4u) != 0;
             }
-        } else if (s_prev[5]) copy_out(32, kThreads - 32);              // warps 1..7 meanwhile: the packed words of the tile before leave
-        __syncthreads();
+            if (found) break;
+            __syncthreads();                                                 // (rare: more than 256 predecessors without a prefix)
+            pidx -= kThreads;
+            pw = 2ull << 62;
+            if (pidx >= 0) pw = *reinterpret_cast<const volatile unsigned long long*>(&P.look[pidx].w0);
+        }
+        const unsigned long long c_ls = s_carry_ls, c_hdr = s_carry_hdr;
+        const unsigned int c_last = s_carry_last;
+        if (tid == 0) {
+            const unsigned long long in = ex + (((unsigned long long)tot.ls << 30) | (unsigned long long)tot.hdr);
+            const unsigned int in_last = tot.last ? tot.last : ex_last;
+            *reinterpret_cast<volatile unsigned long long*>(&P.look[tile].w0) = (2ull << 62) | ((unsigned long long)in_last << 60) | in;
+            if (tile == P.n_tiles - 1) {
+                P.carry_out->ls_total = c_ls + (in >> 30); P.carry_out->hdr_total = c_hdr + (in & 0x3FFFFFFFull);
+                P.carry_out->last = in_last ? in_last : c_last; P.carry_out->fq_rec_base = fq_base;
+            }
+        }
+        const unsigned long long s_pre_ls = c_ls + (ex >> 30), s_pre_hdr = c_hdr + (ex & 0x3FFFFFFFull);
+        const unsigned int s_pre_last = ex_last ? ex_last : c_last;
         const unsigned long long ls_before = s_pre_ls + (inc.ls - g.ls);
         unsigned long long hdr_before = s_pre_hdr + (inc.hdr - g.hdr);
         unsigned int last_before;
