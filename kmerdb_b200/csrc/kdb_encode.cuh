@@ -182,21 +182,26 @@ __device__ __forceinline__ ChunkMasks chunk_masks(Quad quad) {
 // masks and codes later — in k2s_encode they fill the time between publishing a tile's aggregate and looking back for its
 // predecessors' (kdb_encode2.cuh).
 template <typename Quad>
-__device__ __forceinline__ unsigned long long chunk_lf(Quad quad) {
+__device__ __forceinline__ unsigned long long chunk_lf(Quad quad, uint32_t* any_cr, uint32_t* any_hi) {
     unsigned long long lf = 0;
+    uint32_t cr = 0, hi = 0;
 #pragma unroll
     for (int q = 0; q < 4; q++) {
         const uint4 v4 = quad(q);
         const uint32_t m16 = nib(eqmask(v4.x, 0x0A0A0A0Au)) | (nib(eqmask(v4.y, 0x0A0A0A0Au)) << 4) | (nib(eqmask(v4.z, 0x0A0A0A0Au)) << 8) |
                              (nib(eqmask(v4.w, 0x0A0A0A0Au)) << 12);
         lf |= (unsigned long long)m16 << (16 * q);
+        cr |= eqmask(v4.x, 0x0D0D0D0Du) | eqmask(v4.y, 0x0D0D0D0Du) | eqmask(v4.z, 0x0D0D0D0Du) | eqmask(v4.w, 0x0D0D0D0Du);
+        hi |= v4.x | v4.y | v4.z | v4.w;
     }
+    *any_cr = cr; *any_hi = hi & 0x80808080u;
     return lf;
 }
+// letter validity + 2-bit codes: only chunks that hold sequence-line bytes need them (FASTQ: about half)
 template <typename Quad>
-__device__ __forceinline__ ChunkMasks chunk_masks_rest(Quad quad, unsigned long long lf) {
+__device__ __forceinline__ ChunkMasks chunk_masks_rest(Quad quad, unsigned long long lf, uint32_t any_cr, uint32_t any_hi) {
     ChunkMasks M;
-    M.lf = lf; M.acgt = 0; M.any_cr = 0; M.any_hi = 0;
+    M.lf = lf; M.acgt = 0; M.any_cr = any_cr; M.any_hi = any_hi;
 #pragma unroll
     for (int q = 0; q < 4; q++) {
         uint32_t xc = 0, ok16 = 0;
@@ -212,13 +217,10 @@ __device__ __forceinline__ ChunkMasks chunk_masks_rest(Quad quad, unsigned long 
             const uint32_t z = ~(((d & 0x7F7F7F7Fu) + 0x7F7F7F7Fu) | d | 0x7F7F7F7Fu);
             ok16 |= nib(z) << (4 * r);
             xc = (xc << 8) | ((t * 0x40100401u) >> 24);
-            M.any_cr |= eqmask(wv, 0x0D0D0D0Du);
-            M.any_hi |= wv;
         }
         M.x[q] = xc;
         M.acgt |= (unsigned long long)ok16 << (16 * q);
     }
-    M.any_hi &= 0x80808080u;
     return M;
 }
 
