@@ -124,3 +124,33 @@ def test_streamed_text_pieces_and_record_aligned_fragments(tmp_path):
         list(parse._iter_text_pieces(p, 4096, ()))
     with pytest.raises(EOFError):
         gzip.open(p, "rb").read()
+
+
+def test_streaming_keeps_host_memory_bounded(tmp_path):
+    """the input is never held whole.  A 48 MiB FASTA file (and its gzip) streamed in 1 MiB pieces:
+    the Python-level peak while reading, inflating and cutting fragments stays a few pieces, independent of the file size."""
+    import tracemalloc
+    import numpy as np
+    rng = np.random.default_rng(1)
+    line = bytes(rng.choice(np.frombuffer(b"ACGT", dtype=np.uint8), size=150)) + b"\n"
+    rec = b">read\n" + line
+    n = (48 << 20) // len(rec)
+    plain = str(tmp_path / "big.fa")
+    with open(plain, "wb") as fh:
+        for _ in range(64):
+            fh.write(rec * (n // 64))
+    gz = str(tmp_path / "big.fa.gz")
+    with gzip.open(gz, "wb", compresslevel=1) as out, open(plain, "rb") as src:
+        for chunk in iter(lambda: src.read(1 << 22), b""):
+            out.write(chunk)
+    piece = 1 << 20
+    for path in (plain, gz):
+        tracemalloc.start()
+        total = 0
+        for frag in parse._iter_fragments(parse._iter_text_pieces(path, piece, (hashlib.md5(),)), "fasta"):
+            total += len(frag)
+            assert frag[:1] == b">"
+        _cur, peak = tracemalloc.get_traced_memory()
+        tracemalloc.stop()
+        assert total == os.path.getsize(plain)
+        assert peak < 8 * piece, (path, peak)
