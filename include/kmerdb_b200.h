@@ -83,6 +83,9 @@ typedef struct {
 kdb_ctx* kdb_create(int device, int k, int flags);
 void kdb_destroy(kdb_ctx* ctx);
 const char* kdb_last_error(const kdb_ctx* ctx);
+/* Device time (CUDA events) of the kernels of this thread's last kdb_minimizers_batch call: the device-resident rate of the
+ * stateless K4 entry points, whose wall time is dominated by the host -> device copy of their inputs. */
+float kdb_last_kernel_ms(void);
 
 /* Replaces the record loop of kmerdb/parse.py:128-137 (+ kmer.shred kmerdb/kmer.py:489-577).
  * `bytes` is the uncompressed file text, or a fragment of it that starts at a record boundary

@@ -19,7 +19,7 @@ EXPORTS = [
     "kdb_reset", "kdb_timing", "kdb_kmer_to_id_batch", "kdb_synth_record_bytes", "kdb_synth_device",
     "kdb_synth_host", "kdb_microbench_atomics", "kdb_dev_alloc", "kdb_dev_free", "kdb_host_alloc_pinned",
     "kdb_host_free_pinned", "kdb_memcpy_h2d", "kdb_memcpy_d2h", "kdb_nccl_unique_id", "kdb_reduce_nccl", "kdb_reduce_peers",
-    "kdb_bgzf_index", "kdb_inflate_bgzf", "kdb_feed_bgzf_host",
+    "kdb_bgzf_index", "kdb_inflate_bgzf", "kdb_feed_bgzf_host", "kdb_last_kernel_ms",
     "kdb_edge_rows", "kdb_edge_weights", "kdb_minimizers_compat", "kdb_minimizers", "kdb_attach", "kdb_format_rows", "kdb_minimizers_batch",
     "kdb_reader_create", "kdb_reader_feed", "kdb_reader_finish", "kdb_reader_destroy", "kdb_correlation_matrix",
 ]
@@ -73,6 +73,7 @@ def lib():
         ("kdb_kmer_to_id_batch", [ci, ctypes.c_char_p, sz, ci, ci, vp]),
         ("kdb_bgzf_index", [vp, sz, vp, sz, ctypes.POINTER(sz), ctypes.POINTER(u64)]), ("kdb_inflate_bgzf", [ci, vp, sz, vp, sz, ctypes.POINTER(sz)]),
         ("kdb_feed_bgzf_host", [vp, vp, sz]),
+        ("kdb_last_kernel_ms", []),
         ("kdb_nccl_unique_id", [vp, sz]), ("kdb_reduce_nccl", [vp, vp, ci, ci]), ("kdb_reduce_peers", [vp, ci]),
         ("kdb_synth_device", [ci, vp, u64, u64, ci, ci, u64]), ("kdb_synth_host", [vp, u64, u64, ci, ci, u64]),
         ("kdb_microbench_atomics", [ci, sz, u64, ci, ctypes.POINTER(ctypes.c_double)]),
@@ -90,6 +91,7 @@ def lib():
         fn = getattr(L, name)
         fn.restype = ci
         fn.argtypes = args
+    L.kdb_last_kernel_ms.restype = ctypes.c_float
     L.kdb_reader_create.restype = vp
     L.kdb_reader_create.argtypes = [ci, ci]
     L.kdb_reader_destroy.restype = None

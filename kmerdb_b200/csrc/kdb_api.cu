@@ -28,6 +28,7 @@
 using namespace kdb;
 
 static thread_local std::string g_last_error;
+static thread_local float g_last_kernel_ms = 0.f;       // device time of the kernels of the last stateless K4 call (kdb_last_kernel_ms)
 
 struct kdb_ctx {
     int device = 0, k = 0, flags = 0;
@@ -177,6 +178,7 @@ static int occupancy_grid(K kernel, int threads, size_t dyn_smem, int* grid) {
     return KDB_OK;
 }
 
+extern "C" float kdb_last_kernel_ms(void) { return g_last_kernel_ms; }
 extern "C" const char* kdb_last_error(const kdb_ctx* ctx) { return ctx ? ctx->err.c_str() : g_last_error.c_str(); }
 
 extern "C" void kdb_destroy(kdb_ctx* ctx) {
@@ -1557,11 +1559,17 @@ extern "C" int kdb_minimizers_batch(int device, const uint8_t* letters, size_t n
         // fused path: letters -> rows, nothing staged in HBM (k8_minb_fused); first launch counts (and checks the letters), second writes
         const unsigned int blocks = (unsigned int)((n_out + kEdgeBlock - 1) / kEdgeBlock);
         CK(d_cnt.alloc(blocks * sizeof(unsigned int)));
+        cudaEvent_t e0, e1;
+        CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+        CK(cudaEventRecord(e0));
         k8_minb_fused<false><<<blocks, 256>>>(d_let.as<uint8_t>(), n_letters, n_out, d_off.as<unsigned long long>(), n_recs, k, w, d_cnt.as<unsigned int>(),
                                               nullptr, nullptr, nullptr, nullptr, 0, d_bad.as<unsigned int>());
         CK(cudaGetLastError());
+        CK(cudaEventRecord(e1));
         unsigned int bad = 0;
         CK(cudaMemcpy(&bad, d_bad.p, 4, cudaMemcpyDeviceToHost));
+        CK(cudaEventElapsedTime(&g_last_kernel_ms, e0, e1));
+        cudaEventDestroy(e0); cudaEventDestroy(e1);
         if (bad & 1u) return KDB_E_ALPHABET;
         if (bad & 2u) return KDB_E_IUPAC;
         unsigned long long total = 0;
