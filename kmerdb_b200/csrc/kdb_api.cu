@@ -857,7 +857,7 @@ extern "C" int kdb_refinalize(kdb_ctx* ctx) {
 // ---- BGZF input: compressed bytes over PCIe, inflate on the device (kdb_inflate.cuh) ------------------------------------
 // a corrupt member can make the decoder read on past its payload before a check fires (at most 15 bits per output byte of a
 // 64 KiB member): the compressed buffer carries that much slack behind the last member
-constexpr size_t kInflateSlack = 160u << 10;
+constexpr size_t kInflateSlack = (160u << 10) + 512;       // (+ two 128-byte lines of read-ahead)
 static bool g_crc_table_loaded[64] = {false};
 static int load_crc_table(kdb_ctx* ctx, int device) {
     if (device >= 0 && device < 64 && g_crc_table_loaded[device]) return KDB_OK;

@@ -42,23 +42,40 @@ __constant__ unsigned char c_dist_extra[30] = {0, 0, 0, 0, 1, 1, 2, 2, 3, 3, 4, 
 __constant__ unsigned char c_clen_order[19] = {16, 17, 18, 0, 8, 7, 9, 6, 10, 5, 11, 4, 12, 3, 13, 2, 14, 1, 15};
 __constant__ unsigned int c_crc_table[256];  // filled by the host (kdb_api.cu: build_crc_table)
 
-// LSB-first bit reader over global memory, identical in every lane (broadcast loads).  Whole aligned 32-bit words are
-// loaded (the payload may start at any byte: the first word is shifted into place); a word may reach up to 3 bytes past the
-// payload (the member's 8-byte trailer follows it): `used()` tells how many payload bits were really consumed.
+// LSB-first bit reader, identical in every lane.  The payload is fetched a 128-byte line at a time: lane l holds word l of the
+// current line in a register (one coalesced load per 128 bytes of compressed data, the next line requested before it is needed),
+// and a refill is a shuffle from the lane that holds the next word — no memory latency on the decode chain and no dependence on
+// L1, which the per-warp tables leave little of.  The payload may start at any byte: the stream starts at the aligned line below
+// it and the first word is shifted into place.  A line may reach past the payload (the trailer and the next member follow; the
+// buffer carries slack behind the last one): `used()` tells how many payload bits were really consumed.
 struct BitReader {
-    const uint32_t* w;                // aligned word holding the next unread byte ...
+    const uint32_t* line;             // next 128-byte line to request
+    uint32_t cur, nxt;                // my word of the line being consumed / of the line after it
     unsigned long long buf;
     long long bits_in;                // payload bits loaded so far
     int cnt;
+    int widx;                         // next word of the current line (0..32)
     __device__ __forceinline__ void init(const uint8_t* p) {
-        const unsigned int skip = (unsigned int)((uintptr_t)p & 3u);
-        w = reinterpret_cast<const uint32_t*>(p - skip);
-        buf = (unsigned long long)(__ldg(w++) >> (8 * skip));
+        const int lane = threadIdx.x & 31;
+        const uintptr_t a = (uintptr_t)p;
+        line = reinterpret_cast<const uint32_t*>(a & ~(uintptr_t)127);
+        cur = __ldg(line + lane); line += 32;
+        nxt = __ldg(line + lane); line += 32;
+        const unsigned int skip = (unsigned int)(a & 3u);
+        widx = (int)((a & 127u) >> 2);
+        const uint32_t w0 = __shfl_sync(0xffffffffu, cur, widx);
+        widx++;
+        buf = (unsigned long long)(w0 >> (8 * skip));
         cnt = 32 - 8 * (int)skip;
         bits_in = cnt;
     }
-    __device__ __forceinline__ void refill() {                      // at least 33 bits afterwards
-        if (cnt <= 32) { buf |= (unsigned long long)__ldg(w++) << cnt; cnt += 32; bits_in += 32; }
+    __device__ __forceinline__ void refill() {                      // at least 33 bits afterwards; called by all lanes together
+        if (cnt <= 32) {
+            if (widx == 32) { cur = nxt; nxt = __ldg(line + (threadIdx.x & 31)); line += 32; widx = 0; }
+            const uint32_t w = __shfl_sync(0xffffffffu, cur, widx);
+            widx++;
+            buf |= (unsigned long long)w << cnt; cnt += 32; bits_in += 32;
+        }
     }
     __device__ __forceinline__ unsigned int peek(int n) const { return (unsigned int)buf & ((1u << n) - 1u); }
     __device__ __forceinline__ void drop(int n) { buf >>= n; cnt -= n; }
