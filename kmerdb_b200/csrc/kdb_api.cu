@@ -917,7 +917,7 @@ static int inflate_members(kdb_ctx* ctx, int device, const uint8_t* d_comp, cons
     if (int rc = load_crc_table(ctx, device)) return rc;
     static_assert(sizeof(kdb_bgzf_member_t) == sizeof(BgzfMember), "member layout");
     CK(cudaMemcpyAsync(d_members, members, n_members * sizeof(BgzfMember), cudaMemcpyHostToDevice, st));
-    const int grid = (int)std::min<size_t>((n_members + kInfWarps - 1) / kInfWarps, (size_t)148 * 7);
+    const int grid = (int)std::min<size_t>((n_members + kInfWarps - 1) / kInfWarps, (size_t)148 * 8);
     k_inflate_bgzf<<<grid, kInfWarps * 32, 0, st>>>(d_comp, d_members, (unsigned int)n_members, d_out, d_status, check_crc);
     CK(cudaGetLastError());
     return KDB_OK;
@@ -965,17 +965,20 @@ extern "C" int kdb_feed_bgzf_host(kdb_ctx* ctx, const uint8_t* raw, size_t n) {
     BgzfMember* d_mem = reinterpret_cast<BgzfMember*>(ctx->comp_buf + ((n + kInflateSlack + 15) & ~(size_t)15));
     unsigned int* d_st = reinterpret_cast<unsigned int*>(d_mem + nm);
     if (int rc = begin_feed(ctx)) return rc;
-    // pieces of about 32 MiB of compressed bytes, cut at member borders
-    const size_t piece = 32u << 20;
-    std::vector<size_t> cut{0};                                   // member index where each piece starts
-    {
-        size_t start_off = 0;
-        for (size_t i = 0; i < nm; i++) {
-            const size_t member_end = (i + 1 < nm) ? (size_t)mem[i + 1].in_off : n;      // (a piece ends before the header of the next member's payload: close enough)
-            if (member_end - start_off >= piece && i + 1 < nm) { cut.push_back(i + 1); start_off = member_end; }
-        }
-        cut.push_back(nm);
+    // pieces of two waves of members (one warp inflates one member: a piece must hold enough members to fill the GPU — with 32 MiB pieces
+    // a launch had 10 warps per SM and the seventeen launches of a 558 MB file took 143 ms, 8.4 ms each, the latency of ONE member)
+    static int wave_members = 0;                                  // members the GPU inflates at once: resident warps of k_inflate_bgzf
+    if (!wave_members) {
+        int per_sm = 0, sms = 0;
+        CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_inflate_bgzf, kInfWarps * 32, 0));
+        wave_members = std::max(1, per_sm) * sms * kInfWarps;
     }
+    const size_t piece_members = 2 * (size_t)wave_members;
+    std::vector<size_t> cut;                                      // member index where each piece starts
+    for (size_t i = 0; i < nm; i += piece_members) cut.push_back(i);
+    if (cut.size() > 1 && nm - cut.back() < piece_members / 4) cut.pop_back();     // (a short tail joins the piece before it)
+    cut.push_back(nm);
     const size_t n_piece = cut.size() - 1;
     while (ctx->ev_copy.size() < n_piece + 1) { cudaEvent_t e; CK(cudaEventCreate(&e)); ctx->ev_copy.push_back(e); }
     CK(cudaEventRecord(ctx->ev_copy[n_piece], ctx->s_copy));
