@@ -56,7 +56,7 @@ typedef struct {
     uint64_t max_len;      /* parse.py:144 */
     uint64_t mono[4];      /* A,C,G,T letter counts */
     uint64_t err_record;   /* 0-based index of the first record that raises (valid when status != 0) */
-    uint64_t n_windows_with_n; /* windows holding at least one N */
+    uint64_t n_windows_with_n; /* windows holding at least one N (a follower of a kdb_attach sweep reports its LEADER's k here) */
     int32_t status;        /* KDB_OK or the class of the first failing record, in the reference's order */
     int32_t pad_;
 } kdb_stats_t;

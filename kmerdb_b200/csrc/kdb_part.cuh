@@ -296,8 +296,8 @@ __global__ void __launch_bounds__(kCount16Threads) k3p_count16(const uint16_t* _
     }
 }
 
-// 18-bit payloads in 32-bit entries (k = 14): grid = n_buckets * 4; CTA (b, sub) counts the entries of bucket b whose payload
-// bits above 16 equal sub (the four CTAs of a bucket run next to each other: the re-reads hit L2)
+// pb-bit payloads (pb = KDB_PB14 = 17) in 32-bit entries (k = 14): grid = n_buckets * 2^(pb - 16); CTA (b, sub) counts the entries of
+// bucket b whose payload bits above 16 equal sub (the 2^(pb - 16) CTAs of a bucket run next to each other: the re-reads hit L2)
 __global__ void __launch_bounds__(kCount16Threads) k3p_count16w(const uint32_t* __restrict__ stream, const unsigned int* __restrict__ cursor,
                                                                 const unsigned int* __restrict__ fail_base, unsigned int cap, int pb,
                                                                 unsigned int* __restrict__ tab32) {
@@ -319,7 +319,7 @@ __global__ void __launch_bounds__(kCount16Threads) k3p_count16w(const uint32_t* 
 #pragma unroll
         for (int r = 0; r < 4; r++) {
             const uint32_t u = u0 + r * kCount16Threads + tid;
-            v[r] = u < units ? __ldg(src + u) : make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);    // (payloads have 18 bits: no sub matches)
+            v[r] = u < units ? __ldg(src + u) : make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);    // (payloads have pb < 32 bits: no sub matches)
         }
 #pragma unroll
         for (int r = 0; r < 4; r++) {
