@@ -168,6 +168,8 @@ __global__ void __launch_bounds__(kInfWarps * 32) k_inflate_bgzf(const uint8_t* 
         BitReader br;
         br.init(payload);
         unsigned int pos = 0, err = 0;
+        unsigned int pend_pos = 0, pend_len = 0;                    // a short match whose bytes are loaded but not stored yet
+        uint8_t pend_val = 0;
         bool last = false;
         while (!last && !err) {
             if (br.used() > 8ll * (long long)M.in_len) { err = 1; break; }      // (a run of empty blocks in garbage must not read on for ever)
@@ -255,21 +257,37 @@ __global__ void __launch_bounds__(kInfWarps * 32) k_inflate_bgzf(const uint8_t* 
                 if (sym == 256) break;
                 sym -= 257;
                 if (sym >= 29) { err = 1; break; }
-                const unsigned int len = c_len_base[sym] + br.take(c_len_extra[sym]);
+                // base + extra bits by arithmetic (RFC 1951 3.2.5: the tables are geometric) instead of four dependent table loads
+                unsigned int lbase = 3u + (unsigned int)sym, lextra = 0;
+                if (sym >= 8) { lextra = (unsigned int)(sym - 4) >> 2; lbase = 3u + ((4u + ((unsigned int)sym & 3u)) << lextra); }
+                if (sym == 28) { lbase = 258; lextra = 0; }
+                const unsigned int len = lbase + br.take((int)lextra);
                 br.refill();
                 const int ds = decode_sym(br, T.dist, kDistBits, 5, T.dist_cnt, T.dist_sym);
                 if (ds < 0 || ds >= 30) { err = 1; break; }
-                const unsigned int d = c_dist_base[ds] + br.take(c_dist_extra[ds]);
+                unsigned int dbase = 1u + (unsigned int)ds, dextra = 0;
+                if (ds >= 4) { dextra = (unsigned int)(ds - 2) >> 1; dbase = 1u + ((2u + ((unsigned int)ds & 1u)) << dextra); }
+                const unsigned int d = dbase + br.take((int)dextra);
                 if (d > pos) { err = 1; break; }
                 if (pos + len > M.out_len) { err = 2; break; }
-                __syncwarp();                                       // the literals before the match are in place
+                // The bytes of a short match are LOADED now and STORED when the next match (or the end of the member) needs them in
+                // place: the L2 round trip of the load (the text written a moment ago is not in L1) overlaps the decode of the symbols
+                // that follow instead of stalling the warp at the store.
+                if (pend_len) { if (lane < pend_len) dst[pend_pos + lane] = pend_val; pend_len = 0; }
+                __syncwarp();                                       // everything before this match is in place
                 const uint8_t* from = dst + pos - d;
-                if (d >= len) { for (unsigned int i = lane; i < len; i += 32) dst[pos + i] = from[i]; }
-                else { for (unsigned int i = lane; i < len; i += 32) dst[pos + i] = from[i % d]; }
+                if (len <= 32) {
+                    if (lane < len) pend_val = from[d >= len ? lane : lane % d];
+                    pend_pos = pos; pend_len = len;
+                } else {
+                    if (d >= len) { for (unsigned int i = lane; i < len; i += 32) dst[pos + i] = from[i]; }
+                    else { for (unsigned int i = lane; i < len; i += 32) dst[pos + i] = from[i % d]; }
+                    __syncwarp();
+                }
                 pos += len;
-                __syncwarp();
             }
         }
+        if (pend_len) { if (lane < pend_len) dst[pend_pos + lane] = pend_val; pend_len = 0; }
         if (!err && br.used() > 8ll * (long long)M.in_len) err = 1;   // ran past the end of the payload
         if (!err && pos != M.out_len) err = 2;
         __syncwarp();
