@@ -8,6 +8,9 @@
 //   * Huffman tables per warp in shared memory: a 10-bit (literal/length) and an 8-bit (distance) first-level table filled by
 //     the lanes together, longer codes by the canonical count/offset walk (RFC 1951 3.2.2);
 //   * stored and fixed-Huffman blocks included (bgzip's EOF marker is an empty fixed block).
+// Tried and rejected (r02, 10 M reads re-blocked at zlib level 1 / 6): loading the bytes of a short match at once and storing them
+// only when the next match needs them (to overlap the L2 round trip with the following decode), together with length / distance
+// bases by arithmetic instead of table loads: 23.6 / 35.9 GB/s of text against 28.1 / 40.0 without.
 // Checks per member: the stream ends exactly at its last block, the output length equals ISIZE, and CRC-32 of the output
 // equals the trailer (32 lane-chunk CRCs by table, joined with the GF(2) shift operator of zlib's crc32_combine).
 #pragma once
@@ -168,8 +171,6 @@ __global__ void __launch_bounds__(kInfWarps * 32) k_inflate_bgzf(const uint8_t* 
         BitReader br;
         br.init(payload);
         unsigned int pos = 0, err = 0;
-        unsigned int pend_pos = 0, pend_len = 0;                    // a short match whose bytes are loaded but not stored yet
-        uint8_t pend_val = 0;
         bool last = false;
         while (!last && !err) {
             if (br.used() > 8ll * (long long)M.in_len) { err = 1; break; }      // (a run of empty blocks in garbage must not read on for ever)
@@ -257,37 +258,21 @@ __global__ void __launch_bounds__(kInfWarps * 32) k_inflate_bgzf(const uint8_t* 
                 if (sym == 256) break;
                 sym -= 257;
                 if (sym >= 29) { err = 1; break; }
-                // base + extra bits by arithmetic (RFC 1951 3.2.5: the tables are geometric) instead of four dependent table loads
-                unsigned int lbase = 3u + (unsigned int)sym, lextra = 0;
-                if (sym >= 8) { lextra = (unsigned int)(sym - 4) >> 2; lbase = 3u + ((4u + ((unsigned int)sym & 3u)) << lextra); }
-                if (sym == 28) { lbase = 258; lextra = 0; }
-                const unsigned int len = lbase + br.take((int)lextra);
+                const unsigned int len = c_len_base[sym] + br.take(c_len_extra[sym]);
                 br.refill();
                 const int ds = decode_sym(br, T.dist, kDistBits, 5, T.dist_cnt, T.dist_sym);
                 if (ds < 0 || ds >= 30) { err = 1; break; }
-                unsigned int dbase = 1u + (unsigned int)ds, dextra = 0;
-                if (ds >= 4) { dextra = (unsigned int)(ds - 2) >> 1; dbase = 1u + ((2u + ((unsigned int)ds & 1u)) << dextra); }
-                const unsigned int d = dbase + br.take((int)dextra);
+                const unsigned int d = c_dist_base[ds] + br.take(c_dist_extra[ds]);
                 if (d > pos) { err = 1; break; }
                 if (pos + len > M.out_len) { err = 2; break; }
-                // The bytes of a short match are LOADED now and STORED when the next match (or the end of the member) needs them in
-                // place: the L2 round trip of the load (the text written a moment ago is not in L1) overlaps the decode of the symbols
-                // that follow instead of stalling the warp at the store.
-                if (pend_len) { if (lane < pend_len) dst[pend_pos + lane] = pend_val; pend_len = 0; }
-                __syncwarp();                                       // everything before this match is in place
+                __syncwarp();                                       // the literals before the match are in place
                 const uint8_t* from = dst + pos - d;
-                if (len <= 32) {
-                    if (lane < len) pend_val = from[d >= len ? lane : lane % d];
-                    pend_pos = pos; pend_len = len;
-                } else {
-                    if (d >= len) { for (unsigned int i = lane; i < len; i += 32) dst[pos + i] = from[i]; }
-                    else { for (unsigned int i = lane; i < len; i += 32) dst[pos + i] = from[i % d]; }
-                    __syncwarp();
-                }
+                if (d >= len) { for (unsigned int i = lane; i < len; i += 32) dst[pos + i] = from[i]; }
+                else { for (unsigned int i = lane; i < len; i += 32) dst[pos + i] = from[i % d]; }
                 pos += len;
+                __syncwarp();
             }
         }
-        if (pend_len) { if (lane < pend_len) dst[pend_pos + lane] = pend_val; pend_len = 0; }
         if (!err && br.used() > 8ll * (long long)M.in_len) err = 1;   // ran past the end of the payload
         if (!err && pos != M.out_len) err = 2;
         __syncwarp();
@@ -297,7 +282,16 @@ __global__ void __launch_bounds__(kInfWarps * 32) k_inflate_bgzf(const uint8_t* 
             const unsigned int per = (M.out_len + 31) / 32;
             const unsigned int b0 = min(M.out_len, lane * per), b1 = min(M.out_len, b0 + per);
             unsigned int c = 0xFFFFFFFFu;
-            for (unsigned int i = b0; i < b1; i++) c = s_crc[(c ^ dst[i]) & 0xFFu] ^ (c >> 8);
+            {   // bytes up to a 4-byte border, then whole words (one load per four table steps), then the tail
+                unsigned int i = b0;
+                for (; i < b1 && ((uintptr_t)(dst + i) & 3u); i++) c = s_crc[(c ^ dst[i]) & 0xFFu] ^ (c >> 8);
+                for (; i + 4 <= b1; i += 4) {
+                    c ^= *reinterpret_cast<const uint32_t*>(dst + i);
+                    c = s_crc[c & 0xFFu] ^ (c >> 8); c = s_crc[c & 0xFFu] ^ (c >> 8);
+                    c = s_crc[c & 0xFFu] ^ (c >> 8); c = s_crc[c & 0xFFu] ^ (c >> 8);
+                }
+                for (; i < b1; i++) c = s_crc[(c ^ dst[i]) & 0xFFu] ^ (c >> 8);
+            }
             c ^= 0xFFFFFFFFu;
             // operator for `per` zero bytes: start from the one-bit operator, square to one byte, then square-and-multiply
             unsigned int* even = s_mat[warp][0];
