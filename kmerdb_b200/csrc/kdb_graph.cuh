@@ -34,10 +34,15 @@ __device__ __forceinline__ unsigned long long upper_rec(const unsigned long long
 }
 
 // forward and reverse-complement id of the k letters at s (all ACGT); canonical = min
-__device__ __forceinline__ unsigned long long window_id(const uint8_t* __restrict__ s, int k, int canonical) {
+// (`lut`: a shared-memory copy of the class table — the __constant__ table indexed by a data-dependent byte serialises the warp)
+__device__ __forceinline__ void load_lut(uint8_t* s_lut) {
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) s_lut[i] = c_class_lut[i];
+    __syncthreads();
+}
+__device__ __forceinline__ unsigned long long window_id(const uint8_t* __restrict__ s, int k, int canonical, const uint8_t* lut) {
     unsigned long long fwd = 0, rc = 0;
     for (int j = 0; j < k; j++) {
-        const unsigned long long code = c_class_lut[s[j]] & 3u;
+        const unsigned long long code = lut[s[j]] & 3u;
         fwd = (fwd << 2) | code;
         rc |= (3ull - code) << (2 * j);
     }
@@ -49,10 +54,12 @@ __device__ __forceinline__ unsigned long long window_id(const uint8_t* __restric
 __global__ void __launch_bounds__(256) k8_check_letters(const uint8_t* __restrict__ letters, unsigned long long n_letters,
                                                         const unsigned long long* __restrict__ rec_off, unsigned long long n_recs,
                                                         int k, unsigned long long* err_key) {
+    __shared__ uint8_t s_lut[256];
+    load_lut(s_lut);
     const unsigned long long g = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     unsigned long long key = ~0ull;
     if (g < n_letters) {
-        const uint8_t cl = c_class_lut[letters[g]];
+        const uint8_t cl = s_lut[letters[g]];
         if (cl > C_T) {
             const unsigned long long r = upper_rec(rec_off, n_recs, g);
             if (cl == C_N) key = gkey(r, G_LETTER, g - rec_off[r], 0);
@@ -72,14 +79,22 @@ __global__ void __launch_bounds__(256) k8_edge_rows(const uint8_t* __restrict__ 
                                                     unsigned long long* __restrict__ rec, unsigned long long* __restrict__ pos1,
                                                     unsigned long long* __restrict__ id1, unsigned long long* __restrict__ pos2,
                                                     unsigned long long* __restrict__ id2) {
+    __shared__ uint8_t s_lut[256];
+    load_lut(s_lut);
     const unsigned long long e = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     if (e >= n_edges) return;
     const unsigned long long r = upper_rec(edge_off, n_recs, e);
     const unsigned long long i = e - edge_off[r] + 1;                 // graph.py:150: i >= 1
     const uint8_t* s = letters + rec_off[r] + i - 1;
     rec[e] = r; pos1[e] = i - 1; pos2[e] = i;
-    id1[e] = window_id(s, k, canonical);
-    id2[e] = window_id(s + 1, k, canonical);
+    // both windows from one walk over the k + 1 letters: the second id is the first one rolled by a letter
+    unsigned long long fwd = 0, rc = 0;
+    for (int j = 0; j < k; j++) { const unsigned long long code = s_lut[s[j]] & 3u; fwd = (fwd << 2) | code; rc |= (3ull - code) << (2 * j); }
+    id1[e] = (canonical && rc < fwd) ? rc : fwd;
+    const unsigned long long c2 = s_lut[s[k]] & 3u, mask = k == 32 ? ~0ull : ((1ull << (2 * k)) - 1ull);
+    fwd = ((fwd << 2) | c2) & mask;
+    rc = (rc >> 2) | ((3ull - c2) << (2 * (k - 1)));
+    id2[e] = (canonical && rc < fwd) ? rc : fwd;
 }
 
 // ---- aggregated edge weights from the forward (k+1)-mer histogram -------------------------------------
@@ -164,11 +179,11 @@ __global__ void __launch_bounds__(256) k7_edge_weight_write(const unsigned long 
 
 // ---- minimizers ---------------------------------------------------------------------------------------
 // id of the window at s: kIdNone when it holds N (kmer.py:287-289); *bad is raised for other non-ACGT letters
-__device__ __forceinline__ unsigned long long window_id_checked(const uint8_t* __restrict__ s, int k, unsigned int* bad) {
+__device__ __forceinline__ unsigned long long window_id_checked(const uint8_t* __restrict__ s, int k, unsigned int* bad, const uint8_t* lut) {
     unsigned long long fwd = 0, rc = 0;
     bool has_n = false;
     for (int j = 0; j < k; j++) {
-        const uint8_t cl = c_class_lut[s[j]];
+        const uint8_t cl = lut[s[j]];
         if (cl == C_N) has_n = true;
         else if (cl == C_IUPAC) *bad |= 2u;
         else if (cl > C_T) *bad |= 1u;
@@ -182,10 +197,12 @@ __device__ __forceinline__ unsigned long long window_id_checked(const uint8_t* _
 // minimizer.py:65-81: row i = (canonical id of seq[i:i+k], i % W == 0), i < n_rows
 __global__ void __launch_bounds__(256) k8_min_compat(const uint8_t* __restrict__ seq, unsigned long long n_rows, int k, unsigned long long window,
                                                      unsigned long long* __restrict__ ids, uint8_t* __restrict__ is_min, unsigned int* bad_flag) {
+    __shared__ uint8_t s_lut[256];
+    load_lut(s_lut);
     const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     unsigned int bad = 0;
     if (i < n_rows) {
-        ids[i] = window_id_checked(seq + i, k, &bad);
+        ids[i] = window_id_checked(seq + i, k, &bad, s_lut);
         is_min[i] = (uint8_t)(i % window == 0);
     }
     if (bad) atomicOr(bad_flag, bad);
@@ -194,9 +211,11 @@ __global__ void __launch_bounds__(256) k8_min_compat(const uint8_t* __restrict__
 // canonical ids of all windows of one sequence (true minimizers, step 1)
 __global__ void __launch_bounds__(256) k8_window_ids(const uint8_t* __restrict__ seq, unsigned long long n_win, int k,
                                                      unsigned long long* __restrict__ ids, unsigned int* bad_flag) {
+    __shared__ uint8_t s_lut[256];
+    load_lut(s_lut);
     const unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x;
     unsigned int bad = 0;
-    if (i < n_win) { const unsigned long long v = window_id_checked(seq + i, k, &bad); if (v == kIdNone) bad |= 2u; ids[i] = v; }
+    if (i < n_win) { const unsigned long long v = window_id_checked(seq + i, k, &bad, s_lut); if (v == kIdNone) bad |= 2u; ids[i] = v; }
     if (bad) atomicOr(bad_flag, bad);
 }
 
