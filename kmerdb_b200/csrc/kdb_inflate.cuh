@@ -155,7 +155,7 @@ __device__ __forceinline__ unsigned int gf2_times(const unsigned int* mat, unsig
 }
 
 // status per member: 0 ok, 1 malformed stream, 2 length mismatch, 3 CRC mismatch
-__global__ void __launch_bounds__(kInfWarps * 32, 6) k_inflate_bgzf(const uint8_t* __restrict__ comp, const BgzfMember* __restrict__ members, unsigned int n_members,
+__global__ void __launch_bounds__(kInfWarps * 32) k_inflate_bgzf(const uint8_t* __restrict__ comp, const BgzfMember* __restrict__ members, unsigned int n_members,
                                                                  uint8_t* __restrict__ out, unsigned int* __restrict__ status, int check_crc) {
     __shared__ InfTables s_tab[kInfWarps];
     __shared__ unsigned int s_mat[kInfWarps][2][32];
