@@ -246,13 +246,28 @@ __global__ void __launch_bounds__(TB == 14 ? kBucketThreads : 1024) k3p_count(co
     for (uint32_t i = tid; i < (1u << TB); i += nthr) s_tab[i] = 0;
     __syncthreads();
     const uint4* src = reinterpret_cast<const uint4*>(stream + (size_t)b * cap);
-    for (uint32_t u = u0 + tid; u < u1; u += nthr) {
-        const uint4 v = __ldcs(src + u);
-        const uint32_t w[4] = {v.x, v.y, v.z, v.w};
-        const uint32_t valid = min(8u, end - 8 * u);
+    // four 16-byte loads in flight per thread (the kernel sat in long-scoreboard stalls with one), and every atomic unconditional:
+    // 0xFFFF — the padding of k3s_partition's runs, and what entries past the end of the stream are turned into — lands in a per-lane
+    // dummy bin behind the table instead of being branched around
+    const uint32_t dummy = (1u << TB) + (tid & 31u);
+    for (uint32_t ub = u0; ub < u1; ub += 4 * nthr) {
+        uint4 v[4];
+        uint32_t valid[4];
 #pragma unroll
-        for (int q = 0; q < 8; q++)
-            if ((uint32_t)q < valid) atomicAdd(&s_tab[min((w[q >> 1] >> (16 * (q & 1))) & 0xFFFFu, (1u << TB) + (tid & 31u))], 1u);   // (0xFFFF pads the runs of k3s_partition: per-lane dummy bins behind the table)
+        for (int r = 0; r < 4; r++) {
+            const uint32_t u = ub + r * nthr + tid;
+            valid[r] = u < u1 ? min(8u, end - 8 * u) : 0u;
+            v[r] = valid[r] ? __ldcs(src + u) : make_uint4(0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu, 0xFFFFFFFFu);
+        }
+#pragma unroll
+        for (int r = 0; r < 4; r++) {
+            const uint32_t w[4] = {v[r].x, v[r].y, v[r].z, v[r].w};
+#pragma unroll
+            for (int q = 0; q < 8; q++) {
+                const uint32_t e = (w[q >> 1] >> (16 * (q & 1))) & 0xFFFFu;
+                atomicAdd(&s_tab[(uint32_t)q < valid[r] ? min(e, dummy) : dummy], 1u);
+            }
+        }
     }
     __syncthreads();
     if (low_bits) {                                                   // bin p of bucket b (k3s_partition): runs of 2^kBucketShift consecutive ids
