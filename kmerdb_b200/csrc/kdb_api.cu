@@ -42,13 +42,6 @@ struct kdb_ctx {
     unsigned int* tab32 = nullptr;
     unsigned long long* tab64 = nullptr;
     Accum* acc = nullptr;
-    ScanCarry* carry = nullptr;
-    unsigned long long* carry_len = nullptr;   // 2 x u64: partial lengths of the last record seen
-    TileSummary* tile_sum = nullptr;
-    TileState* tile_state = nullptr;
-    size_t tile_cap = 0;
-    unsigned long long* rec_len = nullptr;
-    size_t rec_cap = 0;
     uint8_t* feed_buf = nullptr;
     size_t feed_cap = 0;
     uint32_t* packed = nullptr;                 // K2 output / K3 input, one region per tile of the pass
@@ -67,7 +60,6 @@ struct kdb_ctx {
     size_t stream_cap = 0;
     unsigned int* cursor = nullptr;             // n_buckets cursors + n_buckets fail bases
     // single-pass tokeniser (k2s_encode): look-back status words, border records, ticket, device-resident carry
-    bool single_pass = false;
     TileLook* look = nullptr;                   // n_tiles status words, then n_tiles TileRec (one allocation)
     TileRec* trec = nullptr;
     size_t look_cap = 0;
@@ -88,9 +80,7 @@ struct kdb_ctx {
     void* null_scratch = nullptr;               // kdb_nullomers: per-block zero counts and offsets
     size_t null_cap = 0;
     // host mirrors
-    ScanCarry h_carry{};
-    bool have_carry = false;
-    unsigned long long carry_rec_id = 0, fq_rec_base = 0;
+    unsigned long long total_reads_host = 0;    // records of the job (read back from the device carry at kdb_finish / after a reduce)
     unsigned long long bytes_since_fold = 0;
     bool job_started = false, finished = false, host_layout = false;
     bool tab32_clean = false;                   // tab32 is all zero (every fold leaves it so): reset skips the 4^k x 4 B memset
@@ -186,8 +176,8 @@ extern "C" void kdb_destroy(kdb_ctx* ctx) {
     for (kdb_ctx* f : ctx->followers) f->leader = nullptr;
     if (ctx->leader) { auto& v = ctx->leader->followers; v.erase(std::remove(v.begin(), v.end(), ctx), v.end()); }
     cudaSetDevice(ctx->device);
-    cudaFree(ctx->tab32); cudaFree(ctx->tab64); cudaFree(ctx->acc); cudaFree(ctx->carry); cudaFree(ctx->carry_len);
-    cudaFree(ctx->tile_sum); /* tile_state lives inside the tile_sum allocation */ cudaFree(ctx->rec_len); cudaFree(ctx->feed_buf); cudaFree(ctx->packed); cudaFree(ctx->stream); cudaFree(ctx->cursor);
+    cudaFree(ctx->tab32); cudaFree(ctx->tab64); cudaFree(ctx->acc);
+    cudaFree(ctx->feed_buf); cudaFree(ctx->packed); cudaFree(ctx->stream); cudaFree(ctx->cursor);
     cudaFree(ctx->look); /* trec lives inside the look allocation */ cudaFree(ctx->ticket); cudaFree(ctx->pcarry); cudaFree(ctx->zero_row); cudaFree(ctx->null_scratch); cudaFree(ctx->d_pack); cudaFree(ctx->comp_buf);
     if (ctx->comm && nccl_api().ok) nccl_api().CommDestroy(ctx->comm);
     if (ctx->ev_red0) cudaEventDestroy(ctx->ev_red0);
@@ -208,13 +198,10 @@ static int reset_state(kdb_ctx* ctx) {
     Accum a{};
     a.min_len = ~0ull; a.err_key = ~0ull;
     CK(cudaMemcpyAsync(ctx->acc, &a, sizeof a, cudaMemcpyHostToDevice, ctx->s_compute));
-    CK(cudaMemsetAsync(ctx->carry, 0, sizeof(ScanCarry), ctx->s_compute));
-    CK(cudaMemsetAsync(ctx->carry_len, 0, 2 * sizeof(unsigned long long), ctx->s_compute));
     CK(cudaMemsetAsync(ctx->pcarry, 0, 2 * sizeof(PassCarry), ctx->s_compute));
     ctx->pc_idx = 0;
     CK(cudaStreamSynchronize(ctx->s_compute));
-    ctx->h_carry = ScanCarry{};
-    ctx->have_carry = false; ctx->carry_rec_id = 0; ctx->fq_rec_base = 0; ctx->bytes_since_fold = 0;
+    ctx->total_reads_host = 0; ctx->bytes_since_fold = 0;
     ctx->job_started = true; ctx->finished = false; ctx->host_layout = false; ctx->tab64_valid = false;
     ctx->stats = kdb_stats_t{}; ctx->timing = kdb_timing_t{};
     ctx->stats_dirty = false; ctx->reduce_timed = false; ctx->not_root = false;
@@ -270,14 +257,11 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
     if ((e = cudaMalloc(&ctx->tab32, ctx->nbins * sizeof(unsigned int))) != cudaSuccess) return fail("cudaMalloc tab32", e);
     if ((e = cudaMalloc(&ctx->tab64, ctx->nbins * sizeof(unsigned long long))) != cudaSuccess) return fail("cudaMalloc tab64", e);
     if ((e = cudaMalloc(&ctx->acc, sizeof(Accum))) != cudaSuccess) return fail("cudaMalloc acc", e);
-    if ((e = cudaMalloc(&ctx->carry, sizeof(ScanCarry))) != cudaSuccess) return fail("cudaMalloc carry", e);
-    if ((e = cudaMalloc(&ctx->carry_len, 2 * sizeof(unsigned long long))) != cudaSuccess) return fail("cudaMalloc carry_len", e);
     if ((e = cudaMalloc(&ctx->pcarry, 2 * sizeof(PassCarry))) != cudaSuccess) return fail("cudaMalloc pcarry", e);
     if ((e = cudaMalloc(&ctx->ticket, sizeof(unsigned int))) != cudaSuccess) return fail("cudaMalloc ticket", e);
     if ((e = cudaMalloc(&ctx->zero_row, 256)) != cudaSuccess) return fail("cudaMalloc zero_row", e);
     if ((e = cudaMemset(ctx->zero_row, 0, 256)) != cudaSuccess) return fail("cudaMemset zero_row", e);
-    ctx->single_pass = !getenv("KDB_TWO_PASS");
-    if (ctx->single_pass && !tensor_map_encoder()) { g_last_error = "cuTensorMapEncodeTiled is not available from this driver"; kdb_destroy(ctx); return nullptr; }
+    if (!tensor_map_encoder()) { g_last_error = "cuTensorMapEncodeTiled is not available from this driver"; kdb_destroy(ctx); return nullptr; }
     // launch geometry: persistent CTAs, a whole number per SM
     int rc;
     ctx->hist_kernel = k3_kernel(k, ctx->canonical);
@@ -304,15 +288,14 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
         if (!rc) rc = occupancy_grid(ctx->part_kernel, kPartThreads, dyn, &ctx->part_grid);
         if ((e = cudaMalloc(&ctx->cursor, 2 * ctx->n_buckets * sizeof(unsigned int))) != cudaSuccess) return fail("cudaMalloc cursor", e);
     }
-    if (!rc && ctx->single_pass) rc = ctx->fastq ? occupancy_grid(k2s_encode<true>, kThreads, 0, &ctx->encode_grid) : occupancy_grid(k2s_encode<false>, kThreads, 0, &ctx->encode_grid);
-    else if (!rc) rc = ctx->fastq ? occupancy_grid(k2_encode<true>, kThreads, 0, &ctx->encode_grid) : occupancy_grid(k2_encode<false>, kThreads, 0, &ctx->encode_grid);
+    if (!rc) rc = ctx->fastq ? occupancy_grid(k2s_encode<true>, kThreads, 0, &ctx->encode_grid) : occupancy_grid(k2s_encode<false>, kThreads, 0, &ctx->encode_grid);
     if (rc) { kdb_destroy(ctx); return nullptr; }
     if (reset_state(ctx)) { g_last_error = ctx->err; kdb_destroy(ctx); return nullptr; }
     if ((e = cudaGetLastError()) != cudaSuccess) return fail("kdb_create", e);
     return ctx;
 }
 
-// ---- one pass: K1 scan -> (size rec_len) -> K2+K3 count -> K4 record checks ------------------------
+// ---- passes -----------------------------------------------------------------------------------------------
 static int ensure(kdb_ctx* ctx, void** p, size_t* cap, size_t need, size_t elem) {
     if (need <= *cap) return KDB_OK;
     if (*p) CK(cudaFree(*p));
@@ -351,18 +334,6 @@ static int fold_now(kdb_ctx* ctx, bool count_unique = false, cudaStream_t st = n
     ctx->bytes_since_fold = 0;
     ctx->tab64_valid = true;
     ctx->tab32_clean = true;
-    return KDB_OK;
-}
-
-// The last record seen so far is complete: run the record check on it alone.
-static int close_carry_record(kdb_ctx* ctx) {
-    if (!ctx->have_carry) return KDB_OK;
-    if (ctx->fastq) k4_check_records<true><<<1, 32, 0, ctx->s_compute>>>(ctx->carry_len, 1, ctx->carry_rec_id, ctx->short_k, ctx->acc);
-    else k4_check_records<false><<<1, 32, 0, ctx->s_compute>>>(ctx->carry_len, 1, ctx->carry_rec_id, ctx->short_k, ctx->acc);
-    CK(cudaGetLastError());
-    ctx->timing.total_launches++;
-    CK(cudaMemsetAsync(ctx->carry_len, 0, 2 * sizeof(unsigned long long), ctx->s_compute));
-    ctx->have_carry = false;
     return KDB_OK;
 }
 
@@ -411,96 +382,6 @@ static int count_stage(kdb_ctx* ctx, kdb_ctx* src, unsigned int n_tiles, unsigne
         ctx->timing.total_launches++;
         ctx->bytes_since_fold += hi - lo;
     }
-    return KDB_OK;
-}
-
-static int run_pass(kdb_ctx* ctx, const uint8_t* text, unsigned long long lo, unsigned long long hi, unsigned long long n) {
-    const unsigned int n_tiles = (unsigned int)((hi - lo + kTile - 1) / kTile);
-    if (int rc = ensure(ctx, (void**)&ctx->tile_sum, &ctx->tile_cap, n_tiles, sizeof(TileSummary) + sizeof(TileState))) return rc;
-    ctx->tile_state = reinterpret_cast<TileState*>(ctx->tile_sum + ctx->tile_cap);
-    // the u32 table must not wrap: every text byte adds at most 2 to one bin (DESIGN.md "fold rule")
-    if (ctx->bytes_since_fold + (hi - lo) > 0x7fffffffull) if (int rc = fold_now(ctx)) return rc;
-
-    const ScanCarry before = ctx->h_carry;
-    CK(cudaGetLastError());
-    CK(cudaEventRecord(ctx->ev[0], ctx->s_compute));
-    k1_tile_summary<<<n_tiles, kThreads, 0, ctx->s_compute>>>(text, lo, hi, ctx->tile_sum);
-    CK(cudaGetLastError());
-    k1_carry_scan<<<1, 1024, 0, ctx->s_compute>>>(ctx->tile_sum, ctx->tile_state, n_tiles, ctx->carry);
-    CK(cudaGetLastError());
-    CK(cudaEventRecord(ctx->ev[1], ctx->s_compute));
-    CK(cudaMemcpyAsync(&ctx->h_carry, ctx->carry, sizeof(ScanCarry), cudaMemcpyDeviceToHost, ctx->s_compute));
-    CK(cudaStreamSynchronize(ctx->s_compute));
-    const ScanCarry after = ctx->h_carry;
-
-    // record ids touched by this pass: [rec_first, rec_last]
-    unsigned long long rec_first, rec_last;
-    bool any_record;
-    if (ctx->fastq) {
-        rec_first = ctx->fq_rec_base + (before.ls_total ? (before.ls_total - 1) / 4 : 0);
-        rec_last = ctx->fq_rec_base + (after.ls_total ? (after.ls_total - 1) / 4 : 0);
-        any_record = after.ls_total != 0;
-    } else {
-        rec_first = before.hdr_total ? before.hdr_total - 1 : 0;
-        rec_last = after.hdr_total ? after.hdr_total - 1 : 0;
-        any_record = after.hdr_total != 0;
-    }
-    if (ctx->have_carry && ctx->carry_rec_id != rec_first) if (int rc = close_carry_record(ctx)) return rc;
-    const size_t per = ctx->fastq ? 2 : 1;
-    const size_t n_entries = (size_t)(rec_last - rec_first + 1);
-    if (int rc = ensure(ctx, (void**)&ctx->rec_len, &ctx->rec_cap, n_entries * per, sizeof(unsigned long long))) return rc;
-    CK(cudaMemsetAsync(ctx->rec_len, 0, n_entries * per * sizeof(unsigned long long), ctx->s_compute));
-    if (ctx->have_carry)
-        CK(cudaMemcpyAsync(ctx->rec_len, ctx->carry_len, per * sizeof(unsigned long long), cudaMemcpyDeviceToDevice, ctx->s_compute));
-
-    if (int rc = ensure(ctx, (void**)&ctx->packed, &ctx->packed_cap, (size_t)n_tiles * kPackStride, sizeof(uint32_t))) return rc;
-    EncodeParams P{};
-    P.text = text; P.lo = lo; P.hi = hi; P.n = n; P.tiles = ctx->tile_state; P.n_tiles = n_tiles; P.k = ctx->k;
-    P.skip_n = ctx->skip_n; P.k_halo = std::max(ctx->k, ctx->k_halo); P.packed = ctx->packed; P.rec_len = ctx->rec_len;
-    P.rec_first = rec_first; P.fq_rec_base = ctx->fq_rec_base; P.acc = ctx->acc;
-    CK(cudaEventRecord(ctx->ev[2], ctx->s_compute));
-    {
-        const int grid = (int)std::min<unsigned int>(n_tiles, (unsigned int)ctx->encode_grid);
-        if (ctx->fastq) k2_encode<true><<<grid, kThreads, 0, ctx->s_compute>>>(P);
-        else k2_encode<false><<<grid, kThreads, 0, ctx->s_compute>>>(P);
-        CK(cudaGetLastError());
-    }
-    CK(cudaEventRecord(ctx->ev[6], ctx->s_compute));
-    if (int rc = count_stage(ctx, ctx, n_tiles, lo, hi)) return rc;
-    CK(cudaEventRecord(ctx->ev[3], ctx->s_compute));
-    for (kdb_ctx* f : ctx->followers) {                                  // larger k of a sweep, from the same packed stream
-        CK(cudaEventRecord(f->ev[6], ctx->s_compute));
-        if (int rc = count_stage(f, ctx, n_tiles, lo, hi)) { ctx->err = f->err; return rc; }
-        CK(cudaEventRecord(f->ev[3], ctx->s_compute));
-    }
-    CK(cudaEventRecord(ctx->ev[5], ctx->s_compute));
-    const unsigned long long n_complete = n_entries - 1;
-    if (n_complete) {
-        const int g4 = (int)std::min<unsigned long long>((n_complete + 255) / 256, 148ull * 8);
-        if (ctx->fastq) k4_check_records<true><<<g4, 256, 0, ctx->s_compute>>>(ctx->rec_len, n_complete, rec_first, ctx->short_k, ctx->acc);
-        else k4_check_records<false><<<g4, 256, 0, ctx->s_compute>>>(ctx->rec_len, n_complete, rec_first, ctx->short_k, ctx->acc);
-        CK(cudaGetLastError());
-        ctx->timing.total_launches++;
-    }
-    if (any_record) {
-        CK(cudaMemcpyAsync(ctx->carry_len, ctx->rec_len + (n_entries - 1) * per, per * sizeof(unsigned long long), cudaMemcpyDeviceToDevice, ctx->s_compute));
-        ctx->have_carry = true; ctx->carry_rec_id = rec_last;
-    }
-    CK(cudaEventRecord(ctx->ev[4], ctx->s_compute));
-    CK(cudaEventSynchronize(ctx->ev[4]));
-    float ms = 0;
-    CK(cudaEventElapsedTime(&ms, ctx->ev[0], ctx->ev[1])); ctx->timing.scan_ms += ms;
-    CK(cudaEventElapsedTime(&ms, ctx->ev[2], ctx->ev[6])); ctx->timing.encode_ms += ms;
-    CK(cudaEventElapsedTime(&ms, ctx->ev[6], ctx->ev[3])); ctx->timing.count_ms += ms;
-    CK(cudaEventElapsedTime(&ms, ctx->ev[6], ctx->ev[7])); ctx->timing.partition_ms += ms;
-    CK(cudaEventElapsedTime(&ms, ctx->ev[5], ctx->ev[4])); ctx->timing.final_ms += ms;
-    for (kdb_ctx* f : ctx->followers) {
-        CK(cudaEventElapsedTime(&ms, f->ev[6], f->ev[3])); f->timing.count_ms += ms;
-        CK(cudaEventElapsedTime(&ms, f->ev[6], f->ev[7])); f->timing.partition_ms += ms;
-    }
-    ctx->timing.count_launches++;
-    ctx->timing.total_launches += 4;
-    ctx->bytes_since_fold += hi - lo;
     return KDB_OK;
 }
 
@@ -578,21 +459,12 @@ static int begin_feed(kdb_ctx* ctx) {
     if (ctx->leader) { ctx->err = "kdb_feed on a follower: feed its leader"; return KDB_E_STATE; }
     if (ctx->finished) { ctx->err = "kdb_feed after kdb_finish (call kdb_reset first)"; return KDB_E_STATE; }
     if (!ctx->job_started) { CK(cudaEventRecord(ctx->ev_job0, ctx->s_compute)); ctx->job_started = true; }
-    if (ctx->single_pass) return KDB_OK;                                 // (the end of the feed before reset the line indices on the device)
-    // line indices restart with every fragment (fragments begin at a record boundary)
-    ctx->h_carry.ls_total = 0; ctx->h_carry.last = 0;
-    CK(cudaMemcpyAsync(ctx->carry, &ctx->h_carry, sizeof(ScanCarry), cudaMemcpyHostToDevice, ctx->s_compute));
-    return KDB_OK;
+    return KDB_OK;                                                       // (line indices restart with every fragment: the end of the feed before reset them on the device)
 }
 
 static int end_feed(kdb_ctx* ctx, size_t n) {
-    if (ctx->single_pass) {
-        // line indices restart with every fragment; a FASTQ fragment ends with a complete record
-        if (int rc = close_carry2(ctx, ctx->fastq ? 3 : 2)) return rc;
-    } else if (ctx->fastq) {
-        if (ctx->h_carry.ls_total % 4 != 0) ctx->host_layout = true;   // truncated / blank-line tail: host tokeniser decides
-        ctx->fq_rec_base += ctx->h_carry.ls_total / 4;
-    }
+    // line indices restart with every fragment; a FASTQ fragment ends with a complete record
+    if (int rc = close_carry2(ctx, ctx->fastq ? 3 : 2)) return rc;
     ctx->timing.bytes_fed += n;
     return KDB_OK;
 }
@@ -603,9 +475,9 @@ extern "C" int kdb_feed_device(kdb_ctx* ctx, const uint8_t* dev_bytes, size_t n)
     if (n == 0) return KDB_OK;
     if (!dev_bytes || ((uintptr_t)dev_bytes & 15)) { ctx->err = "device text must be 16-byte aligned"; return KDB_E_ARG; }
     if (int rc = begin_feed(ctx)) return rc;
-    const unsigned long long pass = ctx->single_pass ? kPassBytes : 1ull << 30;     // (TileLook: the counts of a pass fit 30 bits)
+    const unsigned long long pass = kPassBytes;                          // (TileLook: the counts of a pass fit 30 bits)
     for (unsigned long long lo = 0; lo < n; lo += pass)
-        if (int rc = (ctx->single_pass ? run_pass2 : run_pass)(ctx, dev_bytes, lo, std::min<unsigned long long>(lo + pass, n), n)) return rc;
+        if (int rc = run_pass2(ctx, dev_bytes, lo, std::min<unsigned long long>(lo + pass, n), n)) return rc;
     return end_feed(ctx, n);
 }
 
@@ -630,7 +502,7 @@ extern "C" int kdb_feed_host(kdb_ctx* ctx, const uint8_t* bytes, size_t n) {
     for (size_t i = 0; i < n_pass; i++) {
         const unsigned long long lo = i * pass, hi = std::min<unsigned long long>(lo + pass, n);
         CK(cudaStreamWaitEvent(ctx->s_compute, ctx->ev_copy[i], 0));
-        if (int rc = (ctx->single_pass ? run_pass2 : run_pass)(ctx, ctx->feed_buf, lo, hi, n)) return rc;
+        if (int rc = run_pass2(ctx, ctx->feed_buf, lo, hi, n)) return rc;
     }
     float ms = 0;
     CK(cudaEventSynchronize(ctx->ev_copy[n_pass - 1]));
@@ -652,15 +524,15 @@ static int fill_stats(kdb_ctx* ctx) {
     Accum a;
     CK(cudaMemcpyAsync(&a, ctx->acc, sizeof a, cudaMemcpyDeviceToHost, ctx->s_compute));
     CK(cudaStreamSynchronize(ctx->s_compute));
-    if (ctx->single_pass) {
+    {
         PassCarry pc;
         CK(cudaMemcpyAsync(&pc, ctx->pcarry + ctx->pc_idx, sizeof pc, cudaMemcpyDeviceToHost, ctx->s_compute));
         CK(cudaStreamSynchronize(ctx->s_compute));
-        ctx->fq_rec_base = pc.fq_rec_base; ctx->h_carry.hdr_total = pc.hdr_total;
+        ctx->total_reads_host = ctx->fastq ? pc.fq_rec_base : pc.hdr_total;
     }
     kdb_stats_t& s = ctx->stats;
     s = kdb_stats_t{};
-    s.total_reads = ctx->fastq ? ctx->fq_rec_base : ctx->h_carry.hdr_total;
+    s.total_reads = ctx->total_reads_host;
     s.total_kmers = a.total_kmers; s.unique_kmers = a.unique; s.sum_len = a.sum_len;
     s.min_len = a.min_len == ~0ull ? 0 : a.min_len; s.max_len = a.max_len;
     for (int i = 0; i < 4; i++) s.mono[i] = a.mono[i];
@@ -708,8 +580,7 @@ extern "C" int kdb_finish(kdb_ctx* ctx) {
     if (ctx->leader) return finish_follower(ctx);
     if (!ctx->job_started) { CK(cudaEventRecord(ctx->ev_job0, ctx->s_compute)); ctx->job_started = true; }
     CK(cudaEventRecord(ctx->ev[0], ctx->s_compute));
-    if (ctx->single_pass) { if (int rc = close_carry2(ctx, 1)) return rc; }
-    else if (int rc = close_carry_record(ctx)) return rc;
+    if (int rc = close_carry2(ctx, 1)) return rc;
     CK(cudaMemsetAsync(&ctx->acc->unique, 0, sizeof(unsigned long long), ctx->s_compute));
     if (int rc = fold_now(ctx, true)) return rc;
     CK(cudaEventRecord(ctx->ev[1], ctx->s_compute));
@@ -833,10 +704,10 @@ extern "C" int kdb_import_partials(kdb_ctx* ctx, const uint64_t* in16) {
     a.n_windows_with_n = in16[7]; a.min_len = in16[8]; a.max_len = in16[9]; a.err_key = in16[10];
     a.layout_flag = in16[11] ? 1 : 0;
     CK(cudaMemcpy(ctx->acc, &a, sizeof a, cudaMemcpyHostToDevice));
-    if (ctx->fastq) ctx->fq_rec_base = in16[0]; else ctx->h_carry.hdr_total = in16[0];
-    if (ctx->single_pass) {
+    ctx->total_reads_host = in16[0];
+    {
         PassCarry pc{};
-        pc.fq_rec_base = ctx->fq_rec_base; pc.hdr_total = ctx->h_carry.hdr_total;
+        if (ctx->fastq) pc.fq_rec_base = in16[0]; else pc.hdr_total = in16[0];
         CK(cudaMemcpy(ctx->pcarry + ctx->pc_idx, &pc, sizeof pc, cudaMemcpyHostToDevice));
     }
     ctx->host_layout = false;
@@ -952,7 +823,6 @@ extern "C" int kdb_inflate_bgzf(int device, const uint8_t* raw, size_t n, uint8_
 extern "C" int kdb_feed_bgzf_host(kdb_ctx* ctx, const uint8_t* raw, size_t n) {
     if (!ctx || !raw) return KDB_E_ARG;
     if (int rc = set_device(ctx, ctx->device)) return rc;
-    if (!ctx->single_pass) { ctx->err = "kdb_feed_bgzf_host needs the single-pass tokeniser"; return KDB_E_STATE; }
     size_t nm = 0; uint64_t text = 0;
     if (int rc = kdb_bgzf_index(raw, n, nullptr, 0, &nm, &text)) return rc;
     if (text == 0) return KDB_OK;

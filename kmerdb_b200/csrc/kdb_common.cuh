@@ -2,10 +2,9 @@
 //
 // Data layout in HBM:
 //   text      : the uncompressed FASTA/FASTQ bytes of one feed, contiguous, 16-byte aligned
-//   tile_state: one TileState per 16 KiB tile of the current pass (K1 output)
+//   look/trec : decoupled look-back status word and border-record lengths per 16 KiB tile (k2s_encode)
 //   tab32     : uint32[4^k] working histogram (red.global.add.u32 target; 64 MiB at k=12, L2-resident)
 //   tab64     : uint64[4^k] result histogram (tab32 is folded into it before it can overflow)
-//   rec_len   : uint64 per record of the current pass (letters; FASTQ: letters, quality chars)
 //   acc       : Accum, the fused scalar reductions
 #pragma once
 #include <cuda_runtime.h>
@@ -35,28 +34,6 @@ enum : uint32_t { K_HEADER = 0, K_SEQ = 1, K_IGNORE = 2, K_QUAL = 3 };
 // Priority of a raise inside one record, in the order the reference meets them:
 // is_sequence_na over the whole record (kmer.py:519) -> length check (:461-463) -> windows (:309).
 enum : uint32_t { P_ALPHABET = 0, P_SHORT = 1, P_IUPAC = 2 };
-
-struct TileState {
-    unsigned long long ls_base;   // line starts before this tile (within the feed)
-    unsigned long long hdr_base;  // FASTA title lines before this tile (within the file)
-    unsigned int last;            // class of the last line start before the tile: 0 none, 1 other, 2 '>'
-    unsigned int pad;
-};
-
-struct TileSummary {
-    unsigned int ls;    // line starts inside the tile
-    unsigned int hdr;   // of which begin with '>'
-    unsigned int last;  // 0 none, 1 other, 2 '>'  (right-most line start in the tile)
-    unsigned int pad;
-};
-
-// Running totals carried from pass to pass (device resident, updated by the K1 carry scan).
-struct ScanCarry {
-    unsigned long long ls_total;
-    unsigned long long hdr_total;
-    unsigned int last;
-    unsigned int pad;
-};
 
 // ---- single-pass tokeniser (k2s_encode): decoupled look-back over the tiles of a pass --------------------------
 // One status word per tile, written and read whole (no fence is needed around it): [63:62] state (0 nothing, 1 tile aggregate,
@@ -96,22 +73,6 @@ struct Accum {
     unsigned long long unique;
     unsigned int layout_flag;        // != 0: the text needs the host tokeniser
     unsigned int pad;
-};
-
-struct CountParams {
-    const uint8_t* text;             // feed base
-    unsigned long long lo, hi;       // byte range of this pass inside the feed
-    unsigned long long n;            // feed length
-    const TileState* tiles;
-    unsigned int n_tiles;
-    int k;
-    int canonical;
-    int skip_n;
-    unsigned int* tab32;
-    unsigned long long* rec_len;     // indexed by (record id - rec_first), x2 for FASTQ
-    unsigned long long rec_first;    // record id of rec_len[0]
-    unsigned long long hdr_file_base;// FASTQ: records in earlier feeds of the same file (FASTA ids come from hdr_base)
-    Accum* acc;
 };
 
 __device__ __forceinline__ uint32_t revcomp32(uint32_t f, int k) {

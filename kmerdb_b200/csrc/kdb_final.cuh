@@ -1,4 +1,4 @@
-// Finalisation kernels: u32->u64 fold, per-record length checks, unique / nullomer reductions.
+// Finalisation kernels: u32->u64 fold, unique / nullomer reductions (record lengths are checked inside the tokeniser, kdb_encode2.cuh).
 // Replaces kmerdb/parse.py:139-146 (nullomer_array, unique_kmers, min/max read length) and the
 // record-length abort of kmerdb/kmer.py:461-463.
 #pragma once
@@ -57,35 +57,6 @@ __global__ void __launch_bounds__(256) k3_fold_final(unsigned int* __restrict__ 
     if (COUNT) {
         for (int d = 16; d; d >>= 1) nz += __shfl_xor_sync(0xffffffffu, nz, d);
         if ((threadIdx.x & 31) == 0 && nz) atomicAdd(&acc->unique, nz);
-    }
-}
-
-// Records [0, n_complete) of rec_len are closed: min / max length, short-record raise, and for
-// FASTQ the sequence/quality length agreement (Bio.SeqIO raises ValueError otherwise -> host).
-template <bool FASTQ>
-__global__ void __launch_bounds__(256) k4_check_records(const unsigned long long* __restrict__ rec_len, unsigned long long n_complete,
-                                                        unsigned long long rec_first, int k, Accum* acc) {
-    unsigned long long mn = ~0ull, mx = 0, err = ~0ull;
-    unsigned int layout = 0;
-    const unsigned long long stride = (unsigned long long)gridDim.x * blockDim.x;
-    for (unsigned long long i = (unsigned long long)blockIdx.x * blockDim.x + threadIdx.x; i < n_complete; i += stride) {
-        const unsigned long long len = FASTQ ? rec_len[2 * i] : rec_len[i];
-        if (FASTQ && rec_len[2 * i + 1] != len) layout = 1;
-        mn = len < mn ? len : mn;
-        mx = len > mx ? len : mx;
-        if (len < (unsigned long long)k) { const unsigned long long key = (rec_first + i) * 4 + P_SHORT; err = key < err ? key : err; }
-    }
-    for (int d = 16; d; d >>= 1) {
-        unsigned long long o = __shfl_xor_sync(0xffffffffu, mn, d); mn = o < mn ? o : mn;
-        o = __shfl_xor_sync(0xffffffffu, mx, d); mx = o > mx ? o : mx;
-        o = __shfl_xor_sync(0xffffffffu, err, d); err = o < err ? o : err;
-        layout |= __shfl_xor_sync(0xffffffffu, layout, d);
-    }
-    if ((threadIdx.x & 31) == 0) {
-        if (mn != ~0ull) atomicMin(&acc->min_len, mn);
-        if (mx) atomicMax(&acc->max_len, mx);
-        if (err != ~0ull) atomicMin(&acc->err_key, err);
-        if (layout) atomicOr(&acc->layout_flag, 1u);
     }
 }
 
