@@ -289,6 +289,9 @@ extern "C" kdb_ctx* kdb_create(int device, int k, int flags) {
         if ((e = cudaMalloc(&ctx->cursor, 2 * ctx->n_buckets * sizeof(unsigned int))) != cudaSuccess) return fail("cudaMalloc cursor", e);
     }
     if (!rc) rc = ctx->fastq ? occupancy_grid(k2s_encode<true>, kThreads, 0, &ctx->encode_grid) : occupancy_grid(k2s_encode<false>, kThreads, 0, &ctx->encode_grid);
+    // experiment knobs (scripts/concurrency_probe.py): CTAs per SM of the tokeniser / the partition, so that two contexts can share the SMs
+    if (const char* e1 = getenv("KDB_ENC_CTAS")) ctx->encode_grid = std::max(1, atoi(e1)) * 148;
+    if (const char* e2 = getenv("KDB_PART_CTAS")) ctx->part_grid = std::max(1, atoi(e2)) * 148;
     if (rc) { kdb_destroy(ctx); return nullptr; }
     if (reset_state(ctx)) { g_last_error = ctx->err; kdb_destroy(ctx); return nullptr; }
     if ((e = cudaGetLastError()) != cudaSuccess) return fail("kdb_create", e);
@@ -789,7 +792,9 @@ static int inflate_members(kdb_ctx* ctx, int device, const uint8_t* d_comp, cons
     static_assert(sizeof(kdb_bgzf_member_t) == sizeof(BgzfMember), "member layout");
     CK(cudaMemcpyAsync(d_members, members, n_members * sizeof(BgzfMember), cudaMemcpyHostToDevice, st));
     const int grid = (int)std::min<size_t>((n_members + kInfWarps - 1) / kInfWarps, (size_t)148 * 8);
-    k_inflate_bgzf<<<grid, kInfWarps * 32, 0, st>>>(d_comp, d_members, (unsigned int)n_members, d_out, d_status, check_crc);
+    static const bool one_by_one = getenv("KDB_INFLATE_V1") != nullptr;      // (A/B: the first, symbol-at-a-time kernel)
+    if (one_by_one) k_inflate_bgzf<false><<<grid, kInfWarps * 32, 0, st>>>(d_comp, d_members, (unsigned int)n_members, d_out, d_status, check_crc);
+    else k_inflate_bgzf<true><<<grid, kInfWarps * 32, 0, st>>>(d_comp, d_members, (unsigned int)n_members, d_out, d_status, check_crc);
     CK(cudaGetLastError());
     return KDB_OK;
 }
@@ -841,7 +846,7 @@ extern "C" int kdb_feed_bgzf_host(kdb_ctx* ctx, const uint8_t* raw, size_t n) {
     if (!wave_members) {
         int per_sm = 0, sms = 0;
         CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
-        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_inflate_bgzf, kInfWarps * 32, 0));
+        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_inflate_bgzf<true>, kInfWarps * 32, 0));
         wave_members = std::max(1, per_sm) * sms * kInfWarps;
     }
     const size_t piece_members = 2 * (size_t)wave_members;

@@ -155,6 +155,11 @@ __device__ __forceinline__ unsigned int gf2_times(const unsigned int* mat, unsig
 }
 
 // status per member: 0 ok, 1 malformed stream, 2 length mismatch, 3 CRC mismatch
+// BATCH: the symbols of a block are decoded 32 at a time into per-lane tokens (lane t keeps token t), their output positions come
+// from a warp scan, and the copies of a batch run together: literals one byte per lane, matches whose source lies before the
+// batch one per lane side by side (ONE L2 round trip per batch instead of one per match); a match that reads what the same batch
+// writes waits for its turn.  !BATCH: one symbol at a time, the warp copies each match together (r02 first version).
+template <bool BATCH>
 __global__ void __launch_bounds__(kInfWarps * 32) k_inflate_bgzf(const uint8_t* __restrict__ comp, const BgzfMember* __restrict__ members, unsigned int n_members,
                                                                  uint8_t* __restrict__ out, unsigned int* __restrict__ status, int check_crc) {
     __shared__ InfTables s_tab[kInfWarps];
@@ -245,6 +250,69 @@ __global__ void __launch_bounds__(kInfWarps * 32) k_inflate_bgzf(const uint8_t* 
                 if (!build_table(T.lens + 32 + nlen, ndist, T.dist_cnt, T.dist_sym, T.dist, kDistBits, 5, lane)) { err = 1; break; }
             }
             // ---- the symbols of the block ---------------------------------------------------------------------
+            if constexpr (BATCH) {
+                bool eob = false;
+                while (!eob && !err) {
+                    // phase 1: up to 32 tokens; every lane decodes, lane t keeps token t:  (length, distance or literal byte)
+                    unsigned int my_len = 0, my_d = 0, n_tok = 0;
+                    while (n_tok < 32) {
+                        br.refill();
+                        int sym = decode_sym(br, T.lit, kLitBits, 9, T.lit_cnt, T.lit_sym);
+                        if (sym < 0) { err = 1; break; }
+                        unsigned int tl = 1, td = 0x80000000u | (unsigned int)sym;         // literal: top bit set, the byte below
+                        if (sym >= 256) {
+                            if (sym == 256) { eob = true; break; }
+                            sym -= 257;
+                            if (sym >= 29) { err = 1; break; }
+                            tl = c_len_base[sym] + br.take(c_len_extra[sym]);
+                            br.refill();
+                            const int ds = decode_sym(br, T.dist, kDistBits, 5, T.dist_cnt, T.dist_sym);
+                            if (ds < 0 || ds >= 30) { err = 1; break; }
+                            td = c_dist_base[ds] + br.take(c_dist_extra[ds]);
+                        }
+                        if ((unsigned int)lane == n_tok) { my_len = tl; my_d = td; }
+                        n_tok++;
+                    }
+                    if (err) break;
+                    // phase 2: where every token's output goes
+                    unsigned int incl = my_len;
+#pragma unroll
+                    for (int dd = 1; dd < 32; dd <<= 1) { const unsigned int o = __shfl_up_sync(0xffffffffu, incl, dd); if (lane >= dd) incl += o; }
+                    const unsigned int total = __shfl_sync(0xffffffffu, incl, 31);
+                    const unsigned int my_pos = pos + incl - my_len;
+                    const bool is_match = my_len != 0 && !(my_d & 0x80000000u);
+                    if (pos + total > M.out_len) { err = 2; break; }
+                    if (__any_sync(0xffffffffu, is_match && my_d > my_pos)) { err = 1; break; }
+                    // phase 3: literals, and the matches that read only text written before this batch
+                    const unsigned int span = my_len < my_d ? my_len : my_d;                 // bytes of source a match really reads
+                    const bool indep = is_match && my_pos - my_d + span <= pos;
+                    if (my_len != 0 && !is_match) dst[my_pos] = (uint8_t)my_d;
+                    if (indep) {
+                        const uint8_t* from = dst + my_pos - my_d;
+                        for (unsigned int i = 0; i < my_len; i += 8) {
+                            uint8_t v[8];
+#pragma unroll
+                            for (int q = 0; q < 8; q++) { const unsigned int j = i + q; v[q] = j < my_len ? from[my_d >= my_len ? j : j % my_d] : (uint8_t)0; }
+#pragma unroll
+                            for (int q = 0; q < 8; q++) if (i + q < my_len) dst[my_pos + i + q] = v[q];
+                        }
+                    }
+                    __syncwarp();
+                    // the rest in token order: each may read what the one before wrote
+                    unsigned int dep = __ballot_sync(0xffffffffu, is_match && !indep);
+                    while (dep) {
+                        const int t = __ffs(dep) - 1;
+                        dep &= dep - 1;
+                        const unsigned int tl = __shfl_sync(0xffffffffu, my_len, t), td = __shfl_sync(0xffffffffu, my_d, t), tp = __shfl_sync(0xffffffffu, my_pos, t);
+                        const uint8_t* from = dst + tp - td;
+                        if (td >= tl) { for (unsigned int i = lane; i < tl; i += 32) dst[tp + i] = from[i]; }
+                        else { for (unsigned int i = lane; i < tl; i += 32) dst[tp + i] = from[i % td]; }
+                        __syncwarp();
+                    }
+                    pos += total;
+                }
+                continue;                                           // next block of the member
+            }
             while (true) {
                 br.refill();
                 int sym = decode_sym(br, T.lit, kLitBits, 9, T.lit_cnt, T.lit_sym);
