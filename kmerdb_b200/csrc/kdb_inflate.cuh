@@ -2,9 +2,11 @@
 // kmerdb/util.py:80-88).  BGZF (bgzip, Bio.bgzf) is a series of independent gzip members of at most 64 KiB of text each,
 // so the COMPRESSED bytes cross PCIe and every member is inflated by one warp straight into the text buffer the
 // tokeniser reads.  RFC 1951 restated for a warp:
-//   * all 32 lanes run the bit-stream decoder redundantly (same addresses: broadcast loads, no shuffles, no divergence);
-//   * literal: lane 0 stores the byte; match (length, distance): the lanes copy the bytes of the match in parallel
-//     (out[pos + i] = out[pos - d + i mod d] covers overlapping matches), a __syncwarp orders them for the next symbol;
+//   * all 32 lanes run the bit-stream decoder redundantly (no divergence); the compressed bytes arrive a 128-byte line at a time
+//     in registers (one word per lane) and a refill is a shuffle;
+//   * 32 symbols are decoded into per-lane tokens, a warp scan gives their output positions, then the literals (one byte per
+//     lane) and the matches whose source lies before the batch are copied side by side, the rest in token order
+//     (out[pos + i] = out[pos - d + i mod d] covers overlapping matches);
 //   * Huffman tables per warp in shared memory: a 10-bit (literal/length) and an 8-bit (distance) first-level table filled by
 //     the lanes together, longer codes by the canonical count/offset walk (RFC 1951 3.2.2);
 //   * stored and fixed-Huffman blocks included (bgzip's EOF marker is an empty fixed block).
