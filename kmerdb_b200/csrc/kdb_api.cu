@@ -24,6 +24,7 @@
 #include "kdb_corr.cuh"
 #include "kdb_multi.cuh"
 #include "kdb_inflate.cuh"
+#include "kdb_inflate2.cuh"
 
 using namespace kdb;
 
@@ -77,6 +78,8 @@ struct kdb_ctx {
     bool not_root = false;                      // after a reduce only the root holds the whole table
     uint8_t* comp_buf = nullptr;                // kdb_feed_bgzf_host: the compressed bytes, member table, status words
     size_t comp_cap = 0;
+    uint8_t* tok_buf = nullptr;                 // kdb_feed_bgzf_host: match tokens + token counts of one piece (kdb_inflate2.cuh)
+    size_t tok_cap = 0;
     void* null_scratch = nullptr;               // kdb_nullomers: per-block zero counts and offsets
     size_t null_cap = 0;
     // host mirrors
@@ -178,7 +181,7 @@ extern "C" void kdb_destroy(kdb_ctx* ctx) {
     cudaSetDevice(ctx->device);
     cudaFree(ctx->tab32); cudaFree(ctx->tab64); cudaFree(ctx->acc);
     cudaFree(ctx->feed_buf); cudaFree(ctx->packed); cudaFree(ctx->stream); cudaFree(ctx->cursor);
-    cudaFree(ctx->look); /* trec lives inside the look allocation */ cudaFree(ctx->ticket); cudaFree(ctx->pcarry); cudaFree(ctx->zero_row); cudaFree(ctx->null_scratch); cudaFree(ctx->d_pack); cudaFree(ctx->comp_buf);
+    cudaFree(ctx->look); /* trec lives inside the look allocation */ cudaFree(ctx->ticket); cudaFree(ctx->pcarry); cudaFree(ctx->zero_row); cudaFree(ctx->null_scratch); cudaFree(ctx->d_pack); cudaFree(ctx->comp_buf); cudaFree(ctx->tok_buf);
     if (ctx->comm && nccl_api().ok) nccl_api().CommDestroy(ctx->comm);
     if (ctx->ev_red0) cudaEventDestroy(ctx->ev_red0);
     if (ctx->ev_red1) cudaEventDestroy(ctx->ev_red1);
@@ -786,16 +789,51 @@ extern "C" int kdb_bgzf_index(const uint8_t* raw, size_t n, kdb_bgzf_member_t* m
 
 // comp / out: device buffers (comp readable 8 bytes past comp_len); members: host array.  Returns KDB_OK, or KDB_E_FORMAT
 // when a member does not inflate to its ISIZE / CRC-32 (first_bad receives its index).
+// Scratch of the two-kernel inflate for members[0, n): tokens (inflate_token_cap per member) followed by one token count per member.
+static size_t inflate_scratch_bytes(const kdb_bgzf_member_t* members, size_t n_members) {
+    size_t tok = 0;
+    for (size_t i = 0; i < n_members; i++) tok += inflate_token_cap(members[i].out_len);
+    return tok * 4 + n_members * 4 + 64;
+}
+
+// d_scratch: inflate_scratch_bytes(members, n_members) bytes (16-byte aligned).  KDB_INFLATE_WARP=1: the one-kernel path of r02
+// (one warp per member, every lane decoding) for A/B.
 static int inflate_members(kdb_ctx* ctx, int device, const uint8_t* d_comp, const kdb_bgzf_member_t* members, size_t n_members, uint8_t* d_out,
-                           BgzfMember* d_members, unsigned int* d_status, cudaStream_t st, int check_crc) {
+                           BgzfMember* d_members, unsigned int* d_status, uint8_t* d_scratch, cudaStream_t st, int check_crc) {
     if (int rc = load_crc_table(ctx, device)) return rc;
     static_assert(sizeof(kdb_bgzf_member_t) == sizeof(BgzfMember), "member layout");
-    CK(cudaMemcpyAsync(d_members, members, n_members * sizeof(BgzfMember), cudaMemcpyHostToDevice, st));
-    const int grid = (int)std::min<size_t>((n_members + kInfWarps - 1) / kInfWarps, (size_t)148 * 8);
-    static const bool one_by_one = getenv("KDB_INFLATE_V1") != nullptr;      // (A/B: the first, symbol-at-a-time kernel)
-    if (one_by_one) k_inflate_bgzf<false><<<grid, kInfWarps * 32, 0, st>>>(d_comp, d_members, (unsigned int)n_members, d_out, d_status, check_crc);
-    else k_inflate_bgzf<true><<<grid, kInfWarps * 32, 0, st>>>(d_comp, d_members, (unsigned int)n_members, d_out, d_status, check_crc);
+    static const bool warp_kernel = getenv("KDB_INFLATE_WARP") != nullptr;
+    if (warp_kernel) {
+        CK(cudaMemcpyAsync(d_members, members, n_members * sizeof(BgzfMember), cudaMemcpyHostToDevice, st));
+        const int grid = (int)std::min<size_t>((n_members + kInfWarps - 1) / kInfWarps, (size_t)148 * 8);
+        k_inflate_bgzf<true><<<grid, kInfWarps * 32, 0, st>>>(d_comp, d_members, (unsigned int)n_members, d_out, d_status, check_crc);
+        CK(cudaGetLastError());
+        if (ctx) ctx->timing.total_launches++;
+        return KDB_OK;
+    }
+    std::vector<BgzfMember> m(n_members);
+    memcpy(m.data(), members, n_members * sizeof(BgzfMember));
+    size_t quads = 0;
+    for (size_t i = 0; i < n_members; i++) {
+        if (quads > 0xFFFFFFFFull) { if (ctx) ctx->err = "BGZF input too large for one inflate call"; return KDB_E_ARG; }
+        m[i].pad = (unsigned int)quads;
+        quads += inflate_token_cap(m[i].out_len) / 4;
+    }
+    uint32_t* d_tok = reinterpret_cast<uint32_t*>(d_scratch);
+    unsigned int* d_ntok = reinterpret_cast<unsigned int*>(d_tok + 4 * quads);
+    CK(cudaMemcpyAsync(d_members, m.data(), n_members * sizeof(BgzfMember), cudaMemcpyHostToDevice, st));   // (pageable source: staged before the call returns)
+    static bool attr_set[64] = {false};
+    if (device >= 0 && device < 64 && !attr_set[device]) {
+        CK(cudaFuncSetAttribute(k_inflate_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDecSmemBytes));
+        attr_set[device] = true;
+    }
+    k_inflate_decode<<<(unsigned int)((n_members + kDecThreads - 1) / kDecThreads), kDecThreads, kDecSmemBytes, st>>>(d_comp, d_members, (unsigned int)n_members, d_out,
+                                                                                                                       d_tok, d_ntok, d_status);
     CK(cudaGetLastError());
+    k_inflate_resolve<<<(unsigned int)((n_members + kResWarps - 1) / kResWarps), kResWarps * 32, 0, st>>>(d_members, (unsigned int)n_members, d_tok, d_ntok, d_out, d_status,
+                                                                                                            check_crc);
+    CK(cudaGetLastError());
+    if (ctx) ctx->timing.total_launches += 2;
     return KDB_OK;
 }
 
@@ -810,10 +848,11 @@ extern "C" int kdb_inflate_bgzf(int device, const uint8_t* raw, size_t n, uint8_
     std::vector<kdb_bgzf_member_t> mem(nm);
     kdb_bgzf_index(raw, n, mem.data(), nm, &nm, &text);
     CK(cudaSetDevice(device));
-    DevBuf d_comp, d_out, d_mem, d_st;
+    DevBuf d_comp, d_out, d_mem, d_st, d_scr;
     CK(d_comp.alloc(n + kInflateSlack)); CK(d_out.alloc(text + 16)); CK(d_mem.alloc(nm * sizeof(BgzfMember))); CK(d_st.alloc(nm * sizeof(unsigned int)));
+    CK(d_scr.alloc(inflate_scratch_bytes(mem.data(), nm)));
     CK(cudaMemcpy(d_comp.p, raw, n, cudaMemcpyHostToDevice));
-    if (int rc = inflate_members(ctx, device, d_comp.as<uint8_t>(), mem.data(), nm, d_out.as<uint8_t>(), d_mem.as<BgzfMember>(), d_st.as<unsigned int>(), nullptr, 1)) return rc;
+    if (int rc = inflate_members(ctx, device, d_comp.as<uint8_t>(), mem.data(), nm, d_out.as<uint8_t>(), d_mem.as<BgzfMember>(), d_st.as<unsigned int>(), d_scr.as<uint8_t>(), nullptr, 1)) return rc;
     std::vector<unsigned int> status(nm);
     CK(cudaMemcpy(status.data(), d_st.p, nm * sizeof(unsigned int), cudaMemcpyDeviceToHost));
     for (size_t i = 0; i < nm; i++) if (status[i]) { char b[128]; snprintf(b, sizeof b, "BGZF member %zu does not inflate (code %u)", i, status[i]); g_last_error = b; return KDB_E_FORMAT; }
@@ -842,19 +881,31 @@ extern "C" int kdb_feed_bgzf_host(kdb_ctx* ctx, const uint8_t* raw, size_t n) {
     if (int rc = begin_feed(ctx)) return rc;
     // pieces of two waves of members (one warp inflates one member: a piece must hold enough members to fill the GPU — with 32 MiB pieces
     // a launch had 10 warps per SM and the seventeen launches of a 558 MB file took 143 ms, 8.4 ms each, the latency of ONE member)
-    static int wave_members = 0;                                  // members the GPU inflates at once: resident warps of k_inflate_bgzf
+    static int wave_members = 0;                                  // members the GPU inflates at once
+    static size_t piece_members = 0;
     if (!wave_members) {
         int per_sm = 0, sms = 0;
         CK(cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, ctx->device));
-        CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_inflate_bgzf<true>, kInfWarps * 32, 0));
-        wave_members = std::max(1, per_sm) * sms * kInfWarps;
+        if (getenv("KDB_INFLATE_WARP")) {                         // one warp per member: two waves of resident warps
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_inflate_bgzf<true>, kInfWarps * 32, 0));
+            wave_members = std::max(1, per_sm) * sms * kInfWarps;
+            piece_members = 2 * (size_t)wave_members;
+        } else {                                                  // one thread per member (k_inflate_decode): one wave of resident threads
+            CK(cudaFuncSetAttribute(k_inflate_decode, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)kDecSmemBytes));
+            CK(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, k_inflate_decode, kDecThreads, kDecSmemBytes));
+            wave_members = std::max(1, per_sm) * sms * kDecThreads;
+            piece_members = (size_t)wave_members;
+        }
+        if (const char* e = getenv("KDB_INFLATE_PIECE")) piece_members = (size_t)std::max(1, atoi(e));
     }
-    const size_t piece_members = 2 * (size_t)wave_members;
     std::vector<size_t> cut;                                      // member index where each piece starts
     for (size_t i = 0; i < nm; i += piece_members) cut.push_back(i);
     if (cut.size() > 1 && nm - cut.back() < piece_members / 4) cut.pop_back();     // (a short tail joins the piece before it)
     cut.push_back(nm);
     const size_t n_piece = cut.size() - 1;
+    size_t scratch = 0;                                           // pieces run one after the other on the compute stream: one scratch serves all
+    for (size_t pi = 0; pi < n_piece; pi++) scratch = std::max(scratch, inflate_scratch_bytes(mem.data() + cut[pi], cut[pi + 1] - cut[pi]));
+    if (int rc = ensure(ctx, (void**)&ctx->tok_buf, &ctx->tok_cap, scratch, 1)) return rc;
     while (ctx->ev_copy.size() < n_piece + 1) { cudaEvent_t e; CK(cudaEventCreate(&e)); ctx->ev_copy.push_back(e); }
     CK(cudaEventRecord(ctx->ev_copy[n_piece], ctx->s_copy));
     size_t byte0 = 0;
@@ -868,8 +919,7 @@ extern "C" int kdb_feed_bgzf_host(kdb_ctx* ctx, const uint8_t* raw, size_t n) {
     for (size_t pi = 0; pi < n_piece; pi++) {
         CK(cudaStreamWaitEvent(ctx->s_compute, ctx->ev_copy[pi], 0));
         if (int rc = inflate_members(ctx, ctx->device, d_comp, mem.data() + cut[pi], cut[pi + 1] - cut[pi], ctx->feed_buf, d_mem + cut[pi], d_st + cut[pi],
-                                     ctx->s_compute, 1)) return rc;
-        ctx->timing.total_launches++;
+                                     ctx->tok_buf, ctx->s_compute, 1)) return rc;
     }
     CK(cudaEventRecord(ctx->ev[1], ctx->s_compute));
     std::vector<unsigned int> status(nm);

@@ -1,0 +1,425 @@
+// GPU inflate of BGZF members in two kernels (reference: gzip.open at kmerdb/parse.py:63-68).
+//
+// The warp-per-member kernel of kdb_inflate.cuh runs ONE serial Huffman decode in all 32 lanes of a warp and is bound by
+// instruction issue (32-40 warps share four issue slots).  Here the two halves of DEFLATE are split by what they parallelise over:
+//   A  k_inflate_decode   one THREAD per member: the bit stream is decoded into match tokens; literals go straight to their final
+//                         place in the text (the decoder knows the output position).  32 different members per warp, no redundant
+//                         lanes: the kernel is bound by the latency of one decode chain, not by issue.  First-level tables
+//                         (9-bit literal/length, 6-bit distance: 1152 bytes per thread, six warps per SM) live in shared memory, interleaved so that thread t only ever
+//                         touches bank t (no bank conflicts whatever the indices); canonical order for longer codes, code lengths
+//                         and counts are thread-local.
+//   B  k_inflate_resolve  one WARP per member: 32 tokens at a time, output positions by a warp scan, matches that read text
+//                         before the batch are copied side by side (one per lane), the others in token order; then ISIZE / CRC-32
+//                         as before.
+// Token (u32): bit 31 clear: [30:23] literals before the match (0..255), [22:15] length - 3, [14:0] distance - 1;
+//              bit 31 set:   [23:0] literals only (a run longer than 255, stored blocks, the tail of the member).
+// A member of n text bytes yields at most n/3 + n/256 + 1 tokens.
+#pragma once
+#include "kdb_inflate.cuh"
+
+namespace kdb {
+
+constexpr int kDecThreads = 32;                       // members per CTA of kernel A
+constexpr int kDecLitBits = 9, kDecDistBits = 6;
+constexpr int kDecHalfWords = (1 << kDecLitBits) + (1 << kDecDistBits);      // u16 entries per thread
+constexpr size_t kDecSmemBytes = (size_t)kDecThreads * kDecHalfWords * 2;
+
+__host__ __device__ inline unsigned int inflate_token_cap(unsigned int out_len) { return (out_len / 3 + out_len / 256 + 8 + 3) & ~3u; }
+
+// Entry i of this thread's table: u16 pair (i >> 1) sits in word (i >> 1) * 32 + lane, i.e. always in bank `lane`.
+struct LaneTable {
+    unsigned short* base;                              // this lane's first half-word
+    __device__ __forceinline__ unsigned short& at(unsigned int i) const { return base[(i >> 1) * (2 * kDecThreads) + (i & 1u)]; }
+};
+
+// LSB-first bit reader of ONE thread.  The payload is fetched 16 bytes at a time and the NEXT 16 bytes are requested when the current
+// ones are taken into use (some four refills = eight symbols ahead): with 32 independent streams per warp some lane misses L1 at
+// nearly every step, and a load that is needed two symbols after it was issued would put an L2 round trip on every step.
+struct BitReader1 {
+    const uint4* p;
+    uint4 q, nq;                      // words being consumed (q.x next), the 16 bytes after them
+    int left;                         // words left in q
+    unsigned long long buf;
+    int cnt;
+    unsigned int bits_in;
+    __device__ __forceinline__ uint32_t pop() {
+        const uint32_t w = q.x;
+        q.x = q.y; q.y = q.z; q.z = q.w;
+        if (--left == 0) { q = nq; nq = __ldg(p++); left = 4; }
+        return w;
+    }
+    __device__ __forceinline__ void init(const uint8_t* a) {
+        const uintptr_t u = (uintptr_t)a;
+        p = reinterpret_cast<const uint4*>(u & ~(uintptr_t)15);
+        q = __ldg(p++);
+        nq = __ldg(p++);
+        left = 4;
+        for (unsigned int i = (unsigned int)(u & 15u) >> 2; i; i--) pop();
+        const unsigned int skip = (unsigned int)(u & 3u);
+        buf = (unsigned long long)(pop() >> (8 * skip));
+        cnt = 32 - 8 * (int)skip;
+        bits_in = (unsigned int)cnt;
+    }
+    __device__ __forceinline__ void refill() {          // at least 33 bits afterwards
+        if (cnt <= 32) { buf |= (unsigned long long)pop() << cnt; cnt += 32; bits_in += 32; }
+    }
+    __device__ __forceinline__ unsigned int peek(int n) const { return (unsigned int)buf & ((1u << n) - 1u); }
+    __device__ __forceinline__ void drop(int n) { buf >>= n; cnt -= n; }
+    __device__ __forceinline__ unsigned int take(int n) { const unsigned int v = peek(n); drop(n); return v; }
+    __device__ __forceinline__ unsigned int used() const { return bits_in - (unsigned int)cnt; }
+};
+
+// Canonical order + first-level table of n code lengths, by one thread (RFC 1951 3.2.2).  false: over-subscribed set.
+// lim[L] (L = 1..15) = (first code of length L + codes of length L) | (place of that first code in `sym` - first code) << 16:
+// what long_decode needs for the codes the first level does not hold.
+__device__ __noinline__ bool build_table1(const unsigned char* lens, int n, unsigned int* lim, unsigned short* sym, LaneTable tbl, unsigned int tbl_off,
+                                          int tbl_bits, int sym_shift) {
+    unsigned short cnt[16], offs[16];
+    for (int i = 0; i < 16; i++) cnt[i] = 0;
+    for (int i = 0; i < n; i++) cnt[lens[i]]++;
+    cnt[0] = 0;
+    int left = 1;
+    unsigned int first = 0;
+    offs[1] = 0;
+    for (int len = 1; len <= 15; len++) {
+        left <<= 1;
+        left -= cnt[len];
+        if (left < 0) return false;
+        if (len < 15) offs[len + 1] = offs[len] + cnt[len];
+        lim[len] = (first + cnt[len]) | (((unsigned int)offs[len] - first) << 16);
+        first = (first + cnt[len]) << 1;
+    }
+    for (int i = 0; i < n; i++) if (lens[i]) sym[offs[lens[i]]++] = (unsigned short)i;
+    for (unsigned int i = 0; i < (1u << tbl_bits); i++) tbl.at(tbl_off + i) = 0;
+    int code = 0, idx = 0;
+    for (int len = 1; len <= tbl_bits; len++) {
+        const int c = cnt[len];
+        for (int j = 0; j < c; j++) {
+            const unsigned int rev = __brev((unsigned int)(code + j)) >> (32 - len);
+            const unsigned short e = (unsigned short)(sym[idx + j] | (len << sym_shift));
+            for (unsigned int i = rev; i < (1u << tbl_bits); i += 1u << len) tbl.at(tbl_off + i) = e;
+        }
+        code = (code + c) << 1;
+        idx += c;
+    }
+    return true;
+}
+
+// A code longer than the first level (lengths L0 .. L0 + NL - 1): the next 15 bits, first bit on top, against the canonical limit
+// of every length in turn (no shorter code matches: the first level would have held it).  n_sym bounds the look-up for garbage.
+template <int L0, int NL>
+__device__ __forceinline__ int long_decode(BitReader1& br, const unsigned int (&lim)[NL], const unsigned short* sym, unsigned int n_sym) {
+    const unsigned int x = __brev((unsigned int)br.buf) >> 17;
+#pragma unroll
+    for (int i = 0; i < NL; i++) {
+        const int L = L0 + i;
+        const unsigned int c = x >> (15 - L);
+        if (c < (lim[i] & 0xFFFFu)) { br.drop(L); return sym[min((c + (lim[i] >> 16)) & 0xFFFFu, n_sym - 1u)]; }
+    }
+    return -1;
+}
+
+// ---- kernel A: one thread per member ----------------------------------------------------------------------------------------------
+// members[i].pad = first token of member i in `tokens`, in units of four tokens.  status: 0 ok, 1 malformed stream, 2 length mismatch.
+//
+// The lanes of a warp run in lock step (left to themselves they drift apart at the literal / match branch and the warp ends up
+// running one lane at a time: 301 ms instead of 39 for the same input).  A round = every unfinished lane reads one block header
+// and builds its tables, then all lanes decode side by side until the last of them has reached the end of its block.  One
+// iteration = ONE table look-up per lane: a literal / length symbol or, for the lane that has just read a length, the distance —
+// the same instructions on a different table, so a warp whose lanes are half in literals and half in matches does not run both
+// paths one after the other.  A code longer than the first level parks its lane; parked lanes are served together once eight of
+// them wait (the canonical walk and its thread-local symbol array would otherwise be on the path of nearly every iteration: with
+// 32 streams side by side "rare" happens all the time).
+__global__ void __launch_bounds__(kDecThreads) k_inflate_decode(const uint8_t* __restrict__ comp, const BgzfMember* __restrict__ members, unsigned int n_members,
+                                                                uint8_t* __restrict__ out, uint32_t* __restrict__ tokens, unsigned int* __restrict__ n_tokens,
+                                                                unsigned int* __restrict__ status) {
+    extern __shared__ __align__(16) unsigned short s_dec[];
+    __shared__ unsigned int s_base[64];                              // base | extra bits << 16 (RFC 1951 3.2.5): lengths at 0, distances at 32
+    if (threadIdx.x < 29) s_base[threadIdx.x] = c_len_base[threadIdx.x] | ((unsigned int)c_len_extra[threadIdx.x] << 16);
+    if (threadIdx.x < 30) s_base[32 + threadIdx.x] = c_dist_base[threadIdx.x] | ((unsigned int)c_dist_extra[threadIdx.x] << 16);
+    __syncthreads();
+    const unsigned int mi = blockIdx.x * kDecThreads + threadIdx.x;
+    const bool have = mi < n_members;
+    LaneTable T;
+    T.base = s_dec + 2 * threadIdx.x;
+    constexpr unsigned int kLitOff = 0, kDistOff = 1u << kDecLitBits;
+    constexpr int kShift = 9;                                        // every table entry: symbol | code length << 9
+    static_assert(kDecLitBits >= 7, "the code-length alphabet borrows the literal table");
+    unsigned char lens[320];
+    unsigned short lit_sym[288], dist_sym[32];
+    unsigned int lim16[16];                                          // build_table1's limits; the ones in use are copied to registers
+    unsigned int lit_lim[15 - kDecLitBits], dist_lim[15 - kDecDistBits];
+
+    BgzfMember M;
+    M.in_off = 0; M.out_off = 0; M.in_len = 0; M.out_len = 0; M.crc = 0; M.pad = 0;
+    if (have) M = members[mi];
+    uint8_t* const dst = out + M.out_off;
+    const uint8_t* const payload = comp + M.in_off;
+    uint4* tokp = reinterpret_cast<uint4*>(tokens) + M.pad;
+    uint32_t t0 = 0, t1 = 0, t2 = 0, t3 = 0;
+    unsigned int n_tok = 0;
+    auto emit = [&](uint32_t t) {
+        t0 = t1; t1 = t2; t2 = t3; t3 = t;
+        if ((++n_tok & 3u) == 0) *tokp++ = make_uint4(t0, t1, t2, t3);
+    };
+    BitReader1 br;
+    br.p = nullptr; br.q = br.nq = make_uint4(0, 0, 0, 0); br.left = 4; br.buf = 0; br.cnt = 0; br.bits_in = 0;
+    if (have) br.init(payload);
+    unsigned int pos = 0, err = 0, run = 0, mlen = 0;
+    bool done = !have;
+    while (__any_sync(0xffffffffu, !done)) {
+        bool in_block = false;
+        if (!done) {
+            bool last = false;
+            do {                                                    // one block header
+                if (br.used() > 8u * M.in_len) { err = 1; break; }   // (a run of empty blocks in garbage must not read on for ever)
+                br.refill();
+                last = br.take(1) != 0;
+                const unsigned int type = br.take(2);
+                if (type == 0) {                                    // stored: bytes copied as literals
+                    br.drop(br.cnt & 7);
+                    br.refill();
+                    const unsigned int len = br.take(16);
+                    br.refill();
+                    const unsigned int nlen = br.take(16);
+                    if ((len ^ 0xFFFFu) != nlen) { err = 1; break; }
+                    const unsigned int src = br.used() >> 3;
+                    if (src + len > M.in_len || pos + len > M.out_len) { err = 1; break; }
+                    for (unsigned int i = 0; i < len; i++) dst[pos + i] = payload[src + i];
+                    pos += len; run += len;
+                    br.init(payload + src + len);
+                    br.bits_in += 8u * (src + len);
+                    break;
+                }
+                if (type == 3) { err = 1; break; }
+                if (type == 1) {                                    // fixed codes (3.2.6)
+                    for (int i = 0; i < 288; i++) lens[i] = i < 144 ? 8 : (i < 256 ? 9 : (i < 280 ? 7 : 8));
+                    build_table1(lens, 288, lim16, lit_sym, T, kLitOff, kDecLitBits, kShift);
+#pragma unroll
+                    for (int i = 0; i < 15 - kDecLitBits; i++) lit_lim[i] = lim16[kDecLitBits + 1 + i];
+                    for (int i = 0; i < 30; i++) lens[i] = 5;
+                    build_table1(lens, 30, lim16, dist_sym, T, kDistOff, kDecDistBits, kShift);
+#pragma unroll
+                    for (int i = 0; i < 15 - kDecDistBits; i++) dist_lim[i] = lim16[kDecDistBits + 1 + i];
+                    in_block = true;
+                    break;
+                }
+                // dynamic codes (3.2.7)
+                const int nlen = (int)br.take(5) + 257, ndist = (int)br.take(5) + 1, ncode = (int)br.take(4) + 4;
+                if (nlen > 286 || ndist > 30) { err = 1; break; }
+                unsigned char cl[19];
+                for (int i = 0; i < 19; i++) cl[i] = 0;
+                for (int i = 0; i < ncode; i++) { br.refill(); cl[c_clen_order[i]] = (unsigned char)br.take(3); }
+                // the code-length alphabet (at most 7 bits: one level covers it) uses the literal table's place for now
+                if (!build_table1(cl, 19, lim16, dist_sym, T, kLitOff, 7, kShift)) { err = 1; break; }
+                int idx = 0;
+                while (idx < nlen + ndist) {
+                    br.refill();
+                    const unsigned int ce = T.at(kLitOff + br.peek(7));
+                    if (ce == 0) { err = 1; break; }
+                    br.drop((int)(ce >> kShift));
+                    const int sym = (int)(ce & 31u);
+                    if (sym < 16) { lens[idx++] = (unsigned char)sym; continue; }
+                    int rep, val = 0;
+                    if (sym == 16) {
+                        if (idx == 0) { err = 1; break; }
+                        val = lens[idx - 1];
+                        rep = 3 + (int)br.take(2);
+                    } else if (sym == 17) rep = 3 + (int)br.take(3);
+                    else rep = 11 + (int)br.take(7);
+                    if (idx + rep > nlen + ndist) { err = 1; break; }
+                    for (int i = 0; i < rep; i++) lens[idx + i] = (unsigned char)val;
+                    idx += rep;
+                }
+                if (err) break;
+                if (lens[256] == 0) { err = 1; break; }             // no end-of-block code
+                if (!build_table1(lens, nlen, lim16, lit_sym, T, kLitOff, kDecLitBits, kShift)) { err = 1; break; }
+#pragma unroll
+                for (int i = 0; i < 15 - kDecLitBits; i++) lit_lim[i] = lim16[kDecLitBits + 1 + i];
+                if (!build_table1(lens + nlen, ndist, lim16, dist_sym, T, kDistOff, kDecDistBits, kShift)) { err = 1; break; }
+#pragma unroll
+                for (int i = 0; i < 15 - kDecDistBits; i++) dist_lim[i] = lim16[kDecDistBits + 1 + i];
+                in_block = true;
+            } while (false);
+            if (err) in_block = false;
+            if (err || last) done = true;                           // (`done` only stops the next round: the symbols of a last block follow)
+        }
+        __syncwarp();
+        // ---- the symbols of the block ----
+        bool dist_next = false, parked = false;                     // the next look-up is a distance; waiting for the long-code pass
+        // what follows a decoded symbol: a literal, the end of the block, or a base + extra bits (length -> the next look-up is its
+        // distance; distance -> the match is complete)
+        auto symbol = [&](int sym) {
+            if (!dist_next && sym < 256) {
+                if (pos >= M.out_len) { err = 2; in_block = false; }
+                else { dst[pos++] = (uint8_t)sym; run++; }
+                return;
+            }
+            if (!dist_next && sym == 256) { in_block = false; return; }
+            const unsigned int bi = dist_next ? 32u + (unsigned int)sym : (unsigned int)sym - 257u;
+            if (bi >= (dist_next ? 62u : 29u)) { err = 1; in_block = false; return; }
+            const unsigned int be = s_base[bi];
+            const unsigned int v = (be & 0xFFFFu) + br.take((int)(be >> 16));
+            if (!dist_next) { mlen = v; dist_next = true; return; }
+            dist_next = false;
+            if (v > pos) { err = 1; in_block = false; }
+            else if (pos + mlen > M.out_len) { err = 2; in_block = false; }
+            else {
+                if (run > 255u) { emit(0x80000000u | run); run = 0; }
+                emit((run << 23) | ((mlen - 3u) << 15) | (v - 1u));
+                run = 0;
+                pos += mlen;
+            }
+        };
+        while (__any_sync(0xffffffffu, in_block)) {
+            if (in_block && !parked) {
+                br.refill();
+                const unsigned int e = T.at(dist_next ? kDistOff + br.peek(kDecDistBits) : kLitOff + br.peek(kDecLitBits));
+                if (e == 0) parked = true;
+                else { br.drop((int)(e >> kShift)); symbol((int)(e & ((1u << kShift) - 1u))); }
+            }
+            const unsigned int pb = __ballot_sync(0xffffffffu, parked);
+            if (pb && (__popc(pb) >= 8 || !__any_sync(0xffffffffu, in_block && !parked))) {
+                if (parked) {
+                    parked = false;
+                    const int sym = dist_next ? long_decode<kDecDistBits + 1, 15 - kDecDistBits>(br, dist_lim, dist_sym, 32u)
+                                              : long_decode<kDecLitBits + 1, 15 - kDecLitBits>(br, lit_lim, lit_sym, 288u);
+                    if (sym < 0) { err = 1; in_block = false; }
+                    else symbol(sym);
+                }
+            }
+        }
+        if (err) done = true;
+    }
+    if (!have) return;
+    if (!err && br.used() > 8u * M.in_len) err = 1;               // ran past the end of the payload
+    if (!err && pos != M.out_len) err = 2;
+    if (run) emit(0x80000000u | run);
+    {   // the tokens still in registers: the last n_tok & 3 of them
+        uint32_t* tail = reinterpret_cast<uint32_t*>(tokp);
+        const unsigned int r = n_tok & 3u;
+        if (r == 1) tail[0] = t3;
+        else if (r == 2) { tail[0] = t2; tail[1] = t3; }
+        else if (r == 3) { tail[0] = t1; tail[1] = t2; tail[2] = t3; }
+    }
+    n_tokens[mi] = n_tok;
+    status[mi] = err;
+}
+
+// CRC-32 of dst[0, n) by one warp: every lane walks one chunk (word loads, four table steps per word), the partial values are
+// joined front to back with crc(A || B) = shift(crc(A), |B|) ^ crc(B) (zlib crc32_combine; `even` / `odd` = two 32-row operators).
+__device__ __forceinline__ unsigned int warp_crc32(const uint8_t* dst, unsigned int n, int lane, unsigned int* even, unsigned int* odd, const unsigned int* s_crc) {
+    const unsigned int per = (n + 31) / 32;
+    const unsigned int b0 = min(n, lane * per), b1 = min(n, b0 + per);
+    unsigned int c = 0xFFFFFFFFu;
+    {
+        unsigned int i = b0;
+        for (; i < b1 && ((uintptr_t)(dst + i) & 3u); i++) c = s_crc[(c ^ dst[i]) & 0xFFu] ^ (c >> 8);
+        for (; i + 4 <= b1; i += 4) {
+            c ^= *reinterpret_cast<const uint32_t*>(dst + i);
+            c = s_crc[c & 0xFFu] ^ (c >> 8); c = s_crc[c & 0xFFu] ^ (c >> 8);
+            c = s_crc[c & 0xFFu] ^ (c >> 8); c = s_crc[c & 0xFFu] ^ (c >> 8);
+        }
+        for (; i < b1; i++) c = s_crc[(c ^ dst[i]) & 0xFFu] ^ (c >> 8);
+    }
+    c ^= 0xFFFFFFFFu;
+    odd[lane] = lane == 0 ? 0xEDB88320u : (1u << (lane - 1));                       // operator for 1 zero bit
+    __syncwarp();
+    even[lane] = gf2_times(odd, odd[lane]); __syncwarp();                           // 2 bits
+    odd[lane] = gf2_times(even, even[lane]); __syncwarp();                          // 4 bits
+    unsigned int total = 0;
+    for (int L = 0; L < 32; L++) {
+        const unsigned int cl = __shfl_sync(0xffffffffu, c, L);
+        const unsigned int lb0 = min(n, L * per), lb1 = min(n, lb0 + per);
+        const unsigned int len2 = lb1 - lb0;
+        if (len2 == 0) continue;
+        if (L == 0) { total = cl; continue; }
+        unsigned int v = total, nb = len2;
+        const unsigned int four_bits = odd[lane];
+        unsigned int* A = even;
+        unsigned int* B = odd;
+        __syncwarp();
+        do {                                                     // square (first round: one byte), apply when the bit of len2 is set
+            A[lane] = gf2_times(B, B[lane]);
+            __syncwarp();
+            if (nb & 1u) v = gf2_times(A, v);
+            nb >>= 1;
+            unsigned int* t = A; A = B; B = t;
+            __syncwarp();
+        } while (nb);
+        total = v ^ cl;
+        odd[lane] = four_bits;
+        __syncwarp();
+    }
+    return total;
+}
+
+// ---- kernel B: one warp per member ------------------------------------------------------------------------------------------------
+// status (from kernel A) stays unless the CRC fails (3).
+constexpr int kResWarps = 8;
+__global__ void __launch_bounds__(kResWarps * 32) k_inflate_resolve(const BgzfMember* __restrict__ members, unsigned int n_members, const uint32_t* __restrict__ tokens,
+                                                                   const unsigned int* __restrict__ n_tokens, uint8_t* __restrict__ out,
+                                                                   unsigned int* __restrict__ status, int check_crc) {
+    __shared__ unsigned int s_mat[kResWarps][2][32];
+    __shared__ unsigned int s_crc[256];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int i = threadIdx.x; i < 256; i += blockDim.x) s_crc[i] = c_crc_table[i];
+    __syncthreads();
+    const unsigned int mi = blockIdx.x * kResWarps + warp;
+    if (mi >= n_members) return;
+    if (status[mi]) return;
+    const BgzfMember M = members[mi];
+    uint8_t* const dst = out + M.out_off;
+    const uint32_t* const tok = tokens + 4ull * M.pad;
+    const unsigned int n = n_tokens[mi];
+    unsigned int pos = 0;
+    uint32_t t_next = lane < (int)n ? __ldg(tok + lane) : 0x80000000u;
+    for (unsigned int base = 0; base < n; base += 32) {
+        const uint32_t t = t_next;
+        t_next = base + 32 + lane < n ? __ldg(tok + base + 32 + lane) : 0x80000000u;
+        const bool filler = (t & 0x80000000u) != 0;
+        const unsigned int lit = filler ? (t & 0xFFFFFFu) : (t >> 23);
+        const unsigned int my_len = filler ? 0u : ((t >> 15) & 255u) + 3u;
+        const unsigned int my_d = (t & 0x7FFFu) + 1u;
+        unsigned int incl = lit + my_len;
+#pragma unroll
+        for (int dd = 1; dd < 32; dd <<= 1) { const unsigned int o = __shfl_up_sync(0xffffffffu, incl, dd); if (lane >= dd) incl += o; }
+        const unsigned int total = __shfl_sync(0xffffffffu, incl, 31);
+        const unsigned int my_pos = pos + incl - my_len;                          // where my match starts
+        // matches that read only text in place before this batch (kernel A's literals are all in place; what a batch can lack is the
+        // output of its own matches, so anything that ends at or before the batch start is safe)
+        const unsigned int span = my_len < my_d ? my_len : my_d;
+        const bool indep = my_len != 0 && my_pos - my_d + span <= pos;
+        if (indep) {
+            const uint8_t* from = dst + my_pos - my_d;
+            uint8_t* to = dst + my_pos;
+            if (my_d >= my_len) {
+                for (unsigned int i = 0; i < my_len; i += 8) {
+                    uint8_t v[8];
+#pragma unroll
+                    for (int q = 0; q < 8; q++) v[q] = i + q < my_len ? from[i + q] : (uint8_t)0;
+#pragma unroll
+                    for (int q = 0; q < 8; q++) if (i + q < my_len) to[i + q] = v[q];
+                }
+            } else {
+                for (unsigned int i = 0; i < my_len; i++) to[i] = from[i];        // period my_d: reads what this thread has just written
+            }
+        }
+        __syncwarp();
+        unsigned int dep = __ballot_sync(0xffffffffu, my_len != 0 && !indep);
+        while (dep) {                                                            // in token order: each may read what the one before wrote
+            const int w = __ffs(dep) - 1;
+            dep &= dep - 1;
+            const unsigned int tl = __shfl_sync(0xffffffffu, my_len, w), td = __shfl_sync(0xffffffffu, my_d, w), tp = __shfl_sync(0xffffffffu, my_pos, w);
+            const uint8_t* from = dst + tp - td;
+            if (td >= tl) { for (unsigned int i = lane; i < tl; i += 32) dst[tp + i] = from[i]; }
+            else { for (unsigned int i = lane; i < tl; i += 32) dst[tp + i] = from[i % td]; }
+            __syncwarp();
+        }
+        pos += total;
+    }
+    __syncwarp();
+    if (check_crc && warp_crc32(dst, M.out_len, lane, s_mat[warp][0], s_mat[warp][1], s_crc) != M.crc && lane == 0) status[mi] = 3;
+}
+
+}  // namespace kdb

@@ -60,6 +60,27 @@ def test_every_block_type_and_match_shape():
     assert bytes(got) == b"".join(want) == gzip.decompress(blob)
 
 
+def test_members_of_several_blocks():
+    """Members whose deflate stream holds several blocks (dynamic, fixed, empty stored blocks of a sync flush, stored data):
+    threads of one warp then stand in different blocks of different members."""
+    rng = np.random.default_rng(5)
+    members, want = [], []
+    for mi in range(70):
+        parts = [bytes(rng.choice(np.frombuffer(b"ACGTN\n>", dtype=np.uint8), size=int(rng.integers(1, 9000)))) for _ in range(int(rng.integers(1, 6)))]
+        c = zlib.compressobj(int(rng.integers(0, 10)), zlib.DEFLATED, -15)
+        comp = b""
+        for part in parts:
+            comp += c.compress(part) + c.flush([zlib.Z_SYNC_FLUSH, zlib.Z_FULL_FLUSH, zlib.Z_NO_FLUSH][int(rng.integers(0, 3))])
+        comp += c.flush()
+        data = b"".join(parts)
+        head = b"\x1f\x8b\x08\x04\x00\x00\x00\x00\x00\xff" + struct.pack("<H", 6) + b"BC\x02\x00" + struct.pack("<H", len(comp) + 12 + 6 + 8 - 1)
+        members.append(head + comp + struct.pack("<II", zlib.crc32(data) & 0xFFFFFFFF, len(data)))
+        want.append(data)
+    blob = b"".join(members) + kdbfile._BGZF_EOF
+    assert gzip.decompress(blob) == b"".join(want)
+    assert bytes(_native.inflate_bgzf(blob)) == b"".join(want)
+
+
 @pytest.mark.parametrize("name", ["Cacetobutylicum_ATCC824.fasta.gz", "Cdifficile_R3.fasta.gz", "sample.fa"])
 def test_bundled_genomes_reblocked_as_bgzf(name, tmp_path):
     path = os.path.join(DATA, name)
