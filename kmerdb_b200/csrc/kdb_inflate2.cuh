@@ -19,41 +19,54 @@
 
 namespace kdb {
 
-constexpr int kDecThreads = 32;                       // members per CTA of kernel A
+constexpr int kDecThreads = 64;                       // members per CTA of kernel A (two warps: three CTAs = six warps per SM)
 constexpr int kDecLitBits = 9, kDecDistBits = 6;
 constexpr int kDecHalfWords = (1 << kDecLitBits) + (1 << kDecDistBits);      // u16 entries per thread
-constexpr size_t kDecSmemBytes = (size_t)kDecThreads * kDecHalfWords * 2;
+constexpr size_t kDecSmemBytes = (size_t)kDecThreads * kDecHalfWords * 2 + (size_t)kDecThreads * 32;     // tables + the bit readers' rings
 
 __host__ __device__ inline unsigned int inflate_token_cap(unsigned int out_len) { return (out_len / 3 + out_len / 256 + 8 + 3) & ~3u; }
 
 // Entry i of this thread's table: u16 pair (i >> 1) sits in word (i >> 1) * 32 + lane, i.e. always in bank `lane`.
 struct LaneTable {
     unsigned short* base;                              // this lane's first half-word
-    __device__ __forceinline__ unsigned short& at(unsigned int i) const { return base[(i >> 1) * (2 * kDecThreads) + (i & 1u)]; }
+    __device__ __forceinline__ unsigned short& at(unsigned int i) const { return base[(i >> 1) * (2 * kDecThreads) + (i & 1u)]; }   // (64 threads: bank = lane)
 };
 
-// LSB-first bit reader of ONE thread.  The payload is fetched 16 bytes at a time and the NEXT 16 bytes are requested when the current
-// ones are taken into use (some four refills = eight symbols ahead): with 32 independent streams per warp some lane misses L1 at
-// nearly every step, and a load that is needed two symbols after it was issued would put an L2 round trip on every step.
+// LSB-first bit reader of ONE thread.  The payload is staged through a ring of two 16-byte chunks per thread in shared memory,
+// filled by cp.async: when a chunk has been used up, the 16 bytes that follow the other chunk are requested into it, so a
+// request has a whole chunk's worth of symbols (some eight iterations) to arrive and NO register waits for it.  (A register
+// read-ahead does not work here: the warp stalls on the pending register at the first instruction that names it, even a
+// predicated-off move — 29 % of the samples of that version sat on one `@!P MOV`.)
 struct BitReader1 {
-    const uint4* p;
-    uint4 q, nq;                      // words being consumed (q.x next), the 16 bytes after them
-    int left;                         // words left in q
+    const uint8_t* gp;                // next 16 bytes to request
+    uint32_t ring;                    // shared-memory address of this thread's chunk 0; chunk 1 lies kRingStride further
+    uint32_t rd;                      // next word of the ring (0..7)
     unsigned long long buf;
     int cnt;
     unsigned int bits_in;
+    static constexpr uint32_t kRingStride = kDecThreads * 16;
+    __device__ __forceinline__ uint32_t word_addr(uint32_t w) const { return ring + (w >> 2) * kRingStride + (w & 3u) * 4u; }
+    __device__ __forceinline__ void fetch(uint32_t chunk) {
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\ncp.async.commit_group;" ::"r"(ring + chunk * kRingStride), "l"(gp) : "memory");
+        gp += 16;
+    }
     __device__ __forceinline__ uint32_t pop() {
-        const uint32_t w = q.x;
-        q.x = q.y; q.y = q.z; q.z = q.w;
-        if (--left == 0) { q = nq; nq = __ldg(p++); left = 4; }
+        uint32_t w;
+        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(word_addr(rd)) : "memory");
+        rd = (rd + 1u) & 7u;
+        if ((rd & 3u) == 0) {                                       // a chunk is used up: refill it, and the other one must have arrived
+            fetch((rd >> 2) ^ 1u);
+            asm volatile("cp.async.wait_group 1;" ::: "memory");
+        }
         return w;
     }
     __device__ __forceinline__ void init(const uint8_t* a) {
         const uintptr_t u = (uintptr_t)a;
-        p = reinterpret_cast<const uint4*>(u & ~(uintptr_t)15);
-        q = __ldg(p++);
-        nq = __ldg(p++);
-        left = 4;
+        gp = reinterpret_cast<const uint8_t*>(u & ~(uintptr_t)15);
+        asm volatile("cp.async.wait_group 0;" ::: "memory");       // (a re-start after a stored block: nothing of the old position in flight)
+        fetch(0); fetch(1);
+        asm volatile("cp.async.wait_group 1;" ::: "memory");
+        rd = 0;
         for (unsigned int i = (unsigned int)(u & 15u) >> 2; i; i--) pop();
         const unsigned int skip = (unsigned int)(u & 3u);
         buf = (unsigned long long)(pop() >> (8 * skip));
@@ -155,15 +168,11 @@ __global__ void __launch_bounds__(kDecThreads) k_inflate_decode(const uint8_t* _
     if (have) M = members[mi];
     uint8_t* const dst = out + M.out_off;
     const uint8_t* const payload = comp + M.in_off;
-    uint4* tokp = reinterpret_cast<uint4*>(tokens) + M.pad;
-    uint32_t t0 = 0, t1 = 0, t2 = 0, t3 = 0;
-    unsigned int n_tok = 0;
-    auto emit = [&](uint32_t t) {
-        t0 = t1; t1 = t2; t2 = t3; t3 = t;
-        if ((++n_tok & 3u) == 0) *tokp++ = make_uint4(t0, t1, t2, t3);
-    };
+    uint32_t* const tok0 = tokens + 4ull * M.pad;
+    uint32_t* tokp = tok0;
     BitReader1 br;
-    br.p = nullptr; br.q = br.nq = make_uint4(0, 0, 0, 0); br.left = 4; br.buf = 0; br.cnt = 0; br.bits_in = 0;
+    br.ring = (uint32_t)__cvta_generic_to_shared(s_dec + (size_t)kDecThreads * kDecHalfWords) + threadIdx.x * 16u;
+    br.gp = comp; br.rd = 0; br.buf = 0; br.cnt = 0; br.bits_in = 0;
     if (have) br.init(payload);
     unsigned int pos = 0, err = 0, run = 0, mlen = 0;
     bool done = !have;
@@ -249,68 +258,66 @@ __global__ void __launch_bounds__(kDecThreads) k_inflate_decode(const uint8_t* _
         bool dist_next = false, parked = false;                     // the next look-up is a distance; waiting for the long-code pass
         // what follows a decoded symbol: a literal, the end of the block, or a base + extra bits (length -> the next look-up is its
         // distance; distance -> the match is complete)
-        auto symbol = [&](int sym) {
-            if (!dist_next && sym < 256) {
+        auto symbol = [&](unsigned int sym) {
+            const bool lit = !dist_next && sym < 256u;
+            if (lit) {
                 if (pos >= M.out_len) { err = 2; in_block = false; }
                 else { dst[pos++] = (uint8_t)sym; run++; }
                 return;
             }
-            if (!dist_next && sym == 256) { in_block = false; return; }
-            const unsigned int bi = dist_next ? 32u + (unsigned int)sym : (unsigned int)sym - 257u;
+            if (!dist_next && sym == 256u) { in_block = false; return; }
+            const unsigned int bi = dist_next ? 32u + sym : sym - 257u;
             if (bi >= (dist_next ? 62u : 29u)) { err = 1; in_block = false; return; }
             const unsigned int be = s_base[bi];
             const unsigned int v = (be & 0xFFFFu) + br.take((int)(be >> 16));
             if (!dist_next) { mlen = v; dist_next = true; return; }
             dist_next = false;
-            if (v > pos) { err = 1; in_block = false; }
-            else if (pos + mlen > M.out_len) { err = 2; in_block = false; }
-            else {
-                if (run > 255u) { emit(0x80000000u | run); run = 0; }
-                emit((run << 23) | ((mlen - 3u) << 15) | (v - 1u));
-                run = 0;
-                pos += mlen;
-            }
+            if (v > pos || pos + mlen > M.out_len) { err = v > pos ? 1u : 2u; in_block = false; return; }
+            if (run > 255u) { *tokp++ = 0x80000000u | run; run = 0; }
+            *tokp++ = (run << 23) | ((mlen - 3u) << 15) | (v - 1u);
+            run = 0;
+            pos += mlen;
         };
-        while (__any_sync(0xffffffffu, in_block)) {
+        unsigned int ib = __ballot_sync(0xffffffffu, in_block);
+        while (ib) {
             if (in_block && !parked) {
                 br.refill();
                 const unsigned int e = T.at(dist_next ? kDistOff + br.peek(kDecDistBits) : kLitOff + br.peek(kDecLitBits));
                 if (e == 0) parked = true;
-                else { br.drop((int)(e >> kShift)); symbol((int)(e & ((1u << kShift) - 1u))); }
+                else { br.drop((int)(e >> kShift)); symbol(e & ((1u << kShift) - 1u)); }
             }
-            const unsigned int pb = __ballot_sync(0xffffffffu, parked);
-            if (pb && (__popc(pb) >= 8 || !__any_sync(0xffffffffu, in_block && !parked))) {
-                if (parked) {
+            ib = __ballot_sync(0xffffffffu, in_block);
+            const unsigned int pb = __ballot_sync(0xffffffffu, in_block && parked);
+            if (pb && (__popc(pb) >= 8 || pb == ib)) {              // long codes: eight lanes wait, or nobody else can go on
+                if (in_block && parked) {
                     parked = false;
                     const int sym = dist_next ? long_decode<kDecDistBits + 1, 15 - kDecDistBits>(br, dist_lim, dist_sym, 32u)
                                               : long_decode<kDecLitBits + 1, 15 - kDecLitBits>(br, lit_lim, lit_sym, 288u);
                     if (sym < 0) { err = 1; in_block = false; }
-                    else symbol(sym);
+                    else symbol((unsigned int)sym);
                 }
+                ib = __ballot_sync(0xffffffffu, in_block);
             }
         }
         if (err) done = true;
     }
+    asm volatile("cp.async.wait_group 0;" ::: "memory");
     if (!have) return;
     if (!err && br.used() > 8u * M.in_len) err = 1;               // ran past the end of the payload
     if (!err && pos != M.out_len) err = 2;
-    if (run) emit(0x80000000u | run);
-    {   // the tokens still in registers: the last n_tok & 3 of them
-        uint32_t* tail = reinterpret_cast<uint32_t*>(tokp);
-        const unsigned int r = n_tok & 3u;
-        if (r == 1) tail[0] = t3;
-        else if (r == 2) { tail[0] = t2; tail[1] = t3; }
-        else if (r == 3) { tail[0] = t1; tail[1] = t2; tail[2] = t3; }
-    }
-    n_tokens[mi] = n_tok;
+    if (run) *tokp++ = 0x80000000u | run;
+    n_tokens[mi] = (unsigned int)(tokp - tok0);
     status[mi] = err;
 }
 
-// CRC-32 of dst[0, n) by one warp: every lane walks one chunk (word loads, four table steps per word), the partial values are
-// joined front to back with crc(A || B) = shift(crc(A), |B|) ^ crc(B) (zlib crc32_combine; `even` / `odd` = two 32-row operators).
-__device__ __forceinline__ unsigned int warp_crc32(const uint8_t* dst, unsigned int n, int lane, unsigned int* even, unsigned int* odd, const unsigned int* s_crc) {
-    const unsigned int per = (n + 31) / 32;
-    const unsigned int b0 = min(n, lane * per), b1 = min(n, b0 + per);
+// CRC-32 of dst[0, n) by one warp: lane 0 walks the first n - 31 * per bytes, every other lane `per` = n / 32 bytes (word loads, four
+// table steps per word); the partial values are joined front to back with crc(A || B) = shift(crc(A), |B|) ^ crc(B) (zlib
+// crc32_combine).  All 31 joins shift by the same `per` bytes, so the GF(2) operator of that shift is built ONCE (square-and-
+// multiply from the one-byte operator, every lane owning one column) and applied 31 times.  (The r02 kernel rebuilt the chain of
+// squares for every join: two thirds of the instructions of the whole resolve kernel.)   P, Mx: two 32-word operators of this warp.
+__device__ __forceinline__ unsigned int warp_crc32(const uint8_t* dst, unsigned int n, int lane, unsigned int* P, unsigned int* Mx, const unsigned int* s_crc) {
+    const unsigned int per = n / 32, head = n - 31 * per;
+    const unsigned int b0 = lane == 0 ? 0u : head + (lane - 1) * per, b1 = lane == 0 ? head : b0 + per;
     unsigned int c = 0xFFFFFFFFu;
     {
         unsigned int i = b0;
@@ -323,34 +330,18 @@ __device__ __forceinline__ unsigned int warp_crc32(const uint8_t* dst, unsigned 
         for (; i < b1; i++) c = s_crc[(c ^ dst[i]) & 0xFFu] ^ (c >> 8);
     }
     c ^= 0xFFFFFFFFu;
-    odd[lane] = lane == 0 ? 0xEDB88320u : (1u << (lane - 1));                       // operator for 1 zero bit
+    // P = operator for one zero bit, squared three times = one byte; Mx = identity
+    P[lane] = lane == 0 ? 0xEDB88320u : (1u << (lane - 1));
+    Mx[lane] = 1u << lane;
     __syncwarp();
-    even[lane] = gf2_times(odd, odd[lane]); __syncwarp();                           // 2 bits
-    odd[lane] = gf2_times(even, even[lane]); __syncwarp();                          // 4 bits
-    unsigned int total = 0;
-    for (int L = 0; L < 32; L++) {
-        const unsigned int cl = __shfl_sync(0xffffffffu, c, L);
-        const unsigned int lb0 = min(n, L * per), lb1 = min(n, lb0 + per);
-        const unsigned int len2 = lb1 - lb0;
-        if (len2 == 0) continue;
-        if (L == 0) { total = cl; continue; }
-        unsigned int v = total, nb = len2;
-        const unsigned int four_bits = odd[lane];
-        unsigned int* A = even;
-        unsigned int* B = odd;
-        __syncwarp();
-        do {                                                     // square (first round: one byte), apply when the bit of len2 is set
-            A[lane] = gf2_times(B, B[lane]);
-            __syncwarp();
-            if (nb & 1u) v = gf2_times(A, v);
-            nb >>= 1;
-            unsigned int* t = A; A = B; B = t;
-            __syncwarp();
-        } while (nb);
-        total = v ^ cl;
-        odd[lane] = four_bits;
-        __syncwarp();
+    for (int r = 0; r < 3; r++) { const unsigned int t = gf2_times(P, P[lane]); __syncwarp(); P[lane] = t; __syncwarp(); }
+    for (unsigned int nb = per; nb; ) {                          // Mx = product of the squares of P picked by the bits of `per`
+        if (nb & 1u) { const unsigned int t = gf2_times(P, Mx[lane]); __syncwarp(); Mx[lane] = t; __syncwarp(); }
+        nb >>= 1;
+        if (nb) { const unsigned int t = gf2_times(P, P[lane]); __syncwarp(); P[lane] = t; __syncwarp(); }
     }
+    unsigned int total = __shfl_sync(0xffffffffu, c, 0);
+    for (int L = 1; L < 32; L++) total = gf2_times(Mx, total) ^ __shfl_sync(0xffffffffu, c, L);
     return total;
 }
 
