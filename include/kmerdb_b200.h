@@ -117,6 +117,15 @@ int kdb_stats(kdb_ctx* ctx, kdb_stats_t* out);
 int kdb_counts(kdb_ctx* ctx, uint64_t* out);
 /* ascending ids with zero count (parse.py:139-140).  *n receives the total; at most cap are written. */
 int kdb_nullomers(kdb_ctx* ctx, uint64_t* out_ids, size_t cap, size_t* n);
+/* No counterpart in the reference.  kdb_nullomers for callers that cannot call
+ * cudaMalloc (CUDA graph capture, tight serving loops, harnesses that forbid it): allocates nothing, copies nothing, does not
+ * synchronise.  dev_counts: DEVICE uint64[n_bins] (e.g. kdb_device_table of a finished context); dev_out_ids: DEVICE
+ * uint64[cap], receives the first min(cap, *dev_n) ascending ids with zero count; dev_n: DEVICE uint64[1], the number of zero
+ * bins; stream: a cudaStream_t (NULL = default stream) on which three kernels are queued.  The block counts / offsets live in a
+ * static device array of the library sized for n_bins <= 4^14 = 268435456 (1.5 MiB per GPU, held until exit): larger n_bins
+ * -> KDB_E_ARG with kdb_last_error(NULL) saying so.  Every call shares that array: calls that overlap on the GPU race.  The
+ * first call on a device resolves the array's address; make it outside a capture. */
+int kdb_nullomers_static(int device, const uint64_t* dev_counts, size_t n_bins, uint64_t* dev_out_ids, size_t cap, uint64_t* dev_n, void* stream);
 
 /* Multi-GPU: the device pointer of the uint64[4^k] partial table and of the
  * additive scalar pack, for the caller's collective (torch.distributed / NCCL sum-reduce), and

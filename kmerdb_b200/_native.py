@@ -15,7 +15,7 @@ KDB_CANONICAL, KDB_SKIP_N, KDB_FASTQ, KDB_EDGE_KPLUS1 = 1, 2, 4, 8
 
 EXPORTS = [
     "kdb_create", "kdb_destroy", "kdb_last_error", "kdb_feed_host", "kdb_feed_device", "kdb_finish", "kdb_stats",
-    "kdb_counts", "kdb_nullomers", "kdb_device_table", "kdb_export_partials", "kdb_import_partials", "kdb_refinalize",
+    "kdb_counts", "kdb_nullomers", "kdb_nullomers_static", "kdb_device_table", "kdb_export_partials", "kdb_import_partials", "kdb_refinalize",
     "kdb_reset", "kdb_timing", "kdb_kmer_to_id_batch", "kdb_synth_record_bytes", "kdb_synth_device",
     "kdb_synth_host", "kdb_microbench_atomics", "kdb_dev_alloc", "kdb_dev_free", "kdb_host_alloc_pinned",
     "kdb_host_free_pinned", "kdb_memcpy_h2d", "kdb_memcpy_d2h", "kdb_nccl_unique_id", "kdb_reduce_nccl", "kdb_reduce_peers",
@@ -67,6 +67,7 @@ def lib():
         ("kdb_stats", [vp, ctypes.POINTER(Stats)]), ("kdb_counts", [vp, vp]),
         ("kdb_nullomers", [vp, vp, sz, ctypes.POINTER(sz)]),
         ("kdb_device_table", [vp, ctypes.POINTER(vp), ctypes.POINTER(sz)]),
+        ("kdb_nullomers_static", [ci, vp, sz, vp, sz, vp, vp]),
         ("kdb_export_partials", [vp, vp]), ("kdb_import_partials", [vp, vp]), ("kdb_refinalize", [vp]),
         ("kdb_attach", [vp, vp]),
         ("kdb_format_rows", [ci, vp, u64, u64, vp, vp, vp, sz, vp, sz, ctypes.POINTER(sz)]), ("kdb_reset", [vp]), ("kdb_timing", [vp, ctypes.POINTER(Timing)]),

@@ -1668,3 +1668,81 @@ extern "C" int kdb_correlation_matrix(int device, const uint64_t* profiles, size
         }
     return KDB_OK;
 }
+
+// ---- an entry point that allocates nothing (no counterpart in the reference) ---------
+// kdb_nullomers_static: the ascending ids with zero count (what kdb_nullomers returns) for callers that cannot call cudaMalloc
+// (CUDA graph capture, tight serving loops, harnesses that forbid it).  The per-block zero counts and offsets that kdb_nullomers
+// keeps in a cudaMalloc'ed per-context buffer live in ONE file-scope device array here, sized for 4^14 bins (1.5 MiB, held by
+// every GPU that loads the library until exit); the exclusive scan of the block counts runs on the device (kdb_nullomers does it
+// on the host), so the call queues three kernels on the caller's stream and returns: no allocation, no copy, no synchronisation.
+// All calls share the array: every word a call reads was written by that call before (nothing has to start at zero, stale
+// contents of earlier calls are never read), but two calls that overlap on the GPU (different streams, or graphs replayed
+// concurrently) race on it.
+constexpr unsigned long long kStaticMaxBins = 1ull << 28;                       // 4^14
+constexpr unsigned int kStaticMaxBlocks = (unsigned int)(kStaticMaxBins / kNullBlock);
+struct NullScratch {
+    unsigned long long off[kStaticMaxBlocks];       // exclusive scan of cnt
+    unsigned int cnt[kStaticMaxBlocks];             // zero bins per block of kNullBlock bins
+};
+static __device__ __align__(256) unsigned char g_null_scratch[sizeof(NullScratch)];
+
+// one CTA: off[b] = sum of cnt[0, b), *total = sum of all
+__global__ void __launch_bounds__(1024) k6s_null_scan(const unsigned int* __restrict__ cnt, unsigned int blocks, unsigned long long* __restrict__ off,
+                                                      unsigned long long* __restrict__ total) {
+    __shared__ unsigned long long s_warp[32];
+    const unsigned int per = (blocks + 1023u) / 1024u;
+    const unsigned int b0 = min(blocks, threadIdx.x * per), b1 = min(blocks, b0 + per);
+    unsigned long long sum = 0;
+    for (unsigned int b = b0; b < b1; b++) sum += cnt[b];
+    unsigned long long incl = sum;
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    for (int d = 1; d < 32; d <<= 1) { const unsigned long long o = __shfl_up_sync(0xffffffffu, incl, d); if (lane >= d) incl += o; }
+    if (lane == 31) s_warp[warp] = incl;
+    __syncthreads();
+    if (warp == 0) {
+        unsigned long long w = s_warp[lane];
+        for (int d = 1; d < 32; d <<= 1) { const unsigned long long o = __shfl_up_sync(0xffffffffu, w, d); if (lane >= d) w += o; }
+        s_warp[lane] = w;
+    }
+    __syncthreads();
+    unsigned long long run = incl - sum + (warp ? s_warp[warp - 1] : 0ull);
+    for (unsigned int b = b0; b < b1; b++) { off[b] = run; run += cnt[b]; }
+    if (threadIdx.x == 1023) *total = s_warp[31];
+}
+
+// dev_counts: device uint64[n_bins] (e.g. kdb_device_table of a finished context); dev_out_ids: device uint64[cap];
+// dev_n: device uint64[1], receives the number of zero bins (at most `cap` ids are written); stream: a cudaStream_t (NULL: the
+// default stream).  The first call on a device looks the array's address up (cudaGetSymbolAddress): make it outside a capture.
+extern "C" int kdb_nullomers_static(int device, const uint64_t* dev_counts, size_t n_bins, uint64_t* dev_out_ids, size_t cap, uint64_t* dev_n,
+                                    void* stream) {
+    kdb_ctx* ctx = nullptr;
+    if (!dev_counts || !dev_n || (cap && !dev_out_ids)) { g_last_error = "kdb_nullomers_static: null pointer"; return KDB_E_ARG; }
+    if (n_bins == 0 || n_bins > kStaticMaxBins) {
+        char b[192];
+        snprintf(b, sizeof b, "kdb_nullomers_static: n_bins = %zu is outside 1 .. %llu (4^14), the size the static scratch is built for; use kdb_nullomers",
+                 n_bins, kStaticMaxBins);
+        g_last_error = b;
+        return KDB_E_ARG;
+    }
+    if (device < 0 || device >= 64) { g_last_error = "kdb_nullomers_static: device outside 0 .. 63"; return KDB_E_ARG; }
+    CK(cudaSetDevice(device));
+    static NullScratch* scratch_of[64] = {nullptr};                     // the array's DEVICE address, per device (its name is a host-side stand-in)
+    if (!scratch_of[device]) {
+        void* p = nullptr;
+        CK(cudaGetSymbolAddress(&p, g_null_scratch));
+        scratch_of[device] = static_cast<NullScratch*>(p);
+    }
+    NullScratch* sc = scratch_of[device];
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const unsigned int blocks = (unsigned int)((n_bins + kNullBlock - 1) / kNullBlock);
+    const unsigned long long* tab = reinterpret_cast<const unsigned long long*>(dev_counts);
+    k6_null_count<<<blocks, 256, 0, st>>>(tab, (unsigned long long)n_bins, sc->cnt);
+    CK(cudaGetLastError());
+    k6s_null_scan<<<1, 1024, 0, st>>>(sc->cnt, blocks, sc->off, reinterpret_cast<unsigned long long*>(dev_n));
+    CK(cudaGetLastError());
+    if (cap) {
+        k6_null_write<<<blocks, 256, 0, st>>>(tab, (unsigned long long)n_bins, sc->off, reinterpret_cast<unsigned long long*>(dev_out_ids), (unsigned long long)cap);
+        CK(cudaGetLastError());
+    }
+    return KDB_OK;
+}
