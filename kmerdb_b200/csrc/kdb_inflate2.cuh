@@ -35,50 +35,54 @@ struct LaneTable {
 __device__ __forceinline__ uint32_t lds_u16(uint32_t a) { unsigned short v; asm volatile("ld.shared.u16 %0, [%1];" : "=h"(v) : "r"(a)); return v; }
 __device__ __forceinline__ uint32_t lds_u32(uint32_t a) { uint32_t v; asm volatile("ld.shared.u32 %0, [%1];" : "=r"(v) : "r"(a)); return v; }
 
-// LSB-first bit reader of ONE thread.  The payload is staged through a ring of two 16-byte chunks per thread in shared memory,
-// filled by cp.async: when a chunk has been used up, the 16 bytes that follow the other chunk are requested into it, so a
-// request has a whole chunk's worth of symbols (some eight iterations) to arrive and NO register waits for it.  (A register
-// read-ahead does not work here: the warp stalls on the pending register at the first instruction that names it, even a
-// predicated-off move — 29 % of the samples of that version sat on one `@!P MOV`.)
+// LSB-first bit reader of ONE thread.  The payload is staged through a ring of four 8-byte chunks per thread in shared memory,
+// filled by cp.async: while chunk i is read, chunks i+1 .. i+3 hold the bytes that follow (the last two possibly still in
+// flight), so a request has two chunks' worth of symbols to arrive and NO register waits for it.  (A register read-ahead does
+// not work here: the warp stalls on the pending register at the first instruction that names it, even a predicated-off move —
+// 29 % of the samples of that version sat on one `@!P MOV`.)  A refill is a predicated shared-memory load; finished chunks are
+// re-requested by roll(), ONCE per step of the symbol loop (a step reads at most 48 bits = one chunk), so the refills themselves
+// carry no branch.
 struct BitReader1 {
-    const uint8_t* gp;                // next 16 bytes to request
-    uint32_t ring;                    // shared-memory address of this thread's chunk 0; chunk 1 lies kRingStride further
-    uint32_t ra;                      // shared-memory address of the next word
+    const uint8_t* gp;                // next 8 bytes to request
+    uint32_t ring;                    // shared-memory address of this thread's chunk 0; chunk c lies c * kChunkStride further
+    uint32_t ro;                      // ring offset of the next word (0, 4, .. 28)
+    uint32_t rc;                      // the chunk being read as of the last roll()
     unsigned long long buf;
     int cnt;
     unsigned int bits_in;
-    static constexpr uint32_t kRingStride = kDecThreads * 16;
-    __device__ __forceinline__ void fetch(uint32_t chunk_sa) {
-        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\ncp.async.commit_group;" ::"r"(chunk_sa), "l"(gp) : "memory");
-        gp += 16;
+    static constexpr uint32_t kChunkStride = kDecThreads * 8;
+    __device__ __forceinline__ void fetch(uint32_t chunk) {
+        asm volatile("cp.async.ca.shared.global [%0], [%1], 8;\ncp.async.commit_group;" ::"r"(ring + chunk * kChunkStride), "l"(gp) : "memory");
+        gp += 8;
     }
-    __device__ __forceinline__ uint32_t pop() {
-        uint32_t w;
-        asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(ra) : "memory");
-        ra += 4u;
-        if ((ra & 15u) == 0) {                                      // a chunk is used up: refill it, and the other one must have arrived
-            const uint32_t fin = ra - 16u;
-            fetch(fin);
-            ra = fin == ring ? ring + kRingStride : ring;
-            asm volatile("cp.async.wait_group 1;" ::: "memory");
+    __device__ __forceinline__ void refill_on(bool on) {            // at least 33 bits afterwards (when `on`)
+        if (on && cnt <= 32) {
+            uint32_t w;
+            asm volatile("ld.shared.u32 %0, [%1];" : "=r"(w) : "r"(ring + (ro >> 3) * kChunkStride + (ro & 7u)) : "memory");
+            buf |= (unsigned long long)w << cnt; cnt += 32; bits_in += 32;
+            ro = (ro + 4u) & 31u;
         }
-        return w;
     }
+    __device__ __forceinline__ void roll() {                        // after at most two refills
+        if ((ro >> 3) != rc) {
+            fetch(rc);
+            rc = (rc + 1u) & 3u;
+            asm volatile("cp.async.wait_group 2;" ::: "memory");   // all but the two latest requests: the chunk being read and the next
+        }
+    }
+    __device__ __forceinline__ void refill() { refill_on(true); roll(); }
     __device__ __forceinline__ void init(const uint8_t* a) {
         const uintptr_t u = (uintptr_t)a;
-        gp = reinterpret_cast<const uint8_t*>(u & ~(uintptr_t)15);
+        gp = reinterpret_cast<const uint8_t*>(u & ~(uintptr_t)7);
         asm volatile("cp.async.wait_group 0;" ::: "memory");       // (a re-start after a stored block: nothing of the old position in flight)
-        fetch(ring); fetch(ring + kRingStride);
-        asm volatile("cp.async.wait_group 1;" ::: "memory");
-        ra = ring;
-        for (unsigned int i = (unsigned int)(u & 15u) >> 2; i; i--) pop();
-        const unsigned int skip = (unsigned int)(u & 3u);
-        buf = (unsigned long long)(pop() >> (8 * skip));
-        cnt = 32 - 8 * (int)skip;
-        bits_in = (unsigned int)cnt;
-    }
-    __device__ __forceinline__ void refill() {          // at least 33 bits afterwards
-        if (cnt <= 32) { buf |= (unsigned long long)pop() << cnt; cnt += 32; bits_in += 32; }
+        fetch(0); fetch(1); fetch(2); fetch(3);
+        asm volatile("cp.async.wait_group 2;" ::: "memory");
+        rc = 0;
+        ro = (uint32_t)(u & 4u);
+        buf = 0; cnt = 0; bits_in = 0;
+        refill();
+        const int skip = 8 * (int)(u & 3u);
+        buf >>= skip; cnt -= skip; bits_in -= (unsigned int)skip;
     }
     __device__ __forceinline__ unsigned int peek(int n) const { return (unsigned int)buf & ((1u << n) - 1u); }
     __device__ __forceinline__ void drop(int n) { buf >>= n; cnt -= n; }
@@ -178,8 +182,8 @@ __global__ void __launch_bounds__(kDecThreads) k_inflate_decode(const uint8_t* _
     uint32_t* const tok0 = tokens + 4ull * M.pad;
     unsigned int n_tok = 0;
     BitReader1 br;
-    br.ring = (uint32_t)__cvta_generic_to_shared(s_dec + (size_t)kDecThreads * kDecHalfWords) + threadIdx.x * 16u;
-    br.gp = comp; br.ra = br.ring; br.buf = 0; br.cnt = 0; br.bits_in = 0;
+    br.ring = (uint32_t)__cvta_generic_to_shared(s_dec + (size_t)kDecThreads * kDecHalfWords) + threadIdx.x * 8u;
+    br.gp = comp; br.ro = 0; br.rc = 0; br.buf = 0; br.cnt = 0; br.bits_in = 0;
     if (have) br.init(payload);
     unsigned int pos = 0, err = 0, run = 0, mlen = 0;
     bool done = !have;
@@ -271,7 +275,7 @@ __global__ void __launch_bounds__(kDecThreads) k_inflate_decode(const uint8_t* _
             const bool act = in_block && !parked;
             // literal / length symbol
             const bool act1 = act && !dist_next;
-            if (act1) br.refill();
+            br.refill_on(act1);
             unsigned int e1 = lds_u16(tab_sa + (kLitOff + br.peek(kDecLitBits)) * (2u * kDecThreads));
             if (pre1) e1 = pre1;
             pre1 = 0;
@@ -291,7 +295,7 @@ __global__ void __launch_bounds__(kDecThreads) k_inflate_decode(const uint8_t* _
             if (len_sym) { mlen = (be & 0xFFFFu) + br.take((int)(be >> 16)); dist_next = true; }
             // its distance
             const bool act2 = in_block && !parked && dist_next;
-            if (act2) br.refill();
+            br.refill_on(act2);
             unsigned int e2 = lds_u16(tab_sa + (kDistOff + br.peek(kDecDistBits)) * (2u * kDecThreads));
             if (pre2) e2 = pre2;
             pre2 = 0;
@@ -312,6 +316,7 @@ __global__ void __launch_bounds__(kDecThreads) k_inflate_decode(const uint8_t* _
                     pos += mlen;
                 }
             }
+            br.roll();
             ib = __ballot_sync(0xffffffffu, in_block);
             const unsigned int pb = __ballot_sync(0xffffffffu, in_block && parked);
             if (pb && (__popc(pb) >= 8 || pb == ib)) {              // long codes: eight lanes wait, or nobody else can go on
