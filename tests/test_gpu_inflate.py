@@ -126,3 +126,56 @@ def test_fastq_reads_bgzf_equal_uncompressed():
     two = parse.profile_bgzf(_bgzf(text, level=1), 12, "fastq", True, True)
     assert two is not None and np.array_equal(one.counts, two.counts) and one.total_reads == two.total_reads == 40000
     assert one.mononucleotides == two.mononucleotides
+
+
+@pytest.mark.parametrize("fmt,block,env", [("fasta", 65280, {"KDB_INFLATE_PIECE": "64"}), ("fastq", 65280, {"KDB_INFLATE_PIECE": "64"}),
+                                           ("fasta", 60000, {"KDB_INFLATE_PIECE": "64"}), ("fasta", 65280, {"KDB_INFLATE_SERIAL": "1"})])
+def test_pipelined_pieces_equal_the_uncompressed_feed(fmt, block, env, monkeypatch):
+    """kdb_feed_bgzf_host cuts the file into pieces on tile borders (copy, inflate and count overlap piece by piece): many small
+    pieces, records and lines crossing every cut; members that cannot be cut on tile borders (60 000-byte blocks) and the serial
+    path give the same profile."""
+    for a, b in env.items():
+        monkeypatch.setenv(a, b)
+    n = 120000 if fmt == "fastq" else 200000
+    text = bytes(_native.synth_host(n, fastq=(fmt == "fastq"), seed=77))
+    blob = _bgzf(text, block=block, level=1)
+    one = parse.profile_bytes(text, 11, fmt, True, True)
+    two = parse.profile_bgzf(blob, 11, fmt, True, True)
+    assert two is not None and two.total_reads == one.total_reads == n
+    assert np.array_equal(one.counts, two.counts)
+    assert (one.min_read_length, one.max_read_length, one.mononucleotides) == (two.min_read_length, two.max_read_length, two.mononucleotides)
+    bad = bytearray(blob)
+    blocks = parse._bgzf_blocks(bytes(blob))
+    bad[blocks[len(blocks) // 2][2] + 50] ^= 0x04                   # a corrupt member in a middle piece: refused, nothing is kept
+    assert parse.profile_bgzf(bytes(bad), 11, fmt, True, True) is None
+
+
+@pytest.mark.parametrize("env", [{}, {"KDB_INFLATE_PIPELINE": "1", "KDB_INFLATE_PIECE": "64"}, {"KDB_INFLATE_LATE_COPY": "1"}])
+def test_pinned_input_copy_starts_before_the_index(env, monkeypatch):
+    """From page-locked memory the compressed bytes are on their way before the member headers are walked; the result is the
+    one of the uncompressed feed, also when the call is repeated on the same context (buffers and events are reused) and for a
+    file that is not BGZF at all."""
+    for a, b in env.items():
+        monkeypatch.setenv(a, b)
+    text = bytes(_native.synth_host(150000, seed=78))
+    blob = np.frombuffer(_bgzf(text, level=6), dtype=np.uint8)
+    pin = _native.PinnedBuffer(blob.size)
+    try:
+        pin.array[:] = blob
+        want = parse.profile_bytes(text, 10, "fasta", True, True)
+        with _native.Profiler(10) as p:
+            for _ in range(3):
+                p.reset()
+                assert p.feed_bgzf(pin.array) == 0
+                assert p.finish() == 0
+                assert np.array_equal(p.counts(), want.counts)
+                assert p.stats()["total_reads"] == 150000
+            p.reset()
+            pin.array[:4] = np.frombuffer(b">abc", dtype=np.uint8)          # not gzip
+            assert p.feed_bgzf(pin.array) == _native.KDB_E_FORMAT
+            pin.array[:4] = blob[:4]
+            pin.array[blob.size // 2] ^= 0x40                               # a corrupt member
+            p.reset()
+            assert p.feed_bgzf(pin.array) == _native.KDB_E_FORMAT
+    finally:
+        pin.free()
