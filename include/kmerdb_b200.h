@@ -103,7 +103,8 @@ int kdb_feed_device(kdb_ctx* ctx, const uint8_t* dev_bytes, size_t n);
  *   it only reports the text size.  Every member is checked against its ISIZE and CRC-32.
  * kdb_feed_bgzf_host: kdb_feed_host for a whole BGZF file: compressed H2D in pieces, inflate as they arrive, then the text
  *   is tokenised and counted in place.  KDB_E_FORMAT: not BGZF / corrupt member (use the host's gzip, which raises what the
- *   reference raises). */
+ *   reference raises); the job of the context is reset then (nothing of this or earlier feeds is kept).  `raw` may be
+ *   page-locked (the copy then starts before the member headers are walked) or pageable. */
 typedef struct { uint64_t in_off, out_off; uint32_t in_len, out_len, crc, pad_; } kdb_bgzf_member_t;
 int kdb_bgzf_index(const uint8_t* raw, size_t n, kdb_bgzf_member_t* members, size_t cap, size_t* n_members, uint64_t* text_bytes);
 int kdb_inflate_bgzf(int device, const uint8_t* raw, size_t n, uint8_t* host_out, size_t out_cap, size_t* out_len);

@@ -201,7 +201,7 @@ class Profiler:
 
     def feed_bgzf(self, raw):
         """raw: a whole BGZF file (bytes-like, host memory).  Returns KDB_OK, or KDB_E_FORMAT when it is not BGZF / a member
-        is corrupt (nothing was counted then)."""
+        is corrupt (the job is reset then: nothing is kept)."""
         a = raw if isinstance(raw, np.ndarray) else np.frombuffer(raw, dtype=np.uint8)
         a = np.ascontiguousarray(a, dtype=np.uint8)
         return self._check(lib().kdb_feed_bgzf_host(self._ctx, a.ctypes.data, a.size), "kdb_feed_bgzf_host")

@@ -1107,7 +1107,12 @@ extern "C" int kdb_feed_bgzf_host(kdb_ctx* ctx, const uint8_t* raw, size_t n) {
     else CK(cudaEventElapsedTime(&ms, ctx->ev_copy[n_piece], ctx->ev_copy[n_piece - 1]));
     ctx->timing.h2d_ms += ms;
     for (size_t i = 0; i < nm; i++)
-        if (status[i]) { char b[128]; snprintf(b, sizeof b, "BGZF member %zu does not inflate (code %u)", i, status[i]); ctx->err = b; return KDB_E_FORMAT; }
+        if (status[i]) {                                          // (the same contract as the pipelined path: the job starts over)
+            for (kdb_ctx* f : ctx->followers) if (int rc = reset_state(f)) return rc;
+            if (int rc = reset_state(ctx)) return rc;
+            char b[160]; snprintf(b, sizeof b, "BGZF member %zu does not inflate (code %u); the job was reset", i, status[i]); ctx->err = b;
+            return KDB_E_FORMAT;
+        }
     const unsigned long long pass = kPassBytes;
     for (unsigned long long lo = 0; lo < text; lo += pass)
         if (int rc = run_pass2(ctx, ctx->feed_buf, lo, std::min<unsigned long long>(lo + pass, text), text)) return rc;
