@@ -353,11 +353,21 @@ __device__ __forceinline__ unsigned int warp_crc32(const uint8_t* dst, unsigned 
     unsigned int c = 0xFFFFFFFFu;
     {
         unsigned int i = b0;
-        for (; i < b1 && ((uintptr_t)(dst + i) & 3u); i++) c = s_crc[(c ^ dst[i]) & 0xFFu] ^ (c >> 8);
-        for (; i + 4 <= b1; i += 4) {
-            c ^= *reinterpret_cast<const uint32_t*>(dst + i);
-            c = s_crc[c & 0xFFu] ^ (c >> 8); c = s_crc[c & 0xFFu] ^ (c >> 8);
-            c = s_crc[c & 0xFFu] ^ (c >> 8); c = s_crc[c & 0xFFu] ^ (c >> 8);
+        for (; i < b1 && ((uintptr_t)(dst + i) & 15u); i++) c = s_crc[(c ^ dst[i]) & 0xFFu] ^ (c >> 8);
+        if (i + 16 <= b1) {                                      // 16 bytes per load, the next load in flight during the table steps
+            uint4 v = *reinterpret_cast<const uint4*>(dst + i);
+            for (; i + 16 <= b1; i += 16) {
+                uint4 nv = v;
+                if (i + 32 <= b1) nv = *reinterpret_cast<const uint4*>(dst + i + 16);
+                const uint32_t w[4] = {v.x, v.y, v.z, v.w};
+#pragma unroll
+                for (int q = 0; q < 4; q++) {
+                    c ^= w[q];
+                    c = s_crc[c & 0xFFu] ^ (c >> 8); c = s_crc[c & 0xFFu] ^ (c >> 8);
+                    c = s_crc[c & 0xFFu] ^ (c >> 8); c = s_crc[c & 0xFFu] ^ (c >> 8);
+                }
+                v = nv;
+            }
         }
         for (; i < b1; i++) c = s_crc[(c ^ dst[i]) & 0xFFu] ^ (c >> 8);
     }
@@ -380,11 +390,13 @@ __device__ __forceinline__ unsigned int warp_crc32(const uint8_t* dst, unsigned 
 // ---- kernel B: one warp per member ------------------------------------------------------------------------------------------------
 // status (from kernel A) stays unless the CRC fails (3).
 constexpr int kResWarps = 8;
+constexpr unsigned int kSpanBytes = 1024;             // the stretch of text one batch of 32 tokens is assembled in (per warp, shared memory)
 __global__ void __launch_bounds__(kResWarps * 32) k_inflate_resolve(const BgzfMember* __restrict__ members, unsigned int n_members, const uint32_t* __restrict__ tokens,
                                                                    const unsigned int* __restrict__ n_tokens, uint8_t* __restrict__ out,
                                                                    unsigned int* __restrict__ status, int check_crc) {
     __shared__ unsigned int s_mat[kResWarps][2][32];
     __shared__ unsigned int s_crc[256];
+    __shared__ __align__(16) uint32_t s_span[kResWarps][kSpanBytes / 4];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     for (int i = threadIdx.x; i < 256; i += blockDim.x) s_crc[i] = c_crc_table[i];
     __syncthreads();
@@ -409,35 +421,103 @@ __global__ void __launch_bounds__(kResWarps * 32) k_inflate_resolve(const BgzfMe
         for (int dd = 1; dd < 32; dd <<= 1) { const unsigned int o = __shfl_up_sync(0xffffffffu, incl, dd); if (lane >= dd) incl += o; }
         const unsigned int total = __shfl_sync(0xffffffffu, incl, 31);
         const unsigned int my_pos = pos + incl - my_len;                          // where my match starts
+        const unsigned int any = __ballot_sync(0xffffffffu, my_len != 0);
         // matches that read only text in place before this batch (kernel A's literals are all in place; what a batch can lack is the
         // output of its own matches, so anything that ends at or before the batch start is safe)
         const unsigned int span = my_len < my_d ? my_len : my_d;
         const bool indep = my_len != 0 && my_pos - my_d + span <= pos;
-        if (indep) {
-            const uint8_t* from = dst + my_pos - my_d;
-            uint8_t* to = dst + my_pos;
-            if (my_d >= my_len) {
-                for (unsigned int i = 0; i < my_len; i += 8) {
-                    uint8_t v[8];
-#pragma unroll
-                    for (int q = 0; q < 8; q++) v[q] = i + q < my_len ? from[i + q] : (uint8_t)0;
-#pragma unroll
-                    for (int q = 0; q < 8; q++) if (i + q < my_len) to[i + q] = v[q];
-                }
-            } else {
-                for (unsigned int i = 0; i < my_len; i++) to[i] = from[i];        // period my_d: reads what this thread has just written
+        const uintptr_t A = (uintptr_t)(dst + pos);
+        const unsigned int lead = (unsigned int)(A & 3u), nbytes = lead + total;
+        if (any && nbytes <= kSpanBytes) {
+            // The batch's stretch of text is assembled in shared memory and leaves as whole words: (a) the stretch as it is (the
+            // literals are in place), (b) the matches — sources before the stretch by aligned word loads and a funnel shift, sources
+            // inside it from shared memory in token order, (c) one coalesced store.  (Byte-wise copies in global memory, one match per
+            // lane, cost 32 sectors per instruction: the kernel was at 86 % of the LSU wavefront peak.)
+            uint32_t* const sw = s_span[warp];
+            uint8_t* const sp = reinterpret_cast<uint8_t*>(sw);
+            uint32_t* const g = reinterpret_cast<uint32_t*>(A - lead);
+            const unsigned int nwords = (nbytes + 3u) >> 2;
+            // (the first four source words of every match are requested before the stretch itself: one round trip for both)
+            const uint8_t* const from = dst + my_pos - my_d;
+            const uintptr_t S = (uintptr_t)from;
+            const uint32_t* q = reinterpret_cast<const uint32_t*>(S & ~(uintptr_t)3);
+            const bool plain = indep && my_d >= my_len;
+            uint32_t r0 = 0, r1 = 0, r2 = 0, r3 = 0;
+            if (plain) {
+                r0 = q[0]; r1 = q[1];
+                if (my_len > 4) r2 = q[2];
+                if (my_len > 8) r3 = q[3];
             }
-        }
-        __syncwarp();
-        unsigned int dep = __ballot_sync(0xffffffffu, my_len != 0 && !indep);
-        while (dep) {                                                            // in token order: each may read what the one before wrote
-            const int w = __ffs(dep) - 1;
-            dep &= dep - 1;
-            const unsigned int tl = __shfl_sync(0xffffffffu, my_len, w), td = __shfl_sync(0xffffffffu, my_d, w), tp = __shfl_sync(0xffffffffu, my_pos, w);
-            const uint8_t* from = dst + tp - td;
-            if (td >= tl) { for (unsigned int i = lane; i < tl; i += 32) dst[tp + i] = from[i]; }
-            else { for (unsigned int i = lane; i < tl; i += 32) dst[tp + i] = from[i % td]; }
+            for (unsigned int w = lane; w < nwords; w += 32) sw[w] = g[w];
             __syncwarp();
+            if (indep) {
+                uint8_t* to = sp + lead + (my_pos - pos);
+                if (plain) {
+                    const unsigned int sh = 8u * (unsigned int)(S & 3u);
+                    uint32_t lo = r0;
+                    for (unsigned int i = 0; i < my_len; i += 4) {
+                        const uint32_t hi = i == 0 ? r1 : (i == 4 ? r2 : (i == 8 ? r3 : q[(i >> 2) + 1]));
+                        const uint32_t v = __funnelshift_r(lo, hi, sh);
+                        lo = hi;
+                        to[i] = (uint8_t)v;
+                        if (i + 1 < my_len) to[i + 1] = (uint8_t)(v >> 8);
+                        if (i + 2 < my_len) to[i + 2] = (uint8_t)(v >> 16);
+                        if (i + 3 < my_len) to[i + 3] = (uint8_t)(v >> 24);
+                    }
+                } else {
+                    for (unsigned int i = 0; i < my_len; i++) to[i] = i < my_d ? from[i] : to[i - my_d];      // period my_d
+                }
+            }
+            __syncwarp();
+            unsigned int dep = any & ~__ballot_sync(0xffffffffu, indep);
+            while (dep) {                                                        // in token order: each may read what the one before wrote
+                const int w = __ffs(dep) - 1;
+                dep &= dep - 1;
+                const unsigned int tl = __shfl_sync(0xffffffffu, my_len, w), td = __shfl_sync(0xffffffffu, my_d, w), tp = __shfl_sync(0xffffffffu, my_pos, w);
+                for (unsigned int i = lane; i < tl; i += 32) {
+                    const unsigned int p = tp - td + (td >= tl ? i : i % td);    // source position in the member (before tp)
+                    sp[lead + (tp - pos) + i] = p < pos ? dst[p] : sp[lead + (p - pos)];
+                }
+                __syncwarp();
+            }
+            for (unsigned int w = lane; w < nwords; w += 32) {
+                const uint32_t v = sw[w];
+                const unsigned int b0 = 4u * w;
+                if (b0 >= lead && b0 + 4u <= nbytes) g[w] = v;
+                else {                                                           // the first / last word of the stretch: only its own bytes
+                    uint8_t* gb = reinterpret_cast<uint8_t*>(g + w);
+#pragma unroll
+                    for (unsigned int q = 0; q < 4; q++) if (b0 + q >= lead && b0 + q < nbytes) gb[q] = (uint8_t)(v >> (8u * q));
+                }
+            }
+            __syncwarp();
+        } else if (any) {                                                        // a stretch too long to stage: copies in global memory
+            if (indep) {
+                const uint8_t* from = dst + my_pos - my_d;
+                uint8_t* to = dst + my_pos;
+                if (my_d >= my_len) {
+                    for (unsigned int i = 0; i < my_len; i += 8) {
+                        uint8_t v[8];
+#pragma unroll
+                        for (int q = 0; q < 8; q++) v[q] = i + q < my_len ? from[i + q] : (uint8_t)0;
+#pragma unroll
+                        for (int q = 0; q < 8; q++) if (i + q < my_len) to[i + q] = v[q];
+                    }
+                } else {
+                    for (unsigned int i = 0; i < my_len; i++) to[i] = from[i];    // period my_d: reads what this thread has just written
+                }
+            }
+            __syncwarp();
+            unsigned int dep = any & ~__ballot_sync(0xffffffffu, indep);
+            while (dep) {
+                const int w = __ffs(dep) - 1;
+                dep &= dep - 1;
+                const unsigned int tl = __shfl_sync(0xffffffffu, my_len, w), td = __shfl_sync(0xffffffffu, my_d, w), tp = __shfl_sync(0xffffffffu, my_pos, w);
+                const uint8_t* from = dst + tp - td;
+                if (td >= tl) { for (unsigned int i = lane; i < tl; i += 32) dst[tp + i] = from[i]; }
+                else { for (unsigned int i = lane; i < tl; i += 32) dst[tp + i] = from[i % td]; }
+                __syncwarp();
+            }
         }
         pos += total;
     }
