@@ -129,7 +129,9 @@ def test_fastq_reads_bgzf_equal_uncompressed():
 
 
 @pytest.mark.parametrize("fmt,block,env", [("fasta", 65280, {"KDB_INFLATE_PIECE": "64"}), ("fastq", 65280, {"KDB_INFLATE_PIECE": "64"}),
-                                           ("fasta", 60000, {"KDB_INFLATE_PIECE": "64"}), ("fasta", 65280, {"KDB_INFLATE_SERIAL": "1"})])
+                                           ("fasta", 60000, {"KDB_INFLATE_PIECE": "64"}), ("fasta", 65280, {"KDB_INFLATE_SERIAL": "1"}),
+                                           ("fasta", 65280, {"KDB_INFLATE_SERIAL": "1", "KDB_INFLATE_PIECE": "100"}),
+                                           ("fastq", 65280, {"KDB_INFLATE_SERIAL": "1", "KDB_INFLATE_PIECE": "37"})])
 def test_pipelined_pieces_equal_the_uncompressed_feed(fmt, block, env, monkeypatch):
     """kdb_feed_bgzf_host cuts the file into pieces on tile borders (copy, inflate and count overlap piece by piece): many small
     pieces, records and lines crossing every cut; members that cannot be cut on tile borders (60 000-byte blocks) and the serial
@@ -150,7 +152,7 @@ def test_pipelined_pieces_equal_the_uncompressed_feed(fmt, block, env, monkeypat
     assert parse.profile_bgzf(bytes(bad), 11, fmt, True, True) is None
 
 
-@pytest.mark.parametrize("env", [{}, {"KDB_INFLATE_PIPELINE": "1", "KDB_INFLATE_PIECE": "64"}, {"KDB_INFLATE_LATE_COPY": "1"}])
+@pytest.mark.parametrize("env", [{}, {"KDB_INFLATE_PIPELINE": "1", "KDB_INFLATE_PIECE": "64"}, {"KDB_INFLATE_LATE_COPY": "1"}, {"KDB_INFLATE_PIECE": "50"}])
 def test_pinned_input_copy_starts_before_the_index(env, monkeypatch):
     """From page-locked memory the compressed bytes are on their way before the member headers are walked; the result is the
     one of the uncompressed feed, also when the call is repeated on the same context (buffers and events are reused) and for a
