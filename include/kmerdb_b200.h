@@ -97,7 +97,7 @@ int kdb_feed_device(kdb_ctx* ctx, const uint8_t* dev_bytes, size_t n);
 
 /* Compressed input (the reference opens every input through gzip.open, kmerdb/parse.py:63-68).  BGZF
  * (bgzip / Bio.bgzf: independent gzip members of <= 64 KiB of text, size in the 'BC' extra subfield) is inflated ON THE
- * DEVICE, one warp per member, so the compressed bytes are what crosses PCIe.
+ * DEVICE (one thread per member decodes, one warp per member resolves the matches), so the compressed bytes are what crosses PCIe.
  * kdb_bgzf_index: host walk of the member headers (RFC 1952 subfields); KDB_E_FORMAT when `raw` is not BGZF.
  * kdb_inflate_bgzf: the text of a BGZF buffer (host -> device -> inflate -> host), for tests and tools; with host_out == NULL
  *   it only reports the text size.  Every member is checked against its ISIZE and CRC-32.

@@ -407,7 +407,7 @@ def profile_bytes(data, k, fmt="fasta", replace_with_none=True, canonicalize=Tru
 
 
 def profile_bgzf(raw, k, fmt="fasta", replace_with_none=True, canonicalize=True, device=0, want_nullomers=True):
-    """BGZF input: the COMPRESSED bytes go to the device and are inflated there, one warp per member
+    """BGZF input: the COMPRESSED bytes go to the device and are inflated there (a thread per member decodes, a warp per member resolves)
     (kdb_feed_bgzf_host), then tokenised and counted in place.  Returns None when `raw` is not BGZF, a member fails its
     CRC-32 / ISIZE, or the text needs the host tokeniser: the caller then takes the host gzip path, which raises what the
     reference's gzip.open raises."""

@@ -1,5 +1,5 @@
 """f2: BGZF input inflated on the GPU.  The reference opens inputs through gzip.open (kmerdb/parse.py:63-68);
-here the compressed members cross PCIe and one warp inflates each.  Oracle: zlib on the host (the same library gzip.open
+here the compressed members cross PCIe and are inflated on the device (one thread per member decodes, one warp resolves).  Oracle: zlib on the host (the same library gzip.open
 uses).  Inputs: the reference's bundled genomes re-blocked as BGZF, synthetic reads, and blocks that force every DEFLATE
 block type (stored, fixed, dynamic), long matches, overlapping matches and codes longer than the first-level table."""
 import gzip
